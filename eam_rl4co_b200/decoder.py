@@ -1,0 +1,145 @@
+"""AttentionModel decoder, host side (mirror of rl4co/models/zoo/am/decoder.py).
+
+Parameter names match the reference so its checkpoints load unchanged:
+  context_embedding.project_context.weight [E, 2E | E+1], context_embedding.W_placeholder [2E]
+  (TSP), pointer.project_out.weight [E,E], project_node_embeddings.weight [3E,E],
+  project_fixed_context.weight [E,E].
+`pre_decoder_hook` builds the per-instance tables with ordinary GEMMs once per rollout
+(am/decoder.py:206-235 stays in torch); `forward` is one decoder step on the
+sm_100a kernel `rl4co_decode_step`.
+"""
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import _lib
+
+
+class TSPContext(nn.Module):  # context.py:105-140
+    def __init__(self, embed_dim):
+        super().__init__()
+        self.embed_dim = embed_dim
+        self.project_context = nn.Linear(2 * embed_dim, embed_dim, bias=False)
+        self.W_placeholder = nn.Parameter(torch.Tensor(2 * embed_dim).uniform_(-1, 1))
+
+
+class VRPContext(nn.Module):  # context.py:143-157
+    def __init__(self, embed_dim):
+        super().__init__()
+        self.embed_dim = embed_dim
+        self.project_context = nn.Linear(embed_dim + 1, embed_dim, bias=False)
+
+
+class PointerAttention(nn.Module):  # attention.py:224-328
+    def __init__(self, embed_dim, num_heads, mask_inner=True, check_nan=True):
+        super().__init__()
+        self.num_heads = num_heads
+        self.mask_inner = mask_inner
+        self.check_nan = check_nan
+        self.project_out = nn.Linear(embed_dim, embed_dim, bias=False)
+
+
+@dataclass
+class PrecomputedCache:
+    """am/decoder.py:22-41 plus the folded tables the kernels read (include/rl4co_b200.h)."""
+    node_embeddings: torch.Tensor
+    graph_context: object
+    glimpse_key: torch.Tensor
+    glimpse_val: torch.Tensor
+    logit_key_folded: torch.Tensor        # L @ W_out
+    pa: Optional[torch.Tensor]
+    pb: torch.Tensor
+    q0: Optional[torch.Tensor]
+    wcap: Optional[torch.Tensor]
+    env_id: int
+    _logit_key_w: Optional[torch.Tensor] = None
+
+    @property
+    def logit_key(self):
+        return F.linear(self.node_embeddings, self._logit_key_w)
+
+    def cstruct(self) -> _lib.Cache:
+        B, n, E = self.node_embeddings.shape
+        p = lambda t: (t.data_ptr() if t is not None else None)
+        return _lib.Cache(p(self.glimpse_key), p(self.glimpse_val), p(self.logit_key_folded), p(self.pa),
+                          p(self.pb), p(self.q0), p(self.wcap), B, n, E, 8)
+
+
+class AttentionModelDecoder(nn.Module):
+    def __init__(self, embed_dim: int = 128, num_heads: int = 8, env_name: str = "tsp",
+                 mask_inner: bool = True, use_graph_context: bool = True, check_nan: bool = True,
+                 linear_bias: bool = False, out_bias_pointer_attn: bool = False, **unused):
+        super().__init__()
+        if embed_dim != 128 or num_heads != 8:
+            raise NotImplementedError("rl4co_b200 kernels are built for embed_dim=128, num_heads=8")
+        if linear_bias or out_bias_pointer_attn or not mask_inner:
+            raise NotImplementedError("decoder biases / mask_inner=False are not supported by the fused path")
+        if env_name not in ("tsp", "cvrp"):
+            raise NotImplementedError(f"env '{env_name}' is outside the accelerated path (tsp, cvrp)")
+        self.env_name, self.embed_dim, self.num_heads = env_name, embed_dim, num_heads
+        self.context_embedding = TSPContext(embed_dim) if env_name == "tsp" else VRPContext(embed_dim)
+        self.pointer = PointerAttention(embed_dim, num_heads, mask_inner, check_nan)
+        self.project_node_embeddings = nn.Linear(embed_dim, 3 * embed_dim, bias=False)
+        self.project_fixed_context = nn.Linear(embed_dim, embed_dim, bias=False)
+        self.use_graph_context = use_graph_context
+        self.is_dynamic_embedding = False
+
+    def pre_decoder_hook(self, td, env, embeddings, num_starts: int = 0):
+        return td, env, self._precompute_cache(embeddings, num_starts=num_starts)
+
+    @torch.no_grad()
+    def _precompute_cache(self, h: torch.Tensor, num_starts: int = 0) -> PrecomputedCache:
+        E = self.embed_dim
+        B, n, _ = h.shape
+        Wk, Wv, Wl = self.project_node_embeddings.weight.chunk(3, dim=0)
+        Wo = self.pointer.project_out.weight
+        Wc = self.context_embedding.project_context.weight
+        Wl_folded = Wo.t() @ Wl                     # L @ W_out == h @ (W_out^T W_l)^T
+        if self.use_graph_context:
+            gc = F.linear(h.mean(1), self.project_fixed_context.weight)   # decoder.py:223-224
+        else:
+            gc = 0
+        tsp = self.env_name == "tsp"
+        ws = [Wk, Wv, Wl_folded, Wc[:, :E]] + ([Wc[:, E:]] if tsp else [])
+        W = torch.stack([w.contiguous() for w in ws])                       # [k, E, E]
+        tabs = torch.matmul(h.reshape(1, B * n, E), W.transpose(1, 2)).view(len(ws), B, n, E)
+        gk, gv, lkf = tabs[0], tabs[1], tabs[2]
+        gcb = gc[:, None, :] if isinstance(gc, torch.Tensor) else 0
+        if tsp:
+            pa, pb = tabs[3], (tabs[4] + gcb).contiguous()
+            q0 = F.linear(self.context_embedding.W_placeholder, Wc)[None, :].expand(B, E)
+            q0 = (q0 + gc).contiguous()
+            wcap = None
+        else:
+            pa, pb, q0 = None, (tabs[3] + gcb).contiguous(), None
+            wcap = Wc[:, E].contiguous()
+        return PrecomputedCache(h, gc, gk, gv, lkf, pa, pb, q0, wcap,
+                                _lib.ENV_TSP if tsp else _lib.ENV_CVRP, Wl)
+
+    @torch.no_grad()
+    def forward(self, td, cached: PrecomputedCache, num_starts: int = 0):
+        """am/decoder.py:161-198 -> (logits [rows,N'], mask [rows,N']) in start-major row order."""
+        mask = td["action_mask"].contiguous()
+        rows, n = mask.shape
+        dev = mask.device
+        logits = torch.empty(rows, n, dtype=torch.float32, device=dev)
+        err = _lib.new_err(dev)
+        cs = cached.cstruct()
+        cur = td["current_node"].contiguous()
+        if self.env_name == "tsp":
+            first, i_step, used, cap = td["first_node"].contiguous(), td["i"].contiguous(), None, None
+        else:
+            first, i_step = None, None
+            used, cap = td["used_capacity"].contiguous(), td["vehicle_capacity"].contiguous()
+        rc = _lib.lib().rl4co_decode_step(
+            C.c_int32(cached.env_id), C.byref(cs), _lib.ptr(first), _lib.ptr(cur), _lib.ptr(i_step),
+            _lib.ptr(used), _lib.ptr(cap), _lib.ptr(mask), _lib.ptr(logits), _lib.ptr(err),
+            C.c_int64(rows), _lib.stream_ptr())
+        _lib.check(rc, "rl4co_decode_step")
+        if self.pointer.check_nan:
+            _lib.raise_on_err(err)      # attention.py:303-304 (the reference syncs here too)
+        return logits, mask

@@ -1,0 +1,173 @@
+/*
+ * rl4co_b200 — C ABI of the B200-native construction-rollout path.
+ *
+ * One shared library (librl4co_b200.so), `extern "C"`, plain device pointers and sizes,
+ * no C++/torch types.  Every function launches on the CUDA stream passed as `stream`
+ * (a cudaStream_t cast to void*), never allocates or frees, and returns 0 on success or a
+ * negative RL4CO_E_* code for argument / launch errors (text via rl4co_last_error()).
+ * Semantic failures the reference raises as AssertionError (NaN logits, infeasible action,
+ * -inf log-prob, invalid tour, capacity exceeded) are reported through a caller-owned
+ * device `int32 err[2]` word: err[0] = OR of RL4CO_ERR_* bits, err[1] = first offending row+1.
+ *
+ * All citations are file:line in the reference (Tarseus/eam-rl4co, RL4CO v0.6 fork).
+ * Row order at this boundary is the reference's start-major order: row = s*B + b
+ * (rl4co/utils/ops.py:13-16, rl4co/models/zoo/am/decoder.py:195-197).
+ * dtypes follow the reference's TensorDict: actions/current_node/first_node/i int64,
+ * action_mask/done bool (1 byte), visited uint8, everything else float32.
+ */
+#ifndef RL4CO_B200_H
+#define RL4CO_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RL4CO_B200_ABI_VERSION 1
+
+/* return codes */
+#define RL4CO_OK 0
+#define RL4CO_E_ARG (-1)      /* bad size / null pointer / unsupported shape (e.g. N' > limit) */
+#define RL4CO_E_LAUNCH (-2)   /* CUDA launch or runtime error */
+#define RL4CO_E_UNSUPPORTED (-3)
+
+/* err[0] bits — reference assertion they stand for */
+#define RL4CO_ERR_NAN_LOGITS 1      /* "Logits contain NaNs"            attention.py:303-304 */
+#define RL4CO_ERR_INFEASIBLE 2      /* "infeasible action selected"     decoding.py:397-399,413-415 */
+#define RL4CO_ERR_NEG_INF_LOGP 4    /* "Logprobs should not be -inf"    decoding.py:56-58 */
+#define RL4CO_ERR_INVALID_TOUR 8    /* "Invalid tour"                   tsp/env.py:163-168, cvrp/env.py:165-170 */
+#define RL4CO_ERR_CAPACITY 16       /* "Used more than capacity"        cvrp/env.py:176-185 */
+#define RL4CO_ERR_MAX_STEPS 32      /* max_steps exceeded               constructive/base.py:246-250 */
+
+/* env ids, decode modes */
+#define RL4CO_ENV_TSP 0
+#define RL4CO_ENV_CVRP 1
+#define RL4CO_MODE_GREEDY 0         /* decoding.py:391-401 */
+#define RL4CO_MODE_SAMPLING 1       /* decoding.py:403-417 with supplied / counter noise */
+#define RL4CO_MODE_EVALUATE 2       /* decoding.py:452-465 */
+
+int rl4co_b200_abi_version(void);
+const char* rl4co_last_error(void);
+
+/* ---- TSPEnv._step — rl4co/envs/routing/tsp/env.py:62-88 -----------------------------
+ * first_out = action if any(i_in == 0) else first_in   (batch-global test, :65)
+ * mask_out = mask_in with bit `action` cleared (:68-70); done = no bit left (:73);
+ * i_out = i_in + 1; reward_out = 0 (bool, :76).  cur_out = action.                     */
+int rl4co_tsp_step(const int64_t* action, const uint8_t* mask_in, const int64_t* i_in,
+                   const int64_t* first_in, uint8_t* mask_out, int64_t* cur_out,
+                   int64_t* first_out, int64_t* i_out, uint8_t* done_out, uint8_t* reward_out,
+                   int32_t* scratch_flag /* device int32, clobbered */,
+                   int64_t rows, int32_t n_nodes, void* stream);
+
+/* ---- CVRPEnv._step + get_action_mask — rl4co/envs/routing/cvrp/env.py:68-100,132-144 --
+ * demand is [demand_rows, N] (customers only); row r uses demand row r % demand_rows so a
+ * multistart caller need not batchify it.  n_nodes = N+1 (depot = node 0).               */
+int rl4co_cvrp_step_mask(const int64_t* action, const float* demand, int64_t demand_rows,
+                         const float* used_in, const float* vehicle_capacity,
+                         const uint8_t* visited_in, float* used_out, uint8_t* visited_out,
+                         int64_t* cur_out, uint8_t* done_out, uint8_t* reward_out,
+                         uint8_t* mask_out, int64_t rows, int32_t n_nodes, void* stream);
+
+/* ---- CVRPEnv.get_action_mask alone — cvrp/env.py:132-144 (used by _reset :129) -------- */
+int rl4co_cvrp_action_mask(const float* demand, int64_t demand_rows, const float* used,
+                           const float* vehicle_capacity, const uint8_t* visited,
+                           const int64_t* current_node, uint8_t* mask_out, int64_t rows,
+                           int32_t n_nodes, void* stream);
+
+/* ---- _get_reward (+ check_solution_validity) ------------------------------------------
+ * tsp/env.py:152-168, cvrp/env.py:146-185, ops.py:59-95.
+ * locs [loc_rows, n_nodes, 2] (CVRP: depot at node 0); row r uses locs row r % loc_rows.
+ * reward[r] = -(closed tour length); CVRP prepends the depot (cvrp/env.py:148-154).
+ * check != 0 sets RL4CO_ERR_INVALID_TOUR / RL4CO_ERR_CAPACITY in err (demand/capacity
+ * then required for CVRP).                                                               */
+int rl4co_tour_reward(int32_t env, const float* locs, int64_t loc_rows, const int64_t* actions,
+                      int64_t actions_row_stride, int32_t T, const float* demand,
+                      int64_t demand_rows, const float* vehicle_capacity, float* reward,
+                      int32_t check, int32_t* err, int64_t rows, int32_t n_nodes, void* stream);
+
+/* ---- process_logits + DecodingStrategy.step — decoding.py:140-190, 346-465 -------------
+ * logits [rows,n] (read-only; the reference mutates a tanh temp, not the input),
+ * mask bool [rows,n].  logp_all (nullable) receives log_softmax [rows,n].
+ * mode GREEDY: first max index; SAMPLING: argmax(logp + gumbel) with gumbel [rows,n] given,
+ * or generated from (seed, inst_offset + r % B, r / B, t, node) when gumbel == NULL;
+ * EVALUATE: action_in.  Writes action_out, logp_sel.                                      */
+int rl4co_select(const float* logits, const uint8_t* mask, float tanh_clipping,
+                 float temperature, int32_t mode, const float* gumbel, uint32_t seed,
+                 int64_t inst_offset, int64_t B, int32_t t, const int64_t* action_in,
+                 float* logp_all, int64_t* action_out, float* logp_sel, int32_t* err,
+                 int64_t rows, int32_t n_nodes, void* stream);
+
+/* ---- Precomputed per-instance tables consumed by the decoder kernels --------------------
+ * Built by the host with ordinary GEMMs once per rollout (am/decoder.py:206-235 stays in
+ * torch).  All [B, n_nodes, E] fp32 contiguous, E = 128, H = 8:
+ *   gk, gv : glimpse key / value                      (decoder.py:216-220)
+ *   lk     : logit key folded with project_out:  L @ W_out     (attention.py:299,328)
+ *   pa     : TSP  h @ W_ctx[:, :E]^T  (first-node half, context.py:118-140); CVRP NULL
+ *   pb     : TSP  h @ W_ctx[:, E:]^T + graph_context ; CVRP h @ W_ctx[:, :E]^T + graph_context
+ *   q0     : TSP  [B,E] W_ctx @ W_placeholder + graph_context (context.py:124-132); CVRP NULL
+ *   wcap   : CVRP [E] W_ctx[:, E]  (remaining-capacity column, context.py:155-157); TSP NULL  */
+typedef struct rl4co_cache {
+    const float* gk;
+    const float* gv;
+    const float* lk;
+    const float* pa;
+    const float* pb;
+    const float* q0;
+    const float* wcap;
+    int64_t B;
+    int32_t n_nodes;
+    int32_t embed_dim; /* must be 128 */
+    int32_t num_heads; /* must be 8   */
+} rl4co_cache;
+
+/* ---- AttentionModelDecoder.forward — am/decoder.py:161-198 (+ context.py, attention.py) --
+ * One decoder step for all rows: returns logits [rows, n_nodes] in row order.
+ * TSP state: first_node, current_node int64 [rows], i int64 [rows] (i==0 -> placeholder);
+ * CVRP state: current_node int64 [rows], used_capacity, vehicle_capacity float [rows].
+ * mask bool [rows, n_nodes].  Row r belongs to instance r % cache->B.                      */
+int rl4co_decode_step(int32_t env, const rl4co_cache* cache, const int64_t* first_node,
+                      const int64_t* current_node, const int64_t* i_step,
+                      const float* used_capacity, const float* vehicle_capacity,
+                      const uint8_t* mask, float* logits_out, int32_t* err, int64_t rows,
+                      void* stream);
+
+/* ---- ConstructivePolicy.forward main loop, fused — constructive/base.py:221-263 ----------
+ * Persistent kernel: multistart pre-hook (decoding.py:284-332), decoder step, process_logits,
+ * selection, env step and reward for ALL steps of every row, no host sync.                  */
+typedef struct rl4co_rollout_args {
+    int32_t env;               /* RL4CO_ENV_*                                               */
+    int32_t mode;              /* RL4CO_MODE_*                                              */
+    int32_t num_starts;        /* S; 0 or 1 = single start (no forced first action)         */
+    int32_t max_steps;         /* T_alloc: columns available in actions / logp              */
+    float tanh_clipping;       /* 10.0 (am/policy.py:70)                                    */
+    float temperature;         /* 1.0                                                       */
+    uint32_t seed;             /* counter-noise seed (SAMPLING, gumbel == NULL)             */
+    int64_t inst_offset;       /* global index of instance 0 of this shard (noise key)      */
+    const float* locs;         /* [B, n_nodes, 2] (CVRP: depot first)                       */
+    const float* demand;       /* CVRP [B, n_nodes-1] (already / capacity); TSP NULL        */
+    const float* vehicle_capacity; /* CVRP [B]; TSP NULL                                    */
+    const float* gumbel;       /* nullable [rows, max_steps, n_nodes] supplied noise        */
+    const int64_t* actions_in; /* EVALUATE: [rows, actions_in_stride]; multistart: col 0 = start */
+    int64_t actions_in_stride;
+    int32_t actions_in_T;
+    int64_t* actions;          /* out [rows, max_steps] (pre-zeroed by caller)              */
+    float* logp;               /* out [rows, max_steps] (pre-zeroed by caller)              */
+    float* logp_all;           /* nullable out [rows, max_steps, n_nodes] (store_all_logp)  */
+    float* reward;             /* out [rows]  = -tour length                                */
+    float* log_likelihood;     /* out [rows]  = sum_t logp                                  */
+    int32_t* lengths;          /* out [rows]  actions emitted before the row was done       */
+    int32_t* max_len;          /* out device int32: max over rows of lengths (pre-zeroed)   */
+    int32_t* err;              /* device int32[2] (pre-zeroed)                              */
+} rl4co_rollout_args;
+
+int rl4co_rollout(const rl4co_cache* cache, const rl4co_rollout_args* args, void* stream);
+
+/* counter-noise reference values, for tests: gumbel [rows, n_nodes] at step t */
+int rl4co_noise_gumbel(uint32_t seed, int64_t inst_offset, int64_t B, int32_t t, float* out,
+                       int64_t rows, int32_t n_nodes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RL4CO_B200_H */
