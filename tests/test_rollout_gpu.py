@@ -1,0 +1,181 @@
+"""GPU: the fused persistent rollout (`policy(td, env, decode_type=...)`) and the step-granular
+loop vs the oracle, tie-aware, plus the reference fixtures."""
+import pytest
+import torch
+
+import eam_rl4co_b200 as P
+from oracle import rollout_oracle as O
+from helpers import (LL_RTOL, compare_rollout, decoder_weights, golden_files, inst_to_env_td, load_golden,
+                     rel_close)
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+DECODE_TYPES = ["greedy", "sampling", "multistart_greedy", "multistart_sampling"]
+
+
+class _FixedEncoder(torch.nn.Module):
+    def __init__(self, h):
+        super().__init__()
+        self.h = h
+
+    def forward(self, td):
+        return self.h, None
+
+
+def _setup(env_name, pomo, N, B, seed=0):
+    torch.manual_seed(1234 + seed)
+    inst = O.generate_tsp(B, N) if env_name == "tsp" else O.generate_cvrp(B, N)
+    torch.manual_seed(4321)
+    pol = (P.POMOPolicy(env_name) if pomo else P.AttentionModelPolicy(env_name=env_name)).eval()
+    w = decoder_weights(pol)
+    pol = pol.to(DEV)
+    env, td = inst_to_env_td(P, env_name, inst, DEV)
+    with torch.no_grad():
+        h, _ = pol.encoder(td)
+    return inst, pol, w, env, td, h.cpu()
+
+
+@pytest.mark.parametrize("env_name", ["tsp", "cvrp"])
+@pytest.mark.parametrize("pomo,N,B", [(False, 20, 64), (False, 50, 32), (True, 20, 16), (True, 100, 4)])
+@pytest.mark.parametrize("decode_type", DECODE_TYPES)
+def test_fused_rollout_matches_oracle(env_name, pomo, N, B, decode_type):
+    if N >= 100 and not decode_type.startswith("multistart"):
+        pytest.skip("covered by the AM cases")
+    inst, pol, w, env, td, h = _setup(env_name, pomo, N, B)
+    out = pol(td.clone(), env, decode_type=decode_type, noise_seed=2026, instance_offset=3)
+    stats = compare_rollout(env_name, inst, h, w, not pomo, out, decode_type, noise_seed=2026,
+                            instance_offset=3)
+    S = N if decode_type.startswith("multistart") else 1
+    assert out["reward"].shape == (B * S,) and out["log_likelihood"].shape == (B * S,)
+    assert out["actions"].dtype == torch.int64
+    if stats["exact"] == 1.0:
+        assert stats["T_got"] == stats["T_ref"]
+
+
+@pytest.mark.parametrize("env_name", ["tsp", "cvrp"])
+@pytest.mark.parametrize("multistart", [False, True])
+def test_fused_evaluate_reproduces_log_likelihood(env_name, multistart):
+    N, B = 20, 12
+    inst, pol, w, env, td, h = _setup(env_name, multistart, N, B, seed=1)
+    dt = "multistart_sampling" if multistart else "sampling"
+    out = pol(td.clone(), env, decode_type=dt, noise_seed=5)
+    kw = dict(num_starts=N) if multistart else {}
+    ev = pol(td.clone(), env, actions=out["actions"], **kw)
+    assert torch.equal(ev["actions"], out["actions"])
+    assert rel_close(ev["log_likelihood"], out["log_likelihood"], 1e-6)
+    assert rel_close(ev["reward"], out["reward"], 1e-6)
+    with torch.inference_mode():
+        ref = O.rollout(env_name, inst, h, w, actions=out["actions"].cpu(),
+                        num_starts=N if multistart else None, use_graph_context=not multistart)
+    assert rel_close(ev["log_likelihood"], ref["log_likelihood"], LL_RTOL)
+
+
+@pytest.mark.parametrize("env_name", ["tsp", "cvrp"])
+@pytest.mark.parametrize("decode_type", ["greedy", "multistart_sampling"])
+def test_step_granular_loop_equals_fused(env_name, decode_type):
+    """The reference-shaped loop (decoder -> strategy.step -> env.step per step, each on its kernel)
+    and the single persistent kernel run the same device code: identical outputs."""
+    N, B = 20, 8
+    inst, pol, w, env, td, h = _setup(env_name, decode_type != "greedy", N, B, seed=2)
+    a = pol(td.clone(), env, decode_type=decode_type, noise_seed=9)
+    b = pol(td.clone(), env, decode_type=decode_type, noise_seed=9, fused=False)
+    T = min(a["actions"].shape[1], b["actions"].shape[1])
+    assert torch.equal(a["actions"][:, :T], b["actions"][:, :T])
+    assert rel_close(a["log_likelihood"], b["log_likelihood"], 1e-6)
+    assert rel_close(a["reward"], b["reward"], 1e-6)
+    compare_rollout(env_name, inst, h, w, decode_type == "greedy", b, decode_type, noise_seed=9)
+
+
+def test_supplied_noise_tensor_drives_sampling():
+    N, B = 20, 16
+    inst, pol, w, env, td, h = _setup("tsp", False, N, B, seed=3)
+    torch.manual_seed(0)
+    u = torch.rand(B, N, N).clamp_(1e-6, 1 - 1e-6)
+    g = -torch.log(-torch.log(u))
+    out = pol(td.clone(), env, decode_type="sampling", noise=g.to(DEV))
+    with torch.inference_mode():
+        ref = O.rollout("tsp", inst, h, w, "sampling", noise=g)
+    same = (out["actions"].cpu() == ref["actions"]).all(1).float().mean().item()
+    assert same >= 0.9
+    with torch.inference_mode():
+        ev = O.rollout("tsp", inst, h, w, actions=out["actions"].cpu())
+    assert rel_close(out["log_likelihood"], ev["log_likelihood"], LL_RTOL)
+
+
+def test_entropy_and_select_best_and_store_all_logp():
+    N, B = 20, 6
+    inst, pol, w, env, td, h = _setup("cvrp", True, N, B, seed=4)
+    out = pol(td.clone(), env, decode_type="multistart_greedy", return_entropy=True)
+    with torch.inference_mode():
+        ref = O.rollout("cvrp", inst, h, w, "multistart_greedy", use_graph_context=False, store_all_logp=True)
+    if torch.equal(out["actions"].cpu(), ref["actions"]):
+        assert torch.allclose(out["entropy"].cpu(), ref["entropy"], rtol=1e-4, atol=1e-4)
+    best = pol(td.clone(), env, decode_type="multistart_greedy", select_best=True)
+    assert best["reward"].shape == (B,)
+    allr = P.unbatchify(out["reward"], N).max(-1)[0]
+    assert torch.equal(best["reward"], allr)
+
+
+def test_sharding_is_invariant():
+    """Instance-sharded rollouts (as bench.py --gpus N does) equal the unsharded one: noise is keyed by
+    the GLOBAL instance index, rows never interact."""
+    N, B = 20, 12
+    inst, pol, w, env, td, h = _setup("tsp", True, N, B, seed=5)
+    full = pol(td.clone(), env, decode_type="multistart_sampling", noise_seed=1)
+    parts = []
+    for lo in (0, 6):
+        sub = {k: v[lo:lo + 6] for k, v in inst.items()}
+        env2, td2 = inst_to_env_td(P, "tsp", sub, DEV)
+        parts.append(pol(td2, env2, decode_type="multistart_sampling", noise_seed=1, instance_offset=lo))
+    fa = P.unbatchify(full["actions"], N)
+    pa = torch.cat([P.unbatchify(p["actions"], N) for p in parts], 0)
+    assert torch.equal(fa, pa)
+
+
+@pytest.mark.parametrize("path", golden_files(), ids=lambda p: p.split("/")[-1])
+def test_fused_rollout_vs_reference_fixtures(path):
+    """Against outputs of the UNMODIFIED reference (tests/golden)."""
+    g = load_golden(path)
+    z, env_name = g["z"], g["env"]
+    pol = (P.AttentionModelPolicy(env_name=env_name) if g["use_graph_context"] else P.POMOPolicy(env_name)).eval()
+    pol.decoder.load_state_dict(g["w"])
+    pol = pol.to(DEV)
+    env, td = inst_to_env_td(P, env_name, g["inst"], DEV)
+    h = g["h"].to(DEV)
+    pol.encoder = _FixedEncoder(h)           # fixtures carry the reference encoder's output
+    N = g["inst"]["locs"].shape[1]
+    for dt in DECODE_TYPES:
+        if f"{dt}.actions" not in z.files:
+            continue
+        ref_actions = torch.from_numpy(z[f"{dt}.actions"]).long()
+        out = pol(td.clone(), env, decode_type=dt, noise_seed=g["noise_seed"])
+        T = max(out["actions"].shape[1], ref_actions.shape[1])
+        pad = lambda a: torch.nn.functional.pad(a, (0, T - a.shape[1]))
+        same = (pad(out["actions"].cpu()) == pad(ref_actions)).all(1)
+        assert same.float().mean() >= 0.95, (dt, same.float().mean())
+        assert rel_close(out["reward"].cpu()[same], torch.from_numpy(z[f"{dt}.reward"])[same], LL_RTOL)
+        assert rel_close(out["log_likelihood"].cpu()[same],
+                         torch.from_numpy(z[f"{dt}.log_likelihood"])[same], LL_RTOL)
+        # teacher-forced on the reference's own actions: every row comparable
+        kw = dict(num_starts=N) if dt.startswith("multistart") else {}
+        ev = pol(td.clone(), env, actions=ref_actions.to(DEV), **kw)
+        assert rel_close(ev["log_likelihood"].cpu(), torch.from_numpy(z[f"{dt}.eval_log_likelihood"]), LL_RTOL)
+        assert rel_close(ev["reward"].cpu(), torch.from_numpy(z[f"{dt}.reward"]), LL_RTOL)
+
+
+def test_large_shape_properties_tsp100_pomo():
+    """BASELINE-size properties (size-independent): every tour is a permutation, the kernel's reward equals
+    the reward kernel on the emitted actions, log-likelihood equals the teacher-forced re-evaluation."""
+    N, B = 100, 64
+    inst, pol, w, env, td, h = _setup("tsp", True, N, B, seed=6)
+    out = pol(td.clone(), env, decode_type="multistart_greedy")
+    a = out["actions"]
+    assert a.shape == (B * N, N)
+    assert bool((a.sort(1)[0] == torch.arange(N, device=DEV)[None]).all())
+    assert torch.equal(a[:, 0], env.select_start_nodes(td, N))
+    r2 = env.get_reward(td, a)
+    assert rel_close(out["reward"], r2, 1e-6)
+    ev = pol(td.clone(), env, actions=a, num_starts=N)
+    assert rel_close(ev["log_likelihood"], out["log_likelihood"], 1e-6)
+    best = P.unbatchify(out["reward"], N).max(-1)[0]
+    assert bool((best <= 0).all()) and bool((best > -30).all())
