@@ -167,8 +167,15 @@ class AttentionModelPolicy(nn.Module):
             logp_all=logp_all.data_ptr() if store_all else None, reward=reward.data_ptr(),
             log_likelihood=ll.data_ptr(), lengths=lengths.data_ptr(), max_len=meta.data_ptr(),
             err=meta.data_ptr() + 4)
+        events = cfg.get("_events")           # bench.py: CUDA events around the kernel alone
+        if events is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
         rc = _lib.lib().rl4co_rollout(C.byref(cs), C.byref(args), _lib.stream_ptr())
         _lib.check(rc, "rl4co_rollout")
+        if events is not None:
+            e1.record()
+            events.append((e0, e1))
         self.last_lengths = lengths
         if env_id == _lib.ENV_CVRP or check:
             m = meta.tolist()                 # the ONE host sync of the rollout
