@@ -11,7 +11,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librl4co_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["capi.cu", "env_kernels.cu", "decode_kernels.cu", "rollout_kernel.cu"]
+SOURCES = ["capi.cu", "env_kernels.cu", "decode_kernels.cu", "rollout_kernel.cu", "rollout_tc.cu"]
 
 ENV_TSP, ENV_CVRP = 0, 1
 MODE_GREEDY, MODE_SAMPLING, MODE_EVALUATE = 0, 1, 2
@@ -22,12 +22,15 @@ ERR_MESSAGES = [  # (bit, reference assertion text)
     (8, "Invalid tour"),
     (16, "Used more than capacity"),
     (32, "Exceeded maximum number of steps during decoding"),
+    (64, "decoder cache value outside the fp16 range of the tensor-core path"),
 ]
+IMPL_AUTO, IMPL_FP32, IMPL_TC = 0, 1, 2
+ABI_VERSION = 2
 
 EXPORTS = [
     "rl4co_b200_abi_version", "rl4co_last_error", "rl4co_tsp_step", "rl4co_cvrp_step_mask",
     "rl4co_cvrp_action_mask", "rl4co_tour_reward", "rl4co_select", "rl4co_decode_step",
-    "rl4co_rollout", "rl4co_noise_gumbel",
+    "rl4co_rollout", "rl4co_noise_gumbel", "rl4co_tc_image_bytes", "rl4co_tc_pack", "rl4co_tc_decode_step",
 ]
 
 
@@ -50,7 +53,8 @@ def build(verbose: bool = False) -> str:
 
 class Cache(C.Structure):
     _fields_ = [("gk", C.c_void_p), ("gv", C.c_void_p), ("lk", C.c_void_p), ("pa", C.c_void_p),
-                ("pb", C.c_void_p), ("q0", C.c_void_p), ("wcap", C.c_void_p), ("B", C.c_int64),
+                ("pb", C.c_void_p), ("q0", C.c_void_p), ("wcap", C.c_void_p), ("tc_img", C.c_void_p),
+                ("B", C.c_int64),
                 ("n_nodes", C.c_int32), ("embed_dim", C.c_int32), ("num_heads", C.c_int32)]
 
 
@@ -62,7 +66,7 @@ class RolloutArgs(C.Structure):
                 ("actions_in", C.c_void_p), ("actions_in_stride", C.c_int64),
                 ("actions_in_T", C.c_int32), ("actions", C.c_void_p), ("logp", C.c_void_p),
                 ("logp_all", C.c_void_p), ("reward", C.c_void_p), ("log_likelihood", C.c_void_p),
-                ("lengths", C.c_void_p), ("max_len", C.c_void_p), ("err", C.c_void_p)]
+                ("lengths", C.c_void_p), ("max_len", C.c_void_p), ("err", C.c_void_p), ("impl", C.c_int32)]
 
 
 _lib = None
@@ -79,7 +83,8 @@ def lib():
         L.rl4co_last_error.restype = C.c_char_p
         for name in EXPORTS:
             getattr(L, name)  # fail loudly on a missing symbol
-        if L.rl4co_b200_abi_version() != 1:
+        L.rl4co_tc_image_bytes.restype = C.c_int64
+        if L.rl4co_b200_abi_version() != ABI_VERSION:
             raise RuntimeError("librl4co_b200.so ABI version mismatch")
         _lib = L
     return _lib

@@ -259,6 +259,8 @@ using namespace r4;
 
 namespace r4 {
 int check_cache(const rl4co_cache* c, int env, const char* who);
+bool tc_supported(const rl4co_cache* c, int S);
+int launch_rollout_tc(const rl4co_cache* cache, const rl4co_rollout_args& a, cudaStream_t st);
 }
 
 extern "C" int rl4co_rollout(const rl4co_cache* cache, const rl4co_rollout_args* args, void* stream) {
@@ -285,6 +287,11 @@ extern "C" int rl4co_rollout(const rl4co_cache* cache, const rl4co_rollout_args*
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     rl4co_rollout_args a = *args;
     a.num_starts = S;
+    R4_CHECK_ARG(a.impl >= RL4CO_IMPL_AUTO && a.impl <= RL4CO_IMPL_TC, "rollout: bad impl %d", a.impl);
+    if (a.impl == RL4CO_IMPL_TC)
+        R4_CHECK_ARG(tc_supported(cache, S), "rollout: tensor path needs tc_img, 8 <= S=%d <= 128, n_nodes=%d <= 112",
+                     S, cache->n_nodes);
+    if (a.impl != RL4CO_IMPL_FP32 && tc_supported(cache, S)) return launch_rollout_tc(cache, a, st);
     const size_t smem = 3ull * cache->n_nodes * kE * sizeof(float);
     const bool use_smem = S >= 8;
     if (use_smem) {

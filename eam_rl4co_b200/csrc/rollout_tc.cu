@@ -1,0 +1,847 @@
+// Tensor-core (tcgen05 + TMEM) path of the multistart rollout: one CTA = one instance, its S <= 128
+// start rows are the M dimension of every MMA.
+//
+// Per decode step and instance (am/decoder.py:161-198, attention.py:282-328, decoding.py:140-190):
+//   Q[s,:]      = pa[first_s] + pb[cur_s]                      (gather, CUDA cores -> smem A tile)
+//   S_h[s,n]    = Q_h[s,:] . (0.25 K_h[n,:])                   8 x (128 x NPAD x 16)   tcgen05, A,B smem
+//   P_h         = exp(S_h - max) on feasible nodes             TMEM -> regs -> TMEM (in place, fp16 hi/lo)
+//   O_h[s,:]    = P_h[s,:] . V_h[:, :]                         8 x (128 x 16 x NPAD)   tcgen05, A TMEM
+//   heads       = O / rowsum(P)                                TMEM -> regs -> TMEM (fp16 hi/lo)
+//   logits[s,n] = heads[s,:] . (L W_out)[n,:] / sqrt(E)        128 x NPAD x 128        tcgen05, A TMEM
+//   tanh clip, mask, log-softmax, argmax / Gumbel-max / given  TMEM -> regs, 4 threads per row
+//   env step (tsp/env.py:62-88, cvrp/env.py:68-144)            bit-packed mask words in registers/smem
+//
+// Precision: every fp32 operand x is split into fp16 hi + lo (x = hi + lo to 2^-22) and every
+// product is three MMAs (hi*hi + hi*lo + lo*hi) accumulated in fp32 in TMEM, which reproduces the
+// reference's fp32 logits to ~1e-6 (oracle/numerics_tc.py).
+//
+// Shared memory: the six static operand tiles of the instance (K, L, V^T; hi and lo), brought in
+// once per instance by TMA bulk copies from an image built by tc_pack_kernel, stay resident for
+// all T steps; the per-step Q tile (64 channels = 4 heads at a time) is rebuilt by the CUDA cores.
+#include "common.cuh"
+#include "tc_ptx.cuh"
+
+namespace r4 {
+namespace tc {
+
+constexpr int kThreads = 512;
+constexpr int kWarps = kThreads / 32;
+constexpr int kRows = 128;      // MMA M: start rows of one instance, padded
+constexpr int kMaxNPad = 112;   // nodes padded to a multiple of 16 (MMA N / K granularity)
+constexpr uint32_t kTmemCols = 512;
+constexpr uint32_t kColSP = 0;   // scores / probabilities of 4 heads: 4 x NPAD columns
+constexpr uint32_t kColO = 448;  // glimpse accumulators of 4 heads: 4 x 16 columns
+constexpr uint32_t kColHA = 0;   // heads as A operand: hi [0,64), lo [64,128)
+constexpr uint32_t kColLG = 128; // logits accumulators: NPAD columns
+// K-major, no-swizzle operand tiles (see tc_ptx.cuh::smem_desc)
+constexpr uint32_t kLBO = 128;                 // static tiles: the K-chunks of a row group are contiguous
+constexpr uint32_t kSBO_KL = 16 * kLBO;        // K / L tiles: 16 chunks (128 channels) per row group
+constexpr uint32_t kLBO_Q = 144;               // Q tile: chunk stride padded by 16 B (bank spread)
+constexpr uint32_t kSBO_Q = 8 * kLBO_Q;        // 8 chunks (64 channels) per row group
+constexpr uint32_t kQTileBytes = (kRows / 8) * kSBO_Q;
+
+__host__ __device__ inline int npad_of(int n) { return (n + 15) & ~15; }
+__host__ __device__ inline uint32_t tile_bytes(int npad) { return (uint32_t)npad * 256u; }
+
+// shared-memory carve-up
+struct Smem {
+    uint32_t maskw[4][kRows];   // feasible bits, word j = nodes [32j, 32j+32), SoA for conflict-free reads
+    int cur[kRows];
+    int first[kRows];
+    float rem[kRows];           // CVRP: vehicle_capacity - used_capacity
+    float red_a[4][kRows];      // epilogue exchanges between the 4 threads of a row
+    float red_b[4][kRows];
+    float red_c[4][kRows];
+    float red_lp[4][kRows];
+    int red_i[4][kRows];
+    int newvis[kRows];
+    float2 locs[kRows];
+    float demand[kRows];        // indexed by node (node 0 unused)
+    uint64_t tma_bar;
+    uint64_t mma_bar;
+    uint32_t tmem_ptr;
+    uint32_t pad_;
+};
+
+struct Ctx {
+    uint32_t k_hi, k_lo, l_hi, l_lo, v_hi, v_lo, q_hi, q_lo;  // shared-window addresses of the tiles
+    unsigned char* q_hi_p;
+    unsigned char* q_lo_p;
+    Smem* s;
+    uint32_t tmem;
+    int npad, nch;
+    uint32_t sbo_v;
+};
+
+__host__ inline size_t smem_bytes(int npad) { return 6ull * tile_bytes(npad) + 2ull * kQTileBytes + sizeof(Smem); }
+
+// ---- operand image: fp32 cache tables -> fp16 hi/lo tiles in UMMA layout ------------------------------
+// image of instance b = [K_hi][K_lo][L_hi][L_lo][Vt_hi][Vt_lo], each npad*256 bytes:
+//   K, L : rows = nodes, K-dim = channels; byte(r, ch) = (r/8)*2048 + (ch/8)*128 + (r%8)*16 + (ch%8)*2
+//   Vt   : rows = channels, K-dim = nodes; byte(ch, r) = (ch/8)*sbo_v + (r/8)*128 + (ch%8)*16 + (r%8)*2
+// K is pre-scaled by 1/sqrt(d) = 0.25 (exact), L by 1/sqrt(E) (attention.py:299-301, 308-322).
+__global__ void __launch_bounds__(256) tc_pack_kernel(rl4co_cache c, unsigned char* __restrict__ img, int npad,
+                                                      int32_t* err) {
+    const int64_t b = blockIdx.x;
+    const int n = c.n_nodes;
+    const uint32_t tb = tile_bytes(npad);
+    unsigned char* im = img + b * 6ull * tb;
+    const float* gk = c.gk + b * (int64_t)n * kE;
+    const float* gv = c.gv + b * (int64_t)n * kE;
+    const float* lk = c.lk + b * (int64_t)n * kE;
+    const uint32_t sbo_v = (uint32_t)(npad / 8) * 128u;
+    bool bad = false;
+    // K and L: one item = (row r, 8-channel chunk)
+    for (int it = threadIdx.x; it < npad * 16; it += blockDim.x) {
+        const int r = it >> 4, ch = (it & 15) * 8;
+        const uint32_t off = (uint32_t)(r >> 3) * kSBO_KL + (uint32_t)(it & 15) * kLBO + (uint32_t)(r & 7) * 16u;
+        uint4 khi = make_uint4(0, 0, 0, 0), klo = khi, lhi = khi, llo = khi;
+        if (r < n) {
+            const float4 k0 = ld4(gk + r * kE + ch), k1 = ld4(gk + r * kE + ch + 4);
+            const float4 l0 = ld4(lk + r * kE + ch), l1 = ld4(lk + r * kE + ch + 4);
+            const float kk[8] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
+            const float ll[8] = {l0.x, l0.y, l0.z, l0.w, l1.x, l1.y, l1.z, l1.w};
+            uint32_t kh[4], kl[4], lh[4], lw[4];
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+                const float a0 = 0.25f * kk[2 * p], a1 = 0.25f * kk[2 * p + 1];
+                const float b0 = ll[2 * p] / 11.313708498984761f, b1 = ll[2 * p + 1] / 11.313708498984761f;
+                bad |= !(fabsf(a0) <= 65504.f) || !(fabsf(a1) <= 65504.f) || !(fabsf(b0) <= 65504.f) ||
+                       !(fabsf(b1) <= 65504.f);
+                split2(a0, a1, kh[p], kl[p]);
+                split2(b0, b1, lh[p], lw[p]);
+            }
+            khi = make_uint4(kh[0], kh[1], kh[2], kh[3]);
+            klo = make_uint4(kl[0], kl[1], kl[2], kl[3]);
+            lhi = make_uint4(lh[0], lh[1], lh[2], lh[3]);
+            llo = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+        }
+        *reinterpret_cast<uint4*>(im + 0ull * tb + off) = khi;
+        *reinterpret_cast<uint4*>(im + 1ull * tb + off) = klo;
+        *reinterpret_cast<uint4*>(im + 2ull * tb + off) = lhi;
+        *reinterpret_cast<uint4*>(im + 3ull * tb + off) = llo;
+    }
+    // Vt: one item = (8-node chunk rc, channel ch); lanes run over channels (coalesced reads)
+    for (int it = threadIdx.x; it < (npad / 8) * kE; it += blockDim.x) {
+        const int rc = it >> 7, ch = it & 127;
+        float vv[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int r = rc * 8 + i;
+            vv[i] = (r < n) ? gv[r * kE + ch] : 0.f;
+            bad |= !(fabsf(vv[i]) <= 65504.f);
+        }
+        uint32_t vh[4], vl[4];
+#pragma unroll
+        for (int p = 0; p < 4; ++p) split2(vv[2 * p], vv[2 * p + 1], vh[p], vl[p]);
+        const uint32_t off = (uint32_t)(ch >> 3) * sbo_v + (uint32_t)rc * kLBO + (uint32_t)(ch & 7) * 16u;
+        *reinterpret_cast<uint4*>(im + 4ull * tb + off) = make_uint4(vh[0], vh[1], vh[2], vh[3]);
+        *reinterpret_cast<uint4*>(im + 5ull * tb + off) = make_uint4(vl[0], vl[1], vl[2], vl[3]);
+    }
+    if (bad) raise_err(err, RL4CO_ERR_FP16_RANGE, b);
+}
+
+// ---- per-step phases ------------------------------------------------------------------------------
+// Thread roles: warp w -> TMEM lane quadrant q = w % 4 (hardware rule for tcgen05.ld/st), j = w / 4;
+// the thread owns row 32q + lane and, within the row, head j of the current group, mask word j,
+// and the j-th quarter of the logit columns.
+
+// Q tile of head group g (channels [64g, 64g+64)) for rows [0,S): context.py:118-140 (TSP,
+// pa[first] + pb[cur]) / :70-74,155-157 (CVRP, pb[cur] + (cap - used) * wcap), split to fp16 hi/lo.
+template <int ENV>
+__device__ __forceinline__ void build_q(const Ctx& x, const rl4co_cache& c, int64_t b, int S, int g, int warp,
+                                        int lane) {
+    const int l16 = lane & 15, half = lane >> 4;
+    const int64_t base = b * (int64_t)c.n_nodes;
+    const int choff = 64 * g + 4 * l16;
+    for (int rp = warp; 2 * rp < S; rp += kWarps) {
+        const int r = 2 * rp + half;
+        if (r < S) {
+            const int cur = x.s->cur[r];
+            float4 q = ld4(c.pb + (base + cur) * kE + choff);
+            if (ENV == RL4CO_ENV_TSP) {
+                const float4 a = ld4(c.pa + (base + x.s->first[r]) * kE + choff);
+                q = make_float4(a.x + q.x, a.y + q.y, a.z + q.z, a.w + q.w);
+            } else {
+                const float rem = x.s->rem[r];
+                const float4 wc = ld4(c.wcap + choff);
+                q = make_float4(fmaf(rem, wc.x, q.x), fmaf(rem, wc.y, q.y), fmaf(rem, wc.z, q.z),
+                                fmaf(rem, wc.w, q.w));
+            }
+            uint32_t h0, l0, h1, l1;
+            split2(q.x, q.y, h0, l0);
+            split2(q.z, q.w, h1, l1);
+            const uint32_t off = (uint32_t)(r >> 3) * kSBO_Q + (uint32_t)(l16 >> 1) * kLBO_Q +
+                                 (uint32_t)(r & 7) * 16u + (uint32_t)(l16 & 1) * 8u;
+            *reinterpret_cast<uint2*>(x.q_hi_p + off) = make_uint2(h0, h1);
+            *reinterpret_cast<uint2*>(x.q_lo_p + off) = make_uint2(l0, l1);
+        }
+    }
+    fence_proxy_async();
+}
+
+__device__ __forceinline__ void wait_mma(const Ctx& x, uint32_t& par) {
+    mbar_wait(&x.s->mma_bar, par);
+    par ^= 1u;
+    tc_fence_after();
+}
+
+// scores of the 4 heads of group g: S_hg = Q_hg . K_h^T, three MMAs each (hi*hi + hi*lo + lo*hi)
+__device__ __forceinline__ void issue_scores(const Ctx& x, int g) {
+    tc_fence_after();
+    const uint32_t id = idesc_f16(kRows, x.npad);
+#pragma unroll
+    for (int hg = 0; hg < 4; ++hg) {
+        const int h = 4 * g + hg;
+        const uint64_t aq_hi = smem_desc(x.q_hi + 2u * hg * kLBO_Q, kLBO_Q, kSBO_Q);
+        const uint64_t aq_lo = smem_desc(x.q_lo + 2u * hg * kLBO_Q, kLBO_Q, kSBO_Q);
+        const uint64_t bk_hi = smem_desc(x.k_hi + 2u * h * kLBO, kLBO, kSBO_KL);
+        const uint64_t bk_lo = smem_desc(x.k_lo + 2u * h * kLBO, kLBO, kSBO_KL);
+        const uint32_t d = x.tmem + kColSP + (uint32_t)(hg * x.npad);
+        mma_ss(d, aq_hi, bk_hi, id, 0u);
+        mma_ss(d, aq_hi, bk_lo, id, 1u);
+        mma_ss(d, aq_lo, bk_hi, id, 1u);
+    }
+    tc_commit(&x.s->mma_bar);
+}
+
+// O_hg = P_hg . V_h : A = P from TMEM (hi/lo pairs per 16-node chunk), B = V^T tile rows [16h, 16h+16)
+__device__ __forceinline__ void issue_pv(const Ctx& x, int g) {
+    tc_fence_after();
+    const uint32_t id = idesc_f16(kRows, 16);
+#pragma unroll
+    for (int hg = 0; hg < 4; ++hg) {
+        const int h = 4 * g + hg;
+        const uint32_t d = x.tmem + kColO + 16u * hg;
+        const uint32_t a0 = x.tmem + kColSP + (uint32_t)(hg * x.npad);
+        const uint32_t vb = 2u * h * x.sbo_v;
+        for (int jk = 0; jk < x.nch; ++jk) {
+            const uint64_t bv_hi = smem_desc(x.v_hi + vb + 2u * jk * kLBO, kLBO, x.sbo_v);
+            const uint64_t bv_lo = smem_desc(x.v_lo + vb + 2u * jk * kLBO, kLBO, x.sbo_v);
+            const uint32_t a_hi = a0 + 16u * jk, a_lo = a_hi + 8u;
+            mma_ts(d, a_hi, bv_hi, id, jk > 0 ? 1u : 0u);
+            mma_ts(d, a_hi, bv_lo, id, 1u);
+            mma_ts(d, a_lo, bv_hi, id, 1u);
+        }
+    }
+    tc_commit(&x.s->mma_bar);
+}
+
+// logits = heads . (L W_out / sqrt(E))^T : A = heads from TMEM (k-step jk = head jk), B = L tile
+__device__ __forceinline__ void issue_logits(const Ctx& x) {
+    tc_fence_after();
+    const uint32_t id = idesc_f16(kRows, x.npad);
+    const uint32_t d = x.tmem + kColLG;
+#pragma unroll
+    for (int jk = 0; jk < 8; ++jk) {
+        const uint64_t bl_hi = smem_desc(x.l_hi + 2u * jk * kLBO, kLBO, kSBO_KL);
+        const uint64_t bl_lo = smem_desc(x.l_lo + 2u * jk * kLBO, kLBO, kSBO_KL);
+        const uint32_t a_hi = x.tmem + kColHA + 8u * jk, a_lo = a_hi + 64u;
+        mma_ts(d, a_hi, bl_hi, id, jk > 0 ? 1u : 0u);
+        mma_ts(d, a_hi, bl_lo, id, 1u);
+        mma_ts(d, a_lo, bl_hi, id, 1u);
+    }
+    tc_commit(&x.s->mma_bar);
+}
+
+// Masked softmax numerator of one (row, head): S (fp32, NPAD columns of TMEM) -> P = exp(S - max) on
+// feasible nodes, 0 elsewhere (attention.py:308-322: masked scores are -inf -> exactly 0), written
+// back in place as fp16 hi/lo: chunk c (16 nodes) -> hi in columns [16c,16c+8), lo in [16c+8,16c+16).
+// Returns 1 / rowsum (0 for a row without feasible nodes: padding rows).
+__device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int row, float* dbg_scores, int n) {
+    const uint32_t w0 = x.s->maskw[0][row], w1 = x.s->maskw[1][row], w2 = x.s->maskw[2][row],
+                   w3 = x.s->maskw[3][row];
+    float m = -INFINITY;
+    uint32_t a0 = w0, a1 = w1, a2 = w2, a3 = w3;
+    for (int ch = 0; ch < x.nch; ++ch) {
+        uint32_t v[16];
+        tmem_ld16(sp + 16u * ch, v);
+        tc_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            if (dbg_scores != nullptr && 16 * ch + i < n) dbg_scores[16 * ch + i] = __uint_as_float(v[i]);
+            if (a0 & (1u << i)) m = fmaxf(m, __uint_as_float(v[i]));
+        }
+        a0 = __funnelshift_r(a0, a1, 16);
+        a1 = __funnelshift_r(a1, a2, 16);
+        a2 = __funnelshift_r(a2, a3, 16);
+        a3 >>= 16;
+    }
+    if (m == -INFINITY) m = 0.f;
+    const float kLog2e = 1.4426950408889634f;
+    const float ml = m * kLog2e;
+    float l = 0.f;
+    a0 = w0; a1 = w1; a2 = w2; a3 = w3;
+    for (int ch = 0; ch < x.nch; ++ch) {
+        uint32_t v[16];
+        tmem_ld16(sp + 16u * ch, v);
+        tc_wait_ld();
+        uint32_t hi[8], lo[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            float p0 = ex2_approx(fmaf(__uint_as_float(v[2 * i]), kLog2e, -ml));
+            float p1 = ex2_approx(fmaf(__uint_as_float(v[2 * i + 1]), kLog2e, -ml));
+            p0 = (a0 & (1u << (2 * i))) ? p0 : 0.f;
+            p1 = (a0 & (1u << (2 * i + 1))) ? p1 : 0.f;
+            l += p0;
+            l += p1;
+            split2(p0, p1, hi[i], lo[i]);
+        }
+        tmem_st8(sp + 16u * ch, hi);
+        tmem_st8(sp + 16u * ch + 8u, lo);
+        a0 = __funnelshift_r(a0, a1, 16);
+        a1 = __funnelshift_r(a1, a2, 16);
+        a2 = __funnelshift_r(a2, a3, 16);
+        a3 >>= 16;
+    }
+    tc_wait_st();
+    return l > 0.f ? 1.0f / l : 0.f;
+}
+
+// All GEMM phases of one decoder step; on return the raw logits of the instance sit in TMEM
+// columns [kColLG, kColLG + n) (row = lane).  dbg_* (nullable) receive scores [S?,8,n] / heads [.,128]
+// of this thread's row for the parity tests.
+template <int ENV>
+__device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cache& c, int64_t b, int S,
+                                                  uint32_t& mma_par, float* dbg_scores_row, float* dbg_heads_row) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = warp & 3, j = warp >> 2, row = 32 * q + lane;
+    const uint32_t lane_base = x.tmem + ((uint32_t)(32 * q) << 16);
+    const int n = c.n_nodes;
+    float hv[2][16];
+#pragma unroll
+    for (int g = 0; g < 2; ++g) {
+        build_q<ENV>(x, c, b, S, g, warp, lane);
+        __syncthreads();
+        if (threadIdx.x == 0) issue_scores(x, g);
+        wait_mma(x, mma_par);
+        const float inv_l = softmax_inplace(x, lane_base + kColSP + (uint32_t)(j * x.npad), row,
+                                            dbg_scores_row ? dbg_scores_row + (4 * g + j) * n : nullptr, n);
+        tc_fence_before();
+        __syncthreads();
+        if (threadIdx.x == 0) issue_pv(x, g);
+        wait_mma(x, mma_par);
+        uint32_t o[16];
+        tmem_ld16(lane_base + kColO + 16u * j, o);
+        tc_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) hv[g][i] = __uint_as_float(o[i]) * inv_l;
+        tc_fence_before();
+    }
+    // heads -> A operand in TMEM (fp16 hi/lo), k-step = head
+#pragma unroll
+    for (int g = 0; g < 2; ++g) {
+        const int h = 4 * g + j;
+        uint32_t hi[8], lo[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) split2(hv[g][2 * i], hv[g][2 * i + 1], hi[i], lo[i]);
+        tmem_st8(lane_base + kColHA + 8u * h, hi);
+        tmem_st8(lane_base + kColHA + 64u + 8u * h, lo);
+        if (dbg_heads_row != nullptr) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) dbg_heads_row[16 * h + i] = hv[g][i];
+        }
+    }
+    tc_wait_st();
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x == 0) issue_logits(x);
+    wait_mma(x, mma_par);
+}
+
+// ---- selection: process_logits + Greedy / Sampling / Evaluate (decoding.py:140-190, 346-465) --------
+// Four threads per row, thread j takes the j-th quarter of the logit columns (units of 4 columns);
+// max / sum / argmax are combined through shared memory with a 128-thread named barrier per quadrant.
+struct RowSel {
+    int action;
+    float logp;
+};
+
+__device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_args& a, int n, int q, int j,
+                                             int row, bool valid, int64_t grow, int t, int T, uint32_t nkey,
+                                             int given, int& err_bits) {
+    Smem* s = x.s;
+    const uint32_t lg = x.tmem + ((uint32_t)(32 * q) << 16) + kColLG;
+    const int U = (n + 3) >> 2;
+    const int u0 = (U * j) >> 2, u1 = (U * (j + 1)) >> 2;
+    uint32_t raw[28];
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+        uint32_t v4[4] = {0u, 0u, 0u, 0u};
+        if (u0 + k < u1) tmem_ld4(lg + 4u * (u0 + k), v4);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) raw[4 * k + i] = v4[i];
+    }
+    tc_wait_ld();
+    const uint32_t w0 = s->maskw[0][row], w1 = s->maskw[1][row], w2 = s->maskw[2][row], w3 = s->maskw[3][row];
+    const int sh = 4 * u0, wi = sh >> 5;
+    const uint32_t lo = wi == 0 ? w0 : (wi == 1 ? w1 : (wi == 2 ? w2 : w3));
+    const uint32_t hi = wi == 0 ? w1 : (wi == 1 ? w2 : (wi == 2 ? w3 : 0u));
+    const int cnt = 4 * (u1 - u0);
+    const uint32_t inrange = cnt >= 32 ? 0xffffffffu : ((1u << cnt) - 1u);
+    const uint32_t win = __funnelshift_r(lo, hi, sh & 31) & inrange;  // feasible bits of nodes sh .. sh+27
+
+    float xv[28];
+    float lmax = -INFINITY;
+    bool nan_local = false;
+#pragma unroll
+    for (int e = 0; e < 28; ++e) {
+        const bool feas = (win >> e) & 1u;
+        const float v = __uint_as_float(raw[e]);
+        if (feas && v != v) nan_local = true;                       // attention.py:303-304
+        float xx = a.tanh_clipping > 0.f ? tanhf(v) * a.tanh_clipping : v;   // decoding.py:171-172
+        xx = feas ? xx : -INFINITY;                                 // :177
+        if (a.temperature != 1.0f) xx = xx / a.temperature;         // :179
+        xv[e] = xx;
+        lmax = fmaxf(lmax, xx);
+    }
+    if (nan_local && valid) err_bits |= RL4CO_ERR_NAN_LOGITS;
+    s->red_a[j][row] = lmax;
+    bar_sync(1 + q, 128);
+    const float mx = fmaxf(fmaxf(s->red_a[0][row], s->red_a[1][row]), fmaxf(s->red_a[2][row], s->red_a[3][row]));
+    float lsum = 0.f;
+#pragma unroll
+    for (int e = 0; e < 28; ++e) lsum += expf(xv[e] - mx);           // exp(-inf) = 0
+    s->red_b[j][row] = lsum;
+    bar_sync(1 + q, 128);
+    const float logsum = logf(((s->red_b[0][row] + s->red_b[1][row]) + s->red_b[2][row]) + s->red_b[3][row]);
+    float best = -INFINITY, best_lp = -INFINITY;
+    int best_i = 0x7fffffff;
+#pragma unroll
+    for (int e = 0; e < 28; ++e) {
+        const int node = sh + e;
+        const float lp = (xv[e] - mx) - logsum;                     // log_softmax :190
+        if (a.logp_all != nullptr && valid && e < cnt && node < n) a.logp_all[(grow * T + t) * (int64_t)n + node] = lp;
+        float cand = lp;
+        if (a.mode == RL4CO_MODE_SAMPLING) {
+            if ((win >> e) & 1u)
+                cand = lp + (a.gumbel ? a.gumbel[(grow * T + t) * (int64_t)n + node] : noise_gumbel(nkey, node));
+        } else if (a.mode == RL4CO_MODE_EVALUATE) {
+            cand = (e < cnt && node == given) ? 0.f : -INFINITY;
+        }
+        if (cand > best) {  // ascending node order + strict > = first max index (torch.argmax)
+            best = cand;
+            best_i = node;
+            best_lp = lp;
+        }
+    }
+    s->red_c[j][row] = best;
+    s->red_i[j][row] = best_i;
+    s->red_lp[j][row] = best_lp;
+    bar_sync(1 + q, 128);
+    float fb = s->red_c[0][row];
+    int fi = s->red_i[0][row];
+    float flp = s->red_lp[0][row];
+#pragma unroll
+    for (int jj = 1; jj < 4; ++jj) {
+        const float cb = s->red_c[jj][row];
+        if (cb > fb) {
+            fb = cb;
+            fi = s->red_i[jj][row];
+            flp = s->red_lp[jj][row];
+        }
+    }
+    RowSel sel;
+    sel.action = (fi == 0x7fffffff) ? 0 : fi;
+    sel.logp = flp;
+    if (valid && j == 0) {
+        const uint32_t ww = (sel.action >> 5) == 0 ? w0 : ((sel.action >> 5) == 1 ? w1 : ((sel.action >> 5) == 2 ? w2 : w3));
+        if (a.mode != RL4CO_MODE_EVALUATE && !((ww >> (sel.action & 31)) & 1u)) err_bits |= RL4CO_ERR_INFEASIBLE;
+        if (!(sel.logp > -1000.f)) err_bits |= RL4CO_ERR_NEG_INF_LOGP;   // decoding.py:56-58
+    }
+    return sel;
+}
+
+// ---- env step (tsp/env.py:62-88, cvrp/env.py:68-100,132-144), 4 threads per row ------------------------
+struct RowState {
+    uint32_t word;   // TSP: feasible bits of word j; CVRP: visited bits of word j
+    float used, cap; // CVRP (tracked redundantly by the 4 threads of the row)
+    // thread j == 0 only
+    float ll, len;
+    int prev, first_action, nvis, length;
+    bool done;
+};
+
+template <int ENV>
+__device__ __forceinline__ void apply_action(const Ctx& x, const rl4co_rollout_args& a, RowState& st, int n, int q,
+                                             int j, int row, bool valid, int64_t grow, int t, int T, int act,
+                                             float lpa) {
+    Smem* s = x.s;
+    if (j == 0 && valid) {
+        a.actions[grow * T + t] = act;
+        a.logp[grow * T + t] = lpa;
+        st.ll += lpa;
+        // tour length so far (ops.py:82-95): edge prev -> act; CVRP starts at the depot
+        const int from = (st.prev < 0) ? ((ENV == RL4CO_ENV_CVRP) ? 0 : act) : st.prev;
+        const float2 p0 = s->locs[from], p1 = s->locs[act];
+        const float dx = p1.x - p0.x, dy = p1.y - p0.y;
+        st.len += sqrtf(dx * dx + dy * dy);
+        if (st.prev < 0) st.first_action = act;
+        st.prev = act;
+        s->cur[row] = act;
+    }
+    if (ENV == RL4CO_ENV_TSP) {
+        if (valid && (act >> 5) == j) st.word &= ~(1u << (act & 31));
+        s->maskw[j][row] = st.word;
+        if (j == 0 && valid) {
+            if (t == 0) s->first[row] = act;
+            if (!st.done && t + 1 >= n) {
+                st.done = true;
+                st.length = t + 1;
+            }
+        }
+    } else {
+        bool newly = false;
+        if (valid && (act >> 5) == j) {
+            newly = !((st.word >> (act & 31)) & 1u);
+            st.word |= 1u << (act & 31);
+        }
+        int di = act - 1;
+        di = di < 0 ? 0 : (di > n - 2 ? n - 2 : di);
+        st.used = (st.used + s->demand[di + 1]) * ((act != 0) ? 1.0f : 0.0f);   // cvrp/env.py:73-80
+        const float lim = st.cap + 1e-5f;                                       // :135
+        uint32_t feas = 0u;
+#pragma unroll 8
+        for (int i = 0; i < 32; ++i) {
+            const int node = 32 * j + i;
+            const bool ok = valid && node >= 1 && node < n && !((st.word >> i) & 1u) &&
+                            !((s->demand[node < kRows ? node : 0] + st.used) > lim);
+            feas |= (ok ? 1u : 0u) << i;
+        }
+        s->maskw[j][row] = feas;
+        if (newly) s->newvis[row] = 1;
+        bar_sync(1 + q, 128);
+        if (j == 0 && valid) {
+            const bool any_free = (s->maskw[0][row] | s->maskw[1][row] | s->maskw[2][row] | s->maskw[3][row]) != 0u;
+            if (!((act == 0) && any_free)) s->maskw[0][row] = feas | 1u;         // :141-144
+            st.nvis += s->newvis[row];
+            s->newvis[row] = 0;
+            s->rem[row] = st.cap - st.used;
+            if (!st.done && st.nvis == n) {                                      // :87
+                st.done = true;
+                st.length = t + 1;
+            }
+        }
+    }
+}
+
+// ---- context set-up shared by the kernels --------------------------------------------------------------
+__device__ __forceinline__ Ctx make_ctx(unsigned char* smem, int npad) {
+    Ctx x;
+    const uint32_t tb = tile_bytes(npad);
+    const uint32_t base = smem_u32(smem);
+    x.k_hi = base;
+    x.k_lo = base + tb;
+    x.l_hi = base + 2u * tb;
+    x.l_lo = base + 3u * tb;
+    x.v_hi = base + 4u * tb;
+    x.v_lo = base + 5u * tb;
+    x.q_hi = base + 6u * tb;
+    x.q_lo = x.q_hi + kQTileBytes;
+    x.q_hi_p = smem + 6ull * tb;
+    x.q_lo_p = x.q_hi_p + kQTileBytes;
+    x.s = reinterpret_cast<Smem*>(x.q_lo_p + kQTileBytes);
+    x.npad = npad;
+    x.nch = npad / 16;
+    x.sbo_v = (uint32_t)(npad / 8) * 128u;
+    x.tmem = 0;
+    return x;
+}
+
+// barriers, TMEM, zeroed Q tiles (rows >= S are never written afterwards and must stay finite)
+__device__ __forceinline__ void cta_setup(Ctx& x) {
+    const int warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) {
+        mbar_init(&x.s->tma_bar, 1);
+        mbar_init(&x.s->mma_bar, 1);
+        fence_mbar_init();
+    }
+    if (warp == 0) tmem_alloc(&x.s->tmem_ptr, kTmemCols);
+    for (uint32_t i = threadIdx.x; i < 2u * kQTileBytes / 16u; i += kThreads)
+        reinterpret_cast<uint4*>(x.q_hi_p)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = threadIdx.x; i < kRows; i += kThreads) {
+        x.s->newvis[i] = 0;
+        x.s->cur[i] = 0;
+        x.s->first[i] = 0;
+        x.s->rem[i] = 0.f;
+        x.s->demand[i] = 0.f;
+        x.s->locs[i] = make_float2(0.f, 0.f);
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    x.tmem = x.s->tmem_ptr;
+}
+
+// the instance's six operand tiles: one TMA bulk copy each, one mbarrier phase
+__device__ __forceinline__ void load_tiles(const Ctx& x, unsigned char* smem, const unsigned char* img, int64_t b) {
+    const uint32_t tb = tile_bytes(x.npad);
+    fence_proxy_async();
+    mbar_expect_tx(&x.s->tma_bar, 6u * tb);
+    const unsigned char* src = img + b * 6ull * tb;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) bulk_g2s(smem + (size_t)i * tb, src + (size_t)i * tb, tb, &x.s->tma_bar);
+}
+
+// ---- persistent fused rollout (constructive/base.py:221-263), tensor path ------------------------------
+template <int ENV>
+__global__ void __launch_bounds__(kThreads, 1)
+    rollout_tc_kernel(rl4co_cache c, rl4co_rollout_args a, const unsigned char* __restrict__ img, int npad) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    Ctx x = make_ctx(smem, npad);
+    cta_setup(x);
+    Smem* s = x.s;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = warp & 3, j = warp >> 2, row = 32 * q + lane;
+    const int n = c.n_nodes, S = a.num_starts, T = a.max_steps;
+    const bool valid = row < S;
+    uint32_t tma_par = 0, mma_par = 0;
+
+    for (int64_t b = blockIdx.x; b < c.B; b += gridDim.x) {
+        if (threadIdx.x == 0) load_tiles(x, smem, img, b);
+        for (int i = threadIdx.x; i < n; i += kThreads) {
+            s->locs[i] = reinterpret_cast<const float2*>(a.locs)[b * (int64_t)n + i];
+            if (ENV == RL4CO_ENV_CVRP && i >= 1) s->demand[i] = a.demand[b * (int64_t)(n - 1) + i - 1];
+        }
+        const int64_t grow = (int64_t)row * c.B + b;  // start-major (ops.py:13-16)
+        RowState st;
+        st.used = 0.f;
+        st.cap = (ENV == RL4CO_ENV_CVRP) ? a.vehicle_capacity[b] : 1.f;
+        st.ll = 0.f;
+        st.len = 0.f;
+        st.prev = -1;
+        st.first_action = 0;
+        st.nvis = 0;
+        st.length = 0;
+        st.done = false;
+        if (ENV == RL4CO_ENV_TSP) {  // tsp/env.py:90-115: every node feasible
+            const int rem = n - 32 * j;
+            st.word = !valid ? 0u : (rem >= 32 ? 0xffffffffu : (rem <= 0 ? 0u : ((1u << rem) - 1u)));
+        } else {
+            st.word = 0u;            // cvrp/env.py:102-130: nothing visited
+        }
+        int err_bits = 0;
+        // forced first action (decoding.py:305-327; select_start_nodes ops.py:147-161)
+        int act = 0;
+        if (valid) {
+            if (a.mode == RL4CO_MODE_EVALUATE)
+                act = (int)a.actions_in[grow * a.actions_in_stride];
+            else
+                act = (ENV == RL4CO_ENV_TSP) ? (row % n) : (row % (n - 1)) + 1;
+            if (act < 0 || act >= n) {
+                err_bits |= RL4CO_ERR_INFEASIBLE;
+                act = 0;
+            }
+        }
+        mbar_wait(&s->tma_bar, tma_par);
+        tma_par ^= 1u;
+        __syncthreads();
+        apply_action<ENV>(x, a, st, n, q, j, row, valid, grow, 0, T, act, 0.f);
+        int all_done = __syncthreads_and(!valid || j != 0 || st.done);
+
+        for (int t = 1; !all_done; ++t) {
+            if (t >= T) {
+                if (valid && j == 0 && !st.done) err_bits |= RL4CO_ERR_MAX_STEPS;
+                break;
+            }
+            decode_step_gemms<ENV>(x, c, b, S, mma_par, nullptr, nullptr);
+            int given = 0;
+            if (a.mode == RL4CO_MODE_EVALUATE && valid) {
+                given = (t < a.actions_in_T) ? (int)a.actions_in[grow * a.actions_in_stride + t] : 0;
+                if (given < 0 || given >= n) {
+                    if (j == 0) err_bits |= RL4CO_ERR_INFEASIBLE;
+                    given = 0;
+                }
+            }
+            const uint32_t nkey = (a.mode == RL4CO_MODE_SAMPLING) ? noise_key(a.seed, a.inst_offset + b, row, t) : 0u;
+            const RowSel sel = select_row(x, a, n, q, j, row, valid, grow, t, T, nkey, given, err_bits);
+            apply_action<ENV>(x, a, st, n, q, j, row, valid, grow, t, T, sel.action, sel.logp);
+            tc_fence_before();
+            all_done = __syncthreads_and(!valid || j != 0 || st.done);
+        }
+        if (valid && j == 0) {
+            // closing edge (roll(-1) wraps to the first element: TSP first action, CVRP depot)
+            const int to = (ENV == RL4CO_ENV_CVRP) ? 0 : st.first_action;
+            const float2 p0 = s->locs[st.prev], p1 = s->locs[to];
+            const float dx = p1.x - p0.x, dy = p1.y - p0.y;
+            st.len += sqrtf(dx * dx + dy * dy);
+            a.reward[grow] = -st.len;
+            a.log_likelihood[grow] = st.ll;
+            const int len = st.done ? st.length : T;
+            a.lengths[grow] = len;
+            atomicMax(a.max_len, len);
+        }
+        if (valid && err_bits) raise_err(a.err, err_bits, grow);
+        __syncthreads();  // locs / state of this instance are dead before the next one overwrites them
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(x.tmem, kTmemCols);
+}
+
+// ---- one decoder step for all rows (am/decoder.py:161-198): RAW logits for every node --------------------
+template <int ENV>
+__global__ void __launch_bounds__(kThreads, 1)
+    decode_step_tc_kernel(rl4co_cache c, const unsigned char* __restrict__ img, int npad, int S,
+                          const int64_t* __restrict__ first_node, const int64_t* __restrict__ current_node,
+                          const float* __restrict__ used, const float* __restrict__ cap,
+                          const uint8_t* __restrict__ mask, float* __restrict__ logits_out,
+                          float* __restrict__ dbg_scores, float* __restrict__ dbg_heads, int32_t* err) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    Ctx x = make_ctx(smem, npad);
+    cta_setup(x);
+    Smem* s = x.s;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = warp & 3, j = warp >> 2, row = 32 * q + lane;
+    const int n = c.n_nodes;
+    const bool valid = row < S;
+    uint32_t tma_par = 0, mma_par = 0;
+    for (int64_t b = blockIdx.x; b < c.B; b += gridDim.x) {
+        if (threadIdx.x == 0) load_tiles(x, smem, img, b);
+        const int64_t grow = (int64_t)row * c.B + b;
+        uint32_t word = 0u;
+        if (valid) {
+            for (int i = 0; i < 32; ++i) {
+                const int node = 32 * j + i;
+                if (node < n && mask[grow * n + node] != 0) word |= 1u << i;
+            }
+            if (j == 0) {
+                s->cur[row] = (int)current_node[grow];
+                s->first[row] = (ENV == RL4CO_ENV_TSP) ? (int)first_node[grow] : 0;
+                s->rem[row] = (ENV == RL4CO_ENV_CVRP) ? cap[grow] - used[grow] : 0.f;
+            }
+        }
+        s->maskw[j][row] = word;
+        mbar_wait(&s->tma_bar, tma_par);
+        tma_par ^= 1u;
+        __syncthreads();
+        decode_step_gemms<ENV>(x, c, b, S, mma_par,
+                               (dbg_scores != nullptr && valid) ? dbg_scores + grow * (int64_t)(8 * n) : nullptr,
+                               (dbg_heads != nullptr && valid) ? dbg_heads + grow * (int64_t)kE : nullptr);
+        // this thread's quarter of the logit columns
+        const uint32_t lg = x.tmem + ((uint32_t)(32 * q) << 16) + kColLG;
+        const int U = (n + 3) >> 2;
+        const int u0 = (U * j) >> 2, u1 = (U * (j + 1)) >> 2;
+        bool nan_local = false;
+        for (int u = u0; u < u1; ++u) {
+            uint32_t v4[4];
+            tmem_ld4(lg + 4u * u, v4);
+            tc_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int node = 4 * u + i;
+                if (valid && node < n) {
+                    const float v = __uint_as_float(v4[i]);
+                    logits_out[grow * n + node] = v;
+                    nan_local |= (v != v);
+                }
+            }
+        }
+        if (nan_local) raise_err(err, RL4CO_ERR_NAN_LOGITS, grow);  // attention.py:303-304
+        tc_fence_before();
+        __syncthreads();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(x.tmem, kTmemCols);
+}
+
+}  // namespace tc
+
+// ---- host-side launchers ---------------------------------------------------------------------------------
+int check_cache(const rl4co_cache* c, int env, const char* who);
+
+bool tc_supported(const rl4co_cache* c, int S) {
+    return c->tc_img != nullptr && S >= 8 && S <= tc::kRows && tc::npad_of(c->n_nodes) <= tc::kMaxNPad;
+}
+
+template <typename K>
+static int tc_prepare(K kern, int npad, const char* who) {
+    const size_t smem = tc::smem_bytes(npad);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) {
+        set_error("%s: cudaFuncSetAttribute(%zu B smem): %s", who, smem, cudaGetErrorString(e));
+        return RL4CO_E_LAUNCH;
+    }
+    return RL4CO_OK;
+}
+
+static unsigned tc_grid(int64_t B) {
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return (unsigned)(B < sms ? B : sms);
+}
+
+int launch_rollout_tc(const rl4co_cache* cache, const rl4co_rollout_args& a, cudaStream_t st) {
+    const int npad = tc::npad_of(cache->n_nodes);
+    const size_t smem = tc::smem_bytes(npad);
+    const unsigned char* img = reinterpret_cast<const unsigned char*>(cache->tc_img);
+    int rc;
+    if (a.env == RL4CO_ENV_TSP) {
+        if ((rc = tc_prepare(tc::rollout_tc_kernel<RL4CO_ENV_TSP>, npad, "rollout_tc"))) return rc;
+        tc::rollout_tc_kernel<RL4CO_ENV_TSP><<<tc_grid(cache->B), tc::kThreads, smem, st>>>(*cache, a, img, npad);
+    } else {
+        if ((rc = tc_prepare(tc::rollout_tc_kernel<RL4CO_ENV_CVRP>, npad, "rollout_tc"))) return rc;
+        tc::rollout_tc_kernel<RL4CO_ENV_CVRP><<<tc_grid(cache->B), tc::kThreads, smem, st>>>(*cache, a, img, npad);
+    }
+    R4_CHECK_LAUNCH("rollout_tc");
+    return RL4CO_OK;
+}
+
+}  // namespace r4
+
+using namespace r4;
+
+extern "C" int64_t rl4co_tc_image_bytes(int32_t n_nodes) {
+    if (n_nodes < 2 || tc::npad_of(n_nodes) > tc::kMaxNPad) return 0;
+    return 6ll * tc::tile_bytes(tc::npad_of(n_nodes));
+}
+
+extern "C" int rl4co_tc_pack(const rl4co_cache* cache, void* image, int32_t* err, void* stream) {
+    R4_CHECK_ARG(cache && cache->gk && cache->gv && cache->lk && cache->B > 0 && image && err, "tc_pack: null pointer");
+    R4_CHECK_ARG(cache->embed_dim == kE && cache->num_heads == kH, "tc_pack: only embed_dim=128, num_heads=8");
+    R4_CHECK_ARG(rl4co_tc_image_bytes(cache->n_nodes) > 0, "tc_pack: n_nodes=%d outside the tensor path (<= %d)",
+                 cache->n_nodes, tc::kMaxNPad);
+    tc::tc_pack_kernel<<<(unsigned)cache->B, 256, 0, (cudaStream_t)stream>>>(
+        *cache, reinterpret_cast<unsigned char*>(image), tc::npad_of(cache->n_nodes), err);
+    R4_CHECK_LAUNCH("tc_pack");
+    return RL4CO_OK;
+}
+
+extern "C" int rl4co_tc_decode_step(int32_t env, const rl4co_cache* cache, const int64_t* first_node,
+                                    const int64_t* current_node, const float* used_capacity,
+                                    const float* vehicle_capacity, const uint8_t* mask, float* logits_out,
+                                    float* dbg_scores, float* dbg_heads, int32_t* err, int64_t rows,
+                                    void* stream) {
+    R4_CHECK_ARG(env == RL4CO_ENV_TSP || env == RL4CO_ENV_CVRP, "tc_decode_step: bad env %d", env);
+    int rc = check_cache(cache, env, "tc_decode_step");
+    if (rc) return rc;
+    if (rows == 0) return RL4CO_OK;
+    R4_CHECK_ARG(rows > 0 && rows % cache->B == 0, "tc_decode_step: rows=%lld not a multiple of B=%lld",
+                 (long long)rows, (long long)cache->B);
+    const int S = (int)(rows / cache->B);
+    R4_CHECK_ARG(tc_supported(cache, S), "tc_decode_step: needs tc_img, 8 <= S=%d <= 128, n_nodes=%d <= %d", S,
+                 cache->n_nodes, tc::kMaxNPad);
+    R4_CHECK_ARG(current_node && mask && logits_out && err, "tc_decode_step: null pointer");
+    if (env == RL4CO_ENV_TSP) R4_CHECK_ARG(first_node, "tc_decode_step: TSP needs first_node");
+    if (env == RL4CO_ENV_CVRP) R4_CHECK_ARG(used_capacity && vehicle_capacity, "tc_decode_step: CVRP needs capacities");
+    const int npad = tc::npad_of(cache->n_nodes);
+    const size_t smem = tc::smem_bytes(npad);
+    const unsigned char* img = reinterpret_cast<const unsigned char*>(cache->tc_img);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (env == RL4CO_ENV_TSP) {
+        if ((rc = tc_prepare(tc::decode_step_tc_kernel<RL4CO_ENV_TSP>, npad, "tc_decode_step"))) return rc;
+        tc::decode_step_tc_kernel<RL4CO_ENV_TSP><<<tc_grid(cache->B), tc::kThreads, smem, st>>>(
+            *cache, img, npad, S, first_node, current_node, used_capacity, vehicle_capacity, mask, logits_out,
+            dbg_scores, dbg_heads, err);
+    } else {
+        if ((rc = tc_prepare(tc::decode_step_tc_kernel<RL4CO_ENV_CVRP>, npad, "tc_decode_step"))) return rc;
+        tc::decode_step_tc_kernel<RL4CO_ENV_CVRP><<<tc_grid(cache->B), tc::kThreads, smem, st>>>(
+            *cache, img, npad, S, first_node, current_node, used_capacity, vehicle_capacity, mask, logits_out,
+            dbg_scores, dbg_heads, err);
+    }
+    R4_CHECK_LAUNCH("tc_decode_step");
+    return RL4CO_OK;
+}

@@ -57,6 +57,8 @@ class PrecomputedCache:
     wcap: Optional[torch.Tensor]
     env_id: int
     _logit_key_w: Optional[torch.Tensor] = None
+    tc_img: Optional[torch.Tensor] = None   # [B, rl4co_tc_image_bytes(n)] uint8: tcgen05 operand tiles
+    tc_err: Optional[torch.Tensor] = None
 
     @property
     def logit_key(self):
@@ -66,7 +68,7 @@ class PrecomputedCache:
         B, n, E = self.node_embeddings.shape
         p = lambda t: (t.data_ptr() if t is not None else None)
         return _lib.Cache(p(self.glimpse_key), p(self.glimpse_val), p(self.logit_key_folded), p(self.pa),
-                          p(self.pb), p(self.q0), p(self.wcap), B, n, E, 8)
+                          p(self.pb), p(self.q0), p(self.wcap), p(self.tc_img), B, n, E, 8)
 
 
 class AttentionModelDecoder(nn.Module):
@@ -117,12 +119,32 @@ class AttentionModelDecoder(nn.Module):
         else:
             pa, pb, q0 = None, (tabs[3] + gcb).contiguous(), None
             wcap = Wc[:, E].contiguous()
-        return PrecomputedCache(h, gc, gk, gv, lkf, pa, pb, q0, wcap,
-                                _lib.ENV_TSP if tsp else _lib.ENV_CVRP, Wl)
+        cache = PrecomputedCache(h, gc, gk, gv, lkf, pa, pb, q0, wcap,
+                                 _lib.ENV_TSP if tsp else _lib.ENV_CVRP, Wl)
+        if h.is_cuda and 8 <= num_starts <= 128:
+            self._pack_tensor_tiles(cache)
+        return cache
+
+    @staticmethod
+    def _pack_tensor_tiles(cache: PrecomputedCache) -> None:
+        """Operand image of the tcgen05 kernels (multistart rows): fp16 hi/lo tiles of K, L, V^T."""
+        B, n, _ = cache.node_embeddings.shape
+        nbytes = _lib.lib().rl4co_tc_image_bytes(C.c_int32(n))
+        if nbytes <= 0:
+            return                      # n_nodes beyond the tensor path: the fp32 kernels take the rows
+        img = torch.empty(B, nbytes, dtype=torch.uint8, device=cache.node_embeddings.device)
+        err = _lib.new_err(img.device)
+        cs = cache.cstruct()
+        _lib.check(_lib.lib().rl4co_tc_pack(C.byref(cs), _lib.ptr(img), _lib.ptr(err), _lib.stream_ptr()),
+                   "rl4co_tc_pack")
+        cache.tc_img = img
+        cache.tc_err = err              # read together with the rollout's error word
 
     @torch.no_grad()
-    def forward(self, td, cached: PrecomputedCache, num_starts: int = 0):
-        """am/decoder.py:161-198 -> (logits [rows,N'], mask [rows,N']) in start-major row order."""
+    def forward(self, td, cached: PrecomputedCache, num_starts: int = 0, impl: int = _lib.IMPL_AUTO,
+                debug: Optional[dict] = None):
+        """am/decoder.py:161-198 -> (logits [rows,N'], mask [rows,N']) in start-major row order.
+        Multistart rows (8 <= S <= 128) past the first step run on the tcgen05 kernel."""
         mask = td["action_mask"].contiguous()
         rows, n = mask.shape
         dev = mask.device
@@ -130,6 +152,27 @@ class AttentionModelDecoder(nn.Module):
         err = _lib.new_err(dev)
         cs = cached.cstruct()
         cur = td["current_node"].contiguous()
+        use_tc = impl != _lib.IMPL_FP32 and cached.tc_img is not None and 8 <= rows // cs.B <= 128
+        if impl == _lib.IMPL_TC and not use_tc:
+            raise RuntimeError("tensor-core decode step needs multistart rows (8 <= S <= 128) and a packed cache")
+        if use_tc:
+            flat = lambda t: t.reshape(rows).contiguous()
+            first = flat(td["first_node"]) if self.env_name == "tsp" else None
+            used = flat(td["used_capacity"]) if self.env_name == "cvrp" else None
+            cap = flat(td["vehicle_capacity"]) if self.env_name == "cvrp" else None
+            ds = dh = None
+            if debug is not None:
+                ds = torch.zeros(rows, 8, n, dtype=torch.float32, device=dev)
+                dh = torch.zeros(rows, 128, dtype=torch.float32, device=dev)
+                debug["scores"], debug["heads"] = ds, dh
+            rc = _lib.lib().rl4co_tc_decode_step(
+                C.c_int32(cached.env_id), C.byref(cs), _lib.ptr(first), _lib.ptr(flat(cur)), _lib.ptr(used),
+                _lib.ptr(cap), _lib.ptr(mask), _lib.ptr(logits), _lib.ptr(ds), _lib.ptr(dh), _lib.ptr(err),
+                C.c_int64(rows), _lib.stream_ptr())
+            _lib.check(rc, "rl4co_tc_decode_step")
+            if self.pointer.check_nan:
+                _lib.raise_on_err(err)
+            return logits, mask
         if self.env_name == "tsp":
             first, i_step, used, cap = td["first_node"].contiguous(), td["i"].contiguous(), None, None
         else:

@@ -144,6 +144,8 @@ class AttentionModelPolicy(nn.Module):
         ll = torch.empty(rows, dtype=torch.float32, device=dev)
         lengths = torch.empty(rows, dtype=torch.int32, device=dev)
         meta = torch.zeros(3, dtype=torch.int32, device=dev)      # [max_len, err0, err1]
+        if getattr(cache, "tc_err", None) is not None:
+            meta[1:].bitwise_or_(cache.tc_err)                    # fp16-range flag of rl4co_tc_pack, no sync
         noise = cfg.get("noise")
         if noise is not None:
             if tuple(noise.shape) != (rows, T, n):
@@ -166,7 +168,7 @@ class AttentionModelPolicy(nn.Module):
             actions=acts.data_ptr(), logp=logp.data_ptr(),
             logp_all=logp_all.data_ptr() if store_all else None, reward=reward.data_ptr(),
             log_likelihood=ll.data_ptr(), lengths=lengths.data_ptr(), max_len=meta.data_ptr(),
-            err=meta.data_ptr() + 4)
+            err=meta.data_ptr() + 4, impl=int(cfg.get("impl", _lib.IMPL_AUTO)))
         events = cfg.get("_events")           # bench.py: CUDA events around the kernel alone
         if events is not None:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

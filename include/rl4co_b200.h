@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define RL4CO_B200_ABI_VERSION 1
+#define RL4CO_B200_ABI_VERSION 2
 
 /* return codes */
 #define RL4CO_OK 0
@@ -39,6 +39,7 @@ extern "C" {
 #define RL4CO_ERR_INVALID_TOUR 8    /* "Invalid tour"                   tsp/env.py:163-168, cvrp/env.py:165-170 */
 #define RL4CO_ERR_CAPACITY 16       /* "Used more than capacity"        cvrp/env.py:176-185 */
 #define RL4CO_ERR_MAX_STEPS 32      /* max_steps exceeded               constructive/base.py:246-250 */
+#define RL4CO_ERR_FP16_RANGE 64     /* a cache table value is outside the fp16 range of the tensor path */
 
 /* env ids, decode modes */
 #define RL4CO_ENV_TSP 0
@@ -46,6 +47,11 @@ extern "C" {
 #define RL4CO_MODE_GREEDY 0         /* decoding.py:391-401 */
 #define RL4CO_MODE_SAMPLING 1       /* decoding.py:403-417 with supplied / counter noise */
 #define RL4CO_MODE_EVALUATE 2       /* decoding.py:452-465 */
+
+/* rollout kernel selection */
+#define RL4CO_IMPL_AUTO 0           /* tensor path when num_starts >= 8 and cache->tc_img is set */
+#define RL4CO_IMPL_FP32 1           /* fp32 CUDA-core kernels                                     */
+#define RL4CO_IMPL_TC 2             /* tcgen05 kernels; error if the shape is unsupported         */
 
 int rl4co_b200_abi_version(void);
 const char* rl4co_last_error(void);
@@ -106,7 +112,10 @@ int rl4co_select(const float* logits, const uint8_t* mask, float tanh_clipping,
  *   pa     : TSP  h @ W_ctx[:, :E]^T  (first-node half, context.py:118-140); CVRP NULL
  *   pb     : TSP  h @ W_ctx[:, E:]^T + graph_context ; CVRP h @ W_ctx[:, :E]^T + graph_context
  *   q0     : TSP  [B,E] W_ctx @ W_placeholder + graph_context (context.py:124-132); CVRP NULL
- *   wcap   : CVRP [E] W_ctx[:, E]  (remaining-capacity column, context.py:155-157); TSP NULL  */
+ *   wcap   : CVRP [E] W_ctx[:, E]  (remaining-capacity column, context.py:155-157); TSP NULL
+ *   tc_img : [B, rl4co_tc_image_bytes(n_nodes)] bytes written by rl4co_tc_pack from gk/gv/lk: the
+ *            fp16 hi/lo operand tiles of the tcgen05 kernels (K scaled by 1/sqrt(d), L by 1/sqrt(E),
+ *            V transposed), laid out exactly as they sit in shared memory.  NULL = fp32 path only.  */
 typedef struct rl4co_cache {
     const float* gk;
     const float* gv;
@@ -115,6 +124,7 @@ typedef struct rl4co_cache {
     const float* pb;
     const float* q0;
     const float* wcap;
+    const void* tc_img; /* nullable: operand image built by rl4co_tc_pack (tensor path, multistart) */
     int64_t B;
     int32_t n_nodes;
     int32_t embed_dim; /* must be 128 */
@@ -159,9 +169,24 @@ typedef struct rl4co_rollout_args {
     int32_t* lengths;          /* out [rows]  actions emitted before the row was done       */
     int32_t* max_len;          /* out device int32: max over rows of lengths (pre-zeroed)   */
     int32_t* err;              /* device int32[2] (pre-zeroed)                              */
+    int32_t impl;              /* RL4CO_IMPL_AUTO / _FP32 (CUDA cores) / _TC (tcgen05, needs tc_img) */
 } rl4co_rollout_args;
 
 int rl4co_rollout(const rl4co_cache* cache, const rl4co_rollout_args* args, void* stream);
+
+/* ---- Tensor-core (tcgen05/TMEM) path for multistart rows: S = rows/B starts of an instance form the
+ * M dimension of the MMAs (8 <= S <= 128, n_nodes <= 112).  Same arithmetic as above with every fp32
+ * operand split into fp16 hi + lo and three MMAs per product (fp32 accumulate).                      */
+int64_t rl4co_tc_image_bytes(int32_t n_nodes); /* bytes per instance of cache->tc_img; 0 = unsupported */
+int rl4co_tc_pack(const rl4co_cache* cache, void* image, int32_t* err, void* stream);
+/* AttentionModelDecoder.forward (am/decoder.py:161-198) for multistart rows on the tensor path: RAW
+ * logits [rows, n_nodes].  TSP callers must be past the first step (i >= 1, always true after the
+ * multistart pre-hook).  dbg_scores [rows,8,n_nodes] / dbg_heads [rows,128] (nullable) receive the
+ * pre-mask attention scores and the normalised glimpse heads for the parity tests.                   */
+int rl4co_tc_decode_step(int32_t env, const rl4co_cache* cache, const int64_t* first_node,
+                         const int64_t* current_node, const float* used_capacity,
+                         const float* vehicle_capacity, const uint8_t* mask, float* logits_out,
+                         float* dbg_scores, float* dbg_heads, int32_t* err, int64_t rows, void* stream);
 
 /* counter-noise reference values, for tests: gumbel [rows, n_nodes] at step t */
 int rl4co_noise_gumbel(uint32_t seed, int64_t inst_offset, int64_t B, int32_t t, float* out,

@@ -24,15 +24,16 @@ def test_library_builds_and_exports_header_symbols():
     for s in syms:
         assert hasattr(L, s), f"{s} declared in the header but not exported"
     assert set(syms) == set(_lib.EXPORTS)
-    assert L.rl4co_b200_abi_version() == 1
+    assert L.rl4co_b200_abi_version() == _lib.ABI_VERSION
 
 
 def test_struct_layouts_match_header():
     from eam_rl4co_b200 import _lib
-    # 7 pointers + int64 + 3 int32 (+pad) ; see include/rl4co_b200.h
-    assert C.sizeof(_lib.Cache) == 7 * 8 + 8 + 16
+    # 8 pointers + int64 + 3 int32 (+pad) ; see include/rl4co_b200.h
+    assert C.sizeof(_lib.Cache) == 8 * 8 + 8 + 16
     assert _lib.RolloutArgs.seed.offset == 24 and _lib.RolloutArgs.inst_offset.offset == 32
-    assert C.sizeof(_lib.RolloutArgs) == 160 and _lib.RolloutArgs.err.offset == 152
+    assert C.sizeof(_lib.RolloutArgs) == 168 and _lib.RolloutArgs.err.offset == 152
+    assert _lib.RolloutArgs.impl.offset == 160
 
 
 def test_argument_errors_return_codes_without_launching():
@@ -40,11 +41,11 @@ def test_argument_errors_return_codes_without_launching():
     L = _lib.lib()
     rc = L.rl4co_rollout(None, None, None)
     assert rc == -1 and b"null args" in L.rl4co_last_error()
-    cache = _lib.Cache(None, None, None, None, None, None, None, 1, 300, 128, 8)
+    cache = _lib.Cache(None, None, None, None, None, None, None, None, 1, 300, 128, 8)
     rc = L.rl4co_decode_step(0, C.byref(cache), None, None, None, None, None, None, None, None,
                              C.c_int64(1), None)
     assert rc == -1 and b"n_nodes=300" in L.rl4co_last_error()
-    cache = _lib.Cache(None, None, None, None, None, None, None, 1, 20, 64, 8)
+    cache = _lib.Cache(None, None, None, None, None, None, None, None, 1, 20, 64, 8)
     rc = L.rl4co_decode_step(0, C.byref(cache), None, None, None, None, None, None, None, None,
                              C.c_int64(1), None)
     assert rc == -1 and b"embed_dim=128" in L.rl4co_last_error()
