@@ -15,14 +15,14 @@ SOURCES = ["capi.cu", "env_kernels.cu", "decode_kernels.cu", "rollout_kernel.cu"
 
 ENV_TSP, ENV_CVRP = 0, 1
 MODE_GREEDY, MODE_SAMPLING, MODE_EVALUATE = 0, 1, 2
-ERR_MESSAGES = [  # (bit, reference assertion text)
+ERR_MESSAGES = [  # (bit, reference assertion text); first match is raised
+    (64, "decoder cache value outside the fp16 range of the tensor-core path"),
     (1, "Logits contain NaNs"),
     (2, "infeasible action selected"),
     (4, "Logprobs should not be -inf, check sampling procedure!"),
     (8, "Invalid tour"),
     (16, "Used more than capacity"),
     (32, "Exceeded maximum number of steps during decoding"),
-    (64, "decoder cache value outside the fp16 range of the tensor-core path"),
 ]
 IMPL_AUTO, IMPL_FP32, IMPL_TC = 0, 1, 2
 ABI_VERSION = 2

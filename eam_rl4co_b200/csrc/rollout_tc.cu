@@ -556,6 +556,7 @@ __device__ __forceinline__ void cta_setup(Ctx& x) {
         mbar_init(&x.s->mma_bar, 1);
         fence_mbar_init();
     }
+    __syncwarp();
     if (warp == 0) tmem_alloc(&x.s->tmem_ptr, kTmemCols);
     for (uint32_t i = threadIdx.x; i < 2u * kQTileBytes / 16u; i += kThreads)
         reinterpret_cast<uint4*>(x.q_hi_p)[i] = make_uint4(0, 0, 0, 0);
