@@ -66,7 +66,8 @@ class RolloutArgs(C.Structure):
                 ("actions_in", C.c_void_p), ("actions_in_stride", C.c_int64),
                 ("actions_in_T", C.c_int32), ("actions", C.c_void_p), ("logp", C.c_void_p),
                 ("logp_all", C.c_void_p), ("reward", C.c_void_p), ("log_likelihood", C.c_void_p),
-                ("lengths", C.c_void_p), ("max_len", C.c_void_p), ("err", C.c_void_p), ("impl", C.c_int32)]
+                ("lengths", C.c_void_p), ("max_len", C.c_void_p), ("err", C.c_void_p), ("impl", C.c_int32),
+                ("phase_cycles", C.c_void_p)]
 
 
 _lib = None

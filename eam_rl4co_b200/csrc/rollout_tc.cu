@@ -32,7 +32,8 @@ constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kColSP = 0;   // scores / probabilities of 4 heads: 4 x NPAD columns
 constexpr uint32_t kColO = 448;  // glimpse accumulators of 4 heads: 4 x 16 columns
 constexpr uint32_t kColHA = 0;   // heads as A operand: hi [0,64), lo [64,128)
-constexpr uint32_t kColLG = 128; // logits accumulators: NPAD columns
+constexpr uint32_t kColLG = 128; // logits accumulators, even k-steps: NPAD columns
+constexpr uint32_t kColLG2 = 240;// logits accumulators, odd k-steps (two chains pipeline in the tensor core)
 // K-major, no-swizzle operand tiles (see tc_ptx.cuh::smem_desc)
 constexpr uint32_t kLBO = 128;                 // static tiles: the K-chunks of a row group are contiguous
 constexpr uint32_t kSBO_KL = 16 * kLBO;        // K / L tiles: 16 chunks (128 channels) per row group
@@ -148,26 +149,44 @@ __global__ void __launch_bounds__(256) tc_pack_kernel(rl4co_cache c, unsigned ch
 
 // Q tile of head group g (channels [64g, 64g+64)) for rows [0,S): context.py:118-140 (TSP,
 // pa[first] + pb[cur]) / :70-74,155-157 (CVRP, pb[cur] + (cap - used) * wcap), split to fp16 hi/lo.
-template <int ENV>
+template <int ENV, int FIRST_WARP>
 __device__ __forceinline__ void build_q(const Ctx& x, const rl4co_cache& c, int64_t b, int S, int g, int warp,
                                         int lane) {
+    // warps [FIRST_WARP, 16) take part (the MMA issuer warps are left out while they issue PV)
+    constexpr int NW = kWarps - FIRST_WARP;
+    constexpr int ITERS = (kRows / 2 + NW - 1) / NW;
+    if (warp < FIRST_WARP) return;
+    const int w = warp - FIRST_WARP;
     const int l16 = lane & 15, half = lane >> 4;
     const int64_t base = b * (int64_t)c.n_nodes;
     const int choff = 64 * g + 4 * l16;
-    for (int rp = warp; 2 * rp < S; rp += kWarps) {
-        const int r = 2 * rp + half;
+    // kRows / 2 row pairs over NW warps: issue every gather first (L2 latency overlaps)
+    float4 qa[ITERS], qb[ITERS];
+    float rem[ITERS];
+#pragma unroll
+    for (int it = 0; it < ITERS; ++it) {
+        const int r = 2 * (w + NW * it) + half;
+        qa[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        qb[it] = qa[it];
+        rem[it] = 0.f;
         if (r < S) {
-            const int cur = x.s->cur[r];
-            float4 q = ld4(c.pb + (base + cur) * kE + choff);
-            if (ENV == RL4CO_ENV_TSP) {
-                const float4 a = ld4(c.pa + (base + x.s->first[r]) * kE + choff);
-                q = make_float4(a.x + q.x, a.y + q.y, a.z + q.z, a.w + q.w);
-            } else {
-                const float rem = x.s->rem[r];
-                const float4 wc = ld4(c.wcap + choff);
-                q = make_float4(fmaf(rem, wc.x, q.x), fmaf(rem, wc.y, q.y), fmaf(rem, wc.z, q.z),
-                                fmaf(rem, wc.w, q.w));
-            }
+            qb[it] = ld4(c.pb + (base + x.s->cur[r]) * kE + choff);
+            if (ENV == RL4CO_ENV_TSP) qa[it] = ld4(c.pa + (base + x.s->first[r]) * kE + choff);
+            else rem[it] = x.s->rem[r];
+        }
+    }
+    float4 wc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ENV == RL4CO_ENV_CVRP) wc = ld4(c.wcap + choff);
+#pragma unroll
+    for (int it = 0; it < ITERS; ++it) {
+        const int r = 2 * (w + NW * it) + half;
+        if (r < S) {
+            float4 q;
+            if (ENV == RL4CO_ENV_TSP)
+                q = make_float4(qa[it].x + qb[it].x, qa[it].y + qb[it].y, qa[it].z + qb[it].z, qa[it].w + qb[it].w);
+            else
+                q = make_float4(fmaf(rem[it], wc.x, qb[it].x), fmaf(rem[it], wc.y, qb[it].y),
+                                fmaf(rem[it], wc.z, qb[it].z), fmaf(rem[it], wc.w, qb[it].w));
             uint32_t h0, l0, h1, l1;
             split2(q.x, q.y, h0, l0);
             split2(q.z, q.w, h1, l1);
@@ -186,60 +205,65 @@ __device__ __forceinline__ void wait_mma(const Ctx& x, uint32_t& par) {
     tc_fence_after();
 }
 
-// scores of the 4 heads of group g: S_hg = Q_hg . K_h^T, three MMAs each (hi*hi + hi*lo + lo*hi)
-__device__ __forceinline__ void issue_scores(const Ctx& x, int g) {
+// MMA issue is spread over four threads (lane 0 of warps 0..3, one per scheduler): issuer `hg` owns the
+// accumulator chain of head hg of the group (scores, PV) or of one k-step parity (logits), so the four
+// chains are issued concurrently and pipeline in the tensor core; each issuer commits to the same
+// mbarrier (count 4).  Descriptors are advanced by adding to their low word.
+
+// scores of head hg of group g: S_hg = Q_hg . K_h^T, three MMAs (hi*hi + hi*lo + lo*hi)
+__device__ __forceinline__ void issue_scores(const Ctx& x, int g, int hg) {
     tc_fence_after();
     const uint32_t id = idesc_f16(kRows, x.npad);
-#pragma unroll
-    for (int hg = 0; hg < 4; ++hg) {
-        const int h = 4 * g + hg;
-        const uint64_t aq_hi = smem_desc(x.q_hi + 2u * hg * kLBO_Q, kLBO_Q, kSBO_Q);
-        const uint64_t aq_lo = smem_desc(x.q_lo + 2u * hg * kLBO_Q, kLBO_Q, kSBO_Q);
-        const uint64_t bk_hi = smem_desc(x.k_hi + 2u * h * kLBO, kLBO, kSBO_KL);
-        const uint64_t bk_lo = smem_desc(x.k_lo + 2u * h * kLBO, kLBO, kSBO_KL);
-        const uint32_t d = x.tmem + kColSP + (uint32_t)(hg * x.npad);
-        mma_ss(d, aq_hi, bk_hi, id, 0u);
-        mma_ss(d, aq_hi, bk_lo, id, 1u);
-        mma_ss(d, aq_lo, bk_hi, id, 1u);
-    }
+    const int h = 4 * g + hg;
+    const uint64_t aq_hi = smem_desc(x.q_hi + 2u * hg * kLBO_Q, kLBO_Q, kSBO_Q);
+    const uint64_t aq_lo = smem_desc(x.q_lo + 2u * hg * kLBO_Q, kLBO_Q, kSBO_Q);
+    const uint64_t bk_hi = smem_desc(x.k_hi + 2u * h * kLBO, kLBO, kSBO_KL);
+    const uint64_t bk_lo = smem_desc(x.k_lo + 2u * h * kLBO, kLBO, kSBO_KL);
+    const uint32_t d = x.tmem + kColSP + (uint32_t)(hg * x.npad);
+    mma_ss(d, aq_hi, bk_hi, id, 0u);
+    mma_ss(d, aq_hi, bk_lo, id, 1u);
+    mma_ss(d, aq_lo, bk_hi, id, 1u);
     tc_commit(&x.s->mma_bar);
 }
 
 // O_hg = P_hg . V_h : A = P from TMEM (hi/lo pairs per 16-node chunk), B = V^T tile rows [16h, 16h+16)
-__device__ __forceinline__ void issue_pv(const Ctx& x, int g) {
+__device__ __forceinline__ void issue_pv(const Ctx& x, int g, int hg) {
     tc_fence_after();
     const uint32_t id = idesc_f16(kRows, 16);
-#pragma unroll
-    for (int hg = 0; hg < 4; ++hg) {
-        const int h = 4 * g + hg;
-        const uint32_t d = x.tmem + kColO + 16u * hg;
-        const uint32_t a0 = x.tmem + kColSP + (uint32_t)(hg * x.npad);
-        const uint32_t vb = 2u * h * x.sbo_v;
-        for (int jk = 0; jk < x.nch; ++jk) {
-            const uint64_t bv_hi = smem_desc(x.v_hi + vb + 2u * jk * kLBO, kLBO, x.sbo_v);
-            const uint64_t bv_lo = smem_desc(x.v_lo + vb + 2u * jk * kLBO, kLBO, x.sbo_v);
-            const uint32_t a_hi = a0 + 16u * jk, a_lo = a_hi + 8u;
-            mma_ts(d, a_hi, bv_hi, id, jk > 0 ? 1u : 0u);
-            mma_ts(d, a_hi, bv_lo, id, 1u);
-            mma_ts(d, a_lo, bv_hi, id, 1u);
-        }
+    const int h = 4 * g + hg;
+    uint64_t bv_hi = smem_desc(x.v_hi + 2u * h * x.sbo_v, kLBO, x.sbo_v);
+    uint64_t bv_lo = smem_desc(x.v_lo + 2u * h * x.sbo_v, kLBO, x.sbo_v);
+    const uint32_t d = x.tmem + kColO + 16u * hg;
+    uint32_t a = x.tmem + kColSP + (uint32_t)(hg * x.npad);
+    for (int jk = 0; jk < x.nch; ++jk) {
+        mma_ts(d, a, bv_hi, id, jk > 0 ? 1u : 0u);
+        mma_ts(d, a, bv_lo, id, 1u);
+        mma_ts(d, a + 8u, bv_hi, id, 1u);
+        a += 16u;
+        bv_hi += (2u * kLBO) >> 4;   // next 16 nodes = two 16-byte K-chunks further
+        bv_lo += (2u * kLBO) >> 4;
     }
     tc_commit(&x.s->mma_bar);
 }
 
-// logits = heads . (L W_out / sqrt(E))^T : A = heads from TMEM (k-step jk = head jk), B = L tile
-__device__ __forceinline__ void issue_logits(const Ctx& x) {
+// logits = heads . (L W_out / sqrt(E))^T : A = heads from TMEM (k-step jk = head jk), B = L tile;
+// issuer par in {0,1} takes the k-steps of that parity and accumulates in kColLG / kColLG2 (summed by
+// the readers); issuers 2, 3 only arrive.
+__device__ __forceinline__ void issue_logits(const Ctx& x, int par) {
     tc_fence_after();
-    const uint32_t id = idesc_f16(kRows, x.npad);
-    const uint32_t d = x.tmem + kColLG;
+    if (par < 2) {
+        const uint32_t id = idesc_f16(kRows, x.npad);
+        const uint32_t d = x.tmem + (par ? kColLG2 : kColLG);
 #pragma unroll
-    for (int jk = 0; jk < 8; ++jk) {
-        const uint64_t bl_hi = smem_desc(x.l_hi + 2u * jk * kLBO, kLBO, kSBO_KL);
-        const uint64_t bl_lo = smem_desc(x.l_lo + 2u * jk * kLBO, kLBO, kSBO_KL);
-        const uint32_t a_hi = x.tmem + kColHA + 8u * jk, a_lo = a_hi + 64u;
-        mma_ts(d, a_hi, bl_hi, id, jk > 0 ? 1u : 0u);
-        mma_ts(d, a_hi, bl_lo, id, 1u);
-        mma_ts(d, a_lo, bl_hi, id, 1u);
+        for (int j2 = 0; j2 < 4; ++j2) {
+            const int jk = 2 * j2 + par;
+            const uint64_t bl_hi = smem_desc(x.l_hi + 2u * jk * kLBO, kLBO, kSBO_KL);
+            const uint64_t bl_lo = smem_desc(x.l_lo + 2u * jk * kLBO, kLBO, kSBO_KL);
+            const uint32_t a = x.tmem + kColHA + 8u * jk;
+            mma_ts(d, a, bl_hi, id, j2 > 0 ? 1u : 0u);
+            mma_ts(d, a, bl_lo, id, 1u);
+            mma_ts(d, a + 64u, bl_hi, id, 1u);
+        }
     }
     tc_commit(&x.s->mma_bar);
 }
@@ -248,85 +272,184 @@ __device__ __forceinline__ void issue_logits(const Ctx& x) {
 // feasible nodes, 0 elsewhere (attention.py:308-322: masked scores are -inf -> exactly 0), written
 // back in place as fp16 hi/lo: chunk c (16 nodes) -> hi in columns [16c,16c+8), lo in [16c+8,16c+16).
 // Returns 1 / rowsum (0 for a row without feasible nodes: padding rows).
+__device__ __forceinline__ void shift_mask16(uint32_t& a0, uint32_t& a1, uint32_t& a2, uint32_t& a3) {
+    a0 = __funnelshift_r(a0, a1, 16);
+    a1 = __funnelshift_r(a1, a2, 16);
+    a2 = __funnelshift_r(a2, a3, 16);
+    a3 >>= 16;
+}
+
+// masked max of one 16-column chunk (two chains)
+__device__ __forceinline__ void chunk_max(const uint32_t (&v)[16], uint32_t bits, float& m0, float& m1) {
+#pragma unroll
+    for (int i = 0; i < 16; i += 2) {
+        if (bits & (1u << i)) m0 = fmaxf(m0, __uint_as_float(v[i]));
+        if (bits & (2u << i)) m1 = fmaxf(m1, __uint_as_float(v[i + 1]));
+    }
+}
+// P of one 16-column chunk -> fp16 hi/lo words, row sums in two chains
+__device__ __forceinline__ void chunk_exp(const uint32_t (&v)[16], uint32_t bits, float ml, float& l0, float& l1,
+                                          uint32_t (&hi)[8], uint32_t (&lo)[8]) {
+    const float kLog2e = 1.4426950408889634f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        float p0 = ex2_approx(fmaf(__uint_as_float(v[2 * i]), kLog2e, -ml));
+        float p1 = ex2_approx(fmaf(__uint_as_float(v[2 * i + 1]), kLog2e, -ml));
+        p0 = (bits & (1u << (2 * i))) ? p0 : 0.f;
+        p1 = (bits & (2u << (2 * i))) ? p1 : 0.f;
+        l0 += p0;
+        l1 += p1;
+        split2(p0, p1, hi[i], lo[i]);
+    }
+}
+// the last chunk when it holds <= 12 real nodes: `tq` 4-column loads instead of 16 columns
+__device__ __forceinline__ void load_tail(uint32_t addr, int tq, uint32_t (&v)[16]) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        uint32_t v4[4] = {0u, 0u, 0u, 0u};
+        if (k < tq) tmem_ld4(addr + 4u * k, v4);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v[4 * k + i] = v4[i];
+    }
+#pragma unroll
+    for (int i = 12; i < 16; ++i) v[i] = 0u;
+}
+
 __device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int row, float* dbg_scores, int n) {
     const uint32_t w0 = x.s->maskw[0][row], w1 = x.s->maskw[1][row], w2 = x.s->maskw[2][row],
                    w3 = x.s->maskw[3][row];
-    float m = -INFINITY;
+    // full 16-column chunks, then an optional short tail (n = 100: 6 chunks + 4 columns)
+    const int lastv = n - 16 * (x.nch - 1);
+    const int tq = lastv <= 12 ? (lastv + 3) >> 2 : 0;
+    const int nfull = tq ? x.nch - 1 : x.nch;
+    // pass 1: masked row maximum; the next chunk's TMEM load is in flight while one is reduced
+    float m0 = -INFINITY, m1 = -INFINITY;
     uint32_t a0 = w0, a1 = w1, a2 = w2, a3 = w3;
-    for (int ch = 0; ch < x.nch; ++ch) {
-        uint32_t v[16];
-        tmem_ld16(sp + 16u * ch, v);
+    uint32_t va[16], vb[16];
+    if (nfull > 0) tmem_ld16(sp, va);
+    for (int ch = 0; ch < nfull; ch += 2) {
         tc_wait_ld();
+        if (ch + 1 < nfull) tmem_ld16(sp + 16u * (ch + 1), vb);
+        if (dbg_scores != nullptr) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            if (dbg_scores != nullptr && 16 * ch + i < n) dbg_scores[16 * ch + i] = __uint_as_float(v[i]);
-            if (a0 & (1u << i)) m = fmaxf(m, __uint_as_float(v[i]));
+            for (int i = 0; i < 16; ++i)
+                if (16 * ch + i < n) dbg_scores[16 * ch + i] = __uint_as_float(va[i]);
         }
-        a0 = __funnelshift_r(a0, a1, 16);
-        a1 = __funnelshift_r(a1, a2, 16);
-        a2 = __funnelshift_r(a2, a3, 16);
-        a3 >>= 16;
+        chunk_max(va, a0, m0, m1);
+        shift_mask16(a0, a1, a2, a3);
+        if (ch + 1 < nfull) {
+            tc_wait_ld();
+            if (ch + 2 < nfull) tmem_ld16(sp + 16u * (ch + 2), va);
+            if (dbg_scores != nullptr) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                    if (16 * (ch + 1) + i < n) dbg_scores[16 * (ch + 1) + i] = __uint_as_float(vb[i]);
+            }
+            chunk_max(vb, a0, m0, m1);
+            shift_mask16(a0, a1, a2, a3);
+        }
     }
+    if (tq) {
+        load_tail(sp + 16u * nfull, tq, va);
+        tc_wait_ld();
+        if (dbg_scores != nullptr) {
+#pragma unroll
+            for (int i = 0; i < 12; ++i)
+                if (16 * nfull + i < n) dbg_scores[16 * nfull + i] = __uint_as_float(va[i]);
+        }
+        chunk_max(va, a0, m0, m1);
+    }
+    float m = fmaxf(m0, m1);
     if (m == -INFINITY) m = 0.f;
-    const float kLog2e = 1.4426950408889634f;
-    const float ml = m * kLog2e;
-    float l = 0.f;
+    const float ml = m * 1.4426950408889634f;
+    // pass 2: P = exp(S - m) on feasible nodes, split to fp16 hi/lo, stored over S
+    float l0 = 0.f, l1 = 0.f;
     a0 = w0; a1 = w1; a2 = w2; a3 = w3;
-    for (int ch = 0; ch < x.nch; ++ch) {
-        uint32_t v[16];
-        tmem_ld16(sp + 16u * ch, v);
+    if (nfull > 0) tmem_ld16(sp, va);
+    for (int ch = 0; ch < nfull; ch += 2) {
+        tc_wait_ld();
+        if (ch + 1 < nfull) tmem_ld16(sp + 16u * (ch + 1), vb);
+        {
+            uint32_t hi[8], lo[8];
+            chunk_exp(va, a0, ml, l0, l1, hi, lo);
+            tmem_st8(sp + 16u * ch, hi);
+            tmem_st8(sp + 16u * ch + 8u, lo);
+        }
+        shift_mask16(a0, a1, a2, a3);
+        if (ch + 1 < nfull) {
+            tc_wait_ld();
+            if (ch + 2 < nfull) tmem_ld16(sp + 16u * (ch + 2), va);
+            uint32_t hi[8], lo[8];
+            chunk_exp(vb, a0, ml, l0, l1, hi, lo);
+            tmem_st8(sp + 16u * (ch + 1), hi);
+            tmem_st8(sp + 16u * (ch + 1) + 8u, lo);
+            shift_mask16(a0, a1, a2, a3);
+        }
+    }
+    if (tq) {
+        load_tail(sp + 16u * nfull, tq, va);
         tc_wait_ld();
         uint32_t hi[8], lo[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            float p0 = ex2_approx(fmaf(__uint_as_float(v[2 * i]), kLog2e, -ml));
-            float p1 = ex2_approx(fmaf(__uint_as_float(v[2 * i + 1]), kLog2e, -ml));
-            p0 = (a0 & (1u << (2 * i))) ? p0 : 0.f;
-            p1 = (a0 & (1u << (2 * i + 1))) ? p1 : 0.f;
-            l += p0;
-            l += p1;
-            split2(p0, p1, hi[i], lo[i]);
-        }
-        tmem_st8(sp + 16u * ch, hi);
-        tmem_st8(sp + 16u * ch + 8u, lo);
-        a0 = __funnelshift_r(a0, a1, 16);
-        a1 = __funnelshift_r(a1, a2, 16);
-        a2 = __funnelshift_r(a2, a3, 16);
-        a3 >>= 16;
+        chunk_exp(va, a0, ml, l0, l1, hi, lo);   // mask bits beyond n are 0: the padding becomes exact zeros
+        tmem_st8(sp + 16u * nfull, hi);
+        tmem_st8(sp + 16u * nfull + 8u, lo);
     }
     tc_wait_st();
+    const float l = l0 + l1;
     return l > 0.f ? 1.0f / l : 0.f;
 }
 
 // All GEMM phases of one decoder step; on return the raw logits of the instance sit in TMEM
 // columns [kColLG, kColLG + n) (row = lane).  dbg_* (nullable) receive scores [S?,8,n] / heads [.,128]
 // of this thread's row for the parity tests.
+#define R4_STAMP(k)                                       \
+    do {                                                  \
+        if (prof != nullptr) {                            \
+            const long long now__ = clock64();            \
+            prof[k] += now__ - tprev;                     \
+            tprev = now__;                                \
+        }                                                 \
+    } while (0)
+
 template <int ENV>
 __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cache& c, int64_t b, int S,
-                                                  uint32_t& mma_par, float* dbg_scores_row, float* dbg_heads_row) {
+                                                  uint32_t& mma_par, float* dbg_scores_row, float* dbg_heads_row,
+                                                  long long* prof, long long& tprev) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q = warp & 3, j = warp >> 2, row = 32 * q + lane;
     const uint32_t lane_base = x.tmem + ((uint32_t)(32 * q) << 16);
     const int n = c.n_nodes;
+    const bool issuer = (warp < 4) && (lane == 0);   // issuer `warp` owns accumulator chain `warp`
     float hv[2][16];
+    build_q<ENV, 0>(x, c, b, S, 0, warp, lane);
+    __syncthreads();
+    R4_STAMP(0);
+    if (issuer) issue_scores(x, 0, warp);
 #pragma unroll
     for (int g = 0; g < 2; ++g) {
-        build_q<ENV>(x, c, b, S, g, warp, lane);
-        __syncthreads();
-        if (threadIdx.x == 0) issue_scores(x, g);
-        wait_mma(x, mma_par);
+        wait_mma(x, mma_par);                          // scores of group g
+        R4_STAMP(1 + 5 * g);
         const float inv_l = softmax_inplace(x, lane_base + kColSP + (uint32_t)(j * x.npad), row,
                                             dbg_scores_row ? dbg_scores_row + (4 * g + j) * n : nullptr, n);
         tc_fence_before();
         __syncthreads();
-        if (threadIdx.x == 0) issue_pv(x, g);
-        wait_mma(x, mma_par);
+        R4_STAMP(2 + 5 * g);
+        if (issuer) issue_pv(x, g, warp);
+        if (g == 0) build_q<ENV, 4>(x, c, b, S, 1, warp, lane);   // Q of heads 4..7 while PV(0) runs (scores(0) is done)
+        R4_STAMP(3 + 5 * g);
+        wait_mma(x, mma_par);                          // PV of group g
+        R4_STAMP(4 + 5 * g);
         uint32_t o[16];
         tmem_ld16(lane_base + kColO + 16u * j, o);
         tc_wait_ld();
 #pragma unroll
         for (int i = 0; i < 16; ++i) hv[g][i] = __uint_as_float(o[i]) * inv_l;
         tc_fence_before();
+        if (g == 0) {
+            __syncthreads();
+            if (issuer) issue_scores(x, 1, warp);
+            R4_STAMP(5);
+        }
     }
     // heads -> A operand in TMEM (fp16 hi/lo), k-step = head
 #pragma unroll
@@ -345,8 +468,10 @@ __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cach
     tc_wait_st();
     tc_fence_before();
     __syncthreads();
-    if (threadIdx.x == 0) issue_logits(x);
+    R4_STAMP(10);
+    if (issuer) issue_logits(x, warp);
     wait_mma(x, mma_par);
+    R4_STAMP(11);
 }
 
 // ---- selection: process_logits + Greedy / Sampling / Evaluate (decoding.py:140-190, 346-465) --------
@@ -357,6 +482,15 @@ struct RowSel {
     float logp;
 };
 
+// tanh(v) = 1 - 2 / (1 + e^(2v)) on the MUFU ex2 / rcp approximations: absolute error ~2e-7
+// (+-1 exactly at the tails, NaN propagates); the reference's clipped logit 10*tanh is matched to ~2e-6.
+__device__ __forceinline__ float tanh_fast(float v) {
+    const float e2 = ex2_approx(v * 2.8853900817779268f);
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e2 + 1.0f));
+    return fmaf(-2.0f, r, 1.0f);
+}
+
 __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_args& a, int n, int q, int j,
                                              int row, bool valid, int64_t grow, int t, int T, uint32_t nkey,
                                              int given, int& err_bits) {
@@ -364,13 +498,19 @@ __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_a
     const uint32_t lg = x.tmem + ((uint32_t)(32 * q) << 16) + kColLG;
     const int U = (n + 3) >> 2;
     const int u0 = (U * j) >> 2, u1 = (U * (j + 1)) >> 2;
-    uint32_t raw[28];
+    uint32_t raw[28], raw2[28];
 #pragma unroll
     for (int k = 0; k < 7; ++k) {
-        uint32_t v4[4] = {0u, 0u, 0u, 0u};
-        if (u0 + k < u1) tmem_ld4(lg + 4u * (u0 + k), v4);
+        uint32_t v4[4] = {0u, 0u, 0u, 0u}, y4[4] = {0u, 0u, 0u, 0u};
+        if (u0 + k < u1) {
+            tmem_ld4(lg + 4u * (u0 + k), v4);
+            tmem_ld4(lg + (kColLG2 - kColLG) + 4u * (u0 + k), y4);
+        }
 #pragma unroll
-        for (int i = 0; i < 4; ++i) raw[4 * k + i] = v4[i];
+        for (int i = 0; i < 4; ++i) {
+            raw[4 * k + i] = v4[i];
+            raw2[4 * k + i] = y4[i];
+        }
     }
     tc_wait_ld();
     const uint32_t w0 = s->maskw[0][row], w1 = s->maskw[1][row], w2 = s->maskw[2][row], w3 = s->maskw[3][row];
@@ -381,48 +521,75 @@ __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_a
     const uint32_t inrange = cnt >= 32 ? 0xffffffffu : ((1u << cnt) - 1u);
     const uint32_t win = __funnelshift_r(lo, hi, sh & 31) & inrange;  // feasible bits of nodes sh .. sh+27
 
+    // every run-time-uniform option is hoisted out of the unrolled element loops: the loops stay
+    // branch-free so that the 28 independent MUFU / FMA chains of a thread overlap
     float xv[28];
-    float lmax = -INFINITY;
     bool nan_local = false;
 #pragma unroll
     for (int e = 0; e < 28; ++e) {
-        const bool feas = (win >> e) & 1u;
-        const float v = __uint_as_float(raw[e]);
-        if (feas && v != v) nan_local = true;                       // attention.py:303-304
-        float xx = a.tanh_clipping > 0.f ? tanhf(v) * a.tanh_clipping : v;   // decoding.py:171-172
-        xx = feas ? xx : -INFINITY;                                 // :177
-        if (a.temperature != 1.0f) xx = xx / a.temperature;         // :179
-        xv[e] = xx;
-        lmax = fmaxf(lmax, xx);
+        xv[e] = __uint_as_float(raw[e]) + __uint_as_float(raw2[e]);
+        nan_local |= ((win >> e) & 1u) && (xv[e] != xv[e]);         // attention.py:303-304
     }
+    if (a.tanh_clipping > 0.f) {                                    // decoding.py:171-172
+        const float clip = a.tanh_clipping;
+#pragma unroll
+        for (int e = 0; e < 28; ++e) xv[e] = tanh_fast(xv[e]) * clip;
+    }
+#pragma unroll
+    for (int e = 0; e < 28; ++e) xv[e] = ((win >> e) & 1u) ? xv[e] : -INFINITY;   // :177
+    if (a.temperature != 1.0f) {                                    // :179
+        const float temp = a.temperature;
+#pragma unroll
+        for (int e = 0; e < 28; ++e) xv[e] = xv[e] / temp;
+    }
+    float lmax = -INFINITY;
+#pragma unroll
+    for (int e = 0; e < 28; ++e) lmax = fmaxf(lmax, xv[e]);
     if (nan_local && valid) err_bits |= RL4CO_ERR_NAN_LOGITS;
     s->red_a[j][row] = lmax;
     bar_sync(1 + q, 128);
     const float mx = fmaxf(fmaxf(s->red_a[0][row], s->red_a[1][row]), fmaxf(s->red_a[2][row], s->red_a[3][row]));
-    float lsum = 0.f;
+    float ls0 = 0.f, ls1 = 0.f;
 #pragma unroll
-    for (int e = 0; e < 28; ++e) lsum += expf(xv[e] - mx);           // exp(-inf) = 0
-    s->red_b[j][row] = lsum;
+    for (int e = 0; e < 28; e += 2) {                               // exp(-inf) = 0
+        ls0 += ex2_approx((xv[e] - mx) * 1.4426950408889634f);
+        ls1 += ex2_approx((xv[e + 1] - mx) * 1.4426950408889634f);
+    }
+    s->red_b[j][row] = ls0 + ls1;
     bar_sync(1 + q, 128);
     const float logsum = logf(((s->red_b[0][row] + s->red_b[1][row]) + s->red_b[2][row]) + s->red_b[3][row]);
+#pragma unroll
+    for (int e = 0; e < 28; ++e) xv[e] = (xv[e] - mx) - logsum;     // log_softmax :190 (xv now holds logp)
+    if (a.logp_all != nullptr && valid) {
+#pragma unroll
+        for (int e = 0; e < 28; ++e)
+            if (e < cnt && sh + e < n) a.logp_all[(grow * T + t) * (int64_t)n + sh + e] = xv[e];
+    }
+    float cand[28];
+    if (a.mode == RL4CO_MODE_SAMPLING) {
+        if (a.gumbel != nullptr) {
+#pragma unroll
+            for (int e = 0; e < 28; ++e)
+                cand[e] = ((win >> e) & 1u) ? xv[e] + a.gumbel[(grow * T + t) * (int64_t)n + sh + e] : xv[e];
+        } else {
+#pragma unroll
+            for (int e = 0; e < 28; ++e) cand[e] = xv[e] + noise_gumbel(nkey, sh + e);   // -inf stays -inf
+        }
+    } else if (a.mode == RL4CO_MODE_EVALUATE) {
+#pragma unroll
+        for (int e = 0; e < 28; ++e) cand[e] = (e < cnt && sh + e == given) ? 0.f : -INFINITY;
+    } else {
+#pragma unroll
+        for (int e = 0; e < 28; ++e) cand[e] = xv[e];
+    }
     float best = -INFINITY, best_lp = -INFINITY;
     int best_i = 0x7fffffff;
 #pragma unroll
     for (int e = 0; e < 28; ++e) {
-        const int node = sh + e;
-        const float lp = (xv[e] - mx) - logsum;                     // log_softmax :190
-        if (a.logp_all != nullptr && valid && e < cnt && node < n) a.logp_all[(grow * T + t) * (int64_t)n + node] = lp;
-        float cand = lp;
-        if (a.mode == RL4CO_MODE_SAMPLING) {
-            if ((win >> e) & 1u)
-                cand = lp + (a.gumbel ? a.gumbel[(grow * T + t) * (int64_t)n + node] : noise_gumbel(nkey, node));
-        } else if (a.mode == RL4CO_MODE_EVALUATE) {
-            cand = (e < cnt && node == given) ? 0.f : -INFINITY;
-        }
-        if (cand > best) {  // ascending node order + strict > = first max index (torch.argmax)
-            best = cand;
-            best_i = node;
-            best_lp = lp;
+        if (cand[e] > best) {  // ascending node order + strict > = first max index (torch.argmax)
+            best = cand[e];
+            best_i = sh + e;
+            best_lp = xv[e];
         }
     }
     s->red_c[j][row] = best;
@@ -553,7 +720,7 @@ __device__ __forceinline__ void cta_setup(Ctx& x) {
     const int warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) {
         mbar_init(&x.s->tma_bar, 1);
-        mbar_init(&x.s->mma_bar, 1);
+        mbar_init(&x.s->mma_bar, 4);   // four MMA issuer threads commit per phase
         fence_mbar_init();
     }
     __syncwarp();
@@ -598,6 +765,9 @@ __global__ void __launch_bounds__(kThreads, 1)
     const int n = c.n_nodes, S = a.num_starts, T = a.max_steps;
     const bool valid = row < S;
     uint32_t tma_par = 0, mma_par = 0;
+    // optional phase timing (debug): thread 0 of CTA 0 accumulates clock64 deltas per phase
+    long long* prof = (a.phase_cycles != nullptr && blockIdx.x == 0 && threadIdx.x == 0) ? a.phase_cycles : nullptr;
+    long long tprev = clock64();
 
     for (int64_t b = blockIdx.x; b < c.B; b += gridDim.x) {
         if (threadIdx.x == 0) load_tiles(x, smem, img, b);
@@ -640,13 +810,14 @@ __global__ void __launch_bounds__(kThreads, 1)
         __syncthreads();
         apply_action<ENV>(x, a, st, n, q, j, row, valid, grow, 0, T, act, 0.f);
         int all_done = __syncthreads_and(!valid || j != 0 || st.done);
+        R4_STAMP(14);
 
         for (int t = 1; !all_done; ++t) {
             if (t >= T) {
                 if (valid && j == 0 && !st.done) err_bits |= RL4CO_ERR_MAX_STEPS;
                 break;
             }
-            decode_step_gemms<ENV>(x, c, b, S, mma_par, nullptr, nullptr);
+            decode_step_gemms<ENV>(x, c, b, S, mma_par, nullptr, nullptr, prof, tprev);
             int given = 0;
             if (a.mode == RL4CO_MODE_EVALUATE && valid) {
                 given = (t < a.actions_in_T) ? (int)a.actions_in[grow * a.actions_in_stride + t] : 0;
@@ -657,9 +828,11 @@ __global__ void __launch_bounds__(kThreads, 1)
             }
             const uint32_t nkey = (a.mode == RL4CO_MODE_SAMPLING) ? noise_key(a.seed, a.inst_offset + b, row, t) : 0u;
             const RowSel sel = select_row(x, a, n, q, j, row, valid, grow, t, T, nkey, given, err_bits);
+            R4_STAMP(12);
             apply_action<ENV>(x, a, st, n, q, j, row, valid, grow, t, T, sel.action, sel.logp);
             tc_fence_before();
             all_done = __syncthreads_and(!valid || j != 0 || st.done);
+            R4_STAMP(13);
         }
         if (valid && j == 0) {
             // closing edge (roll(-1) wraps to the first element: TSP first action, CVRP depot)
@@ -717,23 +890,26 @@ __global__ void __launch_bounds__(kThreads, 1)
         mbar_wait(&s->tma_bar, tma_par);
         tma_par ^= 1u;
         __syncthreads();
+        long long tprev = 0;
         decode_step_gemms<ENV>(x, c, b, S, mma_par,
                                (dbg_scores != nullptr && valid) ? dbg_scores + grow * (int64_t)(8 * n) : nullptr,
-                               (dbg_heads != nullptr && valid) ? dbg_heads + grow * (int64_t)kE : nullptr);
+                               (dbg_heads != nullptr && valid) ? dbg_heads + grow * (int64_t)kE : nullptr, nullptr,
+                               tprev);
         // this thread's quarter of the logit columns
         const uint32_t lg = x.tmem + ((uint32_t)(32 * q) << 16) + kColLG;
         const int U = (n + 3) >> 2;
         const int u0 = (U * j) >> 2, u1 = (U * (j + 1)) >> 2;
         bool nan_local = false;
         for (int u = u0; u < u1; ++u) {
-            uint32_t v4[4];
+            uint32_t v4[4], y4[4];
             tmem_ld4(lg + 4u * u, v4);
+            tmem_ld4(lg + (kColLG2 - kColLG) + 4u * u, y4);
             tc_wait_ld();
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const int node = 4 * u + i;
                 if (valid && node < n) {
-                    const float v = __uint_as_float(v4[i]);
+                    const float v = __uint_as_float(v4[i]) + __uint_as_float(y4[i]);
                     logits_out[grow * n + node] = v;
                     nan_local |= (v != v);
                 }

@@ -168,7 +168,8 @@ class AttentionModelPolicy(nn.Module):
             actions=acts.data_ptr(), logp=logp.data_ptr(),
             logp_all=logp_all.data_ptr() if store_all else None, reward=reward.data_ptr(),
             log_likelihood=ll.data_ptr(), lengths=lengths.data_ptr(), max_len=meta.data_ptr(),
-            err=meta.data_ptr() + 4, impl=int(cfg.get("impl", _lib.IMPL_AUTO)))
+            err=meta.data_ptr() + 4, impl=int(cfg.get("impl", _lib.IMPL_AUTO)),
+            phase_cycles=cfg["_phase_cycles"].data_ptr() if cfg.get("_phase_cycles") is not None else None)
         events = cfg.get("_events")           # bench.py: CUDA events around the kernel alone
         if events is not None:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

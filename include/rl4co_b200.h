@@ -170,6 +170,8 @@ typedef struct rl4co_rollout_args {
     int32_t* max_len;          /* out device int32: max over rows of lengths (pre-zeroed)   */
     int32_t* err;              /* device int32[2] (pre-zeroed)                              */
     int32_t impl;              /* RL4CO_IMPL_AUTO / _FP32 (CUDA cores) / _TC (tcgen05, needs tc_img) */
+    long long* phase_cycles;   /* nullable debug out, device int64[16]: clock64 cycles CTA 0 spent per phase
+                                  of the tensor-path kernel (accumulated; caller zeroes)               */
 } rl4co_rollout_args;
 
 int rl4co_rollout(const rl4co_cache* cache, const rl4co_rollout_args* args, void* stream);

@@ -1,0 +1,37 @@
+"""In-kernel phase timing of the tensor-path rollout kernel (debug counter rl4co_rollout_args.phase_cycles):
+clock64 cycles thread 0 of CTA 0 spends in each phase, accumulated over its instances and steps.
+usage (GPU box): python profiles/phase_timing.py [B]"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import eam_rl4co_b200 as P
+import bench
+
+NAMES = ["Q(0) build+sync", "wait scores(0)", "softmax(0)+sync", "issue PV(0)+Q(1) build", "wait PV(0)",
+         "drain O(0)+sync+issue scores(1)", "wait scores(1)", "softmax(1)+sync", "issue PV(1)", "wait PV(1)",
+         "drain O(1)+heads->TMEM+sync", "logits issue+wait", "select", "env step+sync", "instance prologue", "-"]
+
+def main():
+    B = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
+    dev = torch.device("cuda", 0)
+    pol = bench.make_policy().to(dev)
+    env = P.TSPEnv(generator_params=dict(num_loc=bench.N_NODES), device=dev)
+    locs = bench.make_instances(B).to(dev)
+    td = env.reset(P.TensorDict({"locs": locs}, batch_size=[B]))
+    with torch.no_grad():
+        h, _ = pol.encoder(td)
+    for it in range(3):
+        pc = torch.zeros(16, dtype=torch.int64, device=dev)
+        cfg = dict(temperature=1.0, tanh_clipping=10.0, mask_logits=True, store_all_logp=False, _phase_cycles=pc)
+        pol._forward_fused(td, env, h, "multistart_greedy", None, 10**6, False, cfg)
+        torch.cuda.synchronize()
+    c = pc.tolist()
+    n_inst = (B + 147) // 148
+    steps = n_inst * (bench.N_NODES - 1)
+    tot = sum(c)
+    print(f"CTA 0: {n_inst} instances, {steps} decode steps, {tot} cycles total, {tot / steps:.0f} cycles/step")
+    for name, v in zip(NAMES, c):
+        print(f"  {name:34s} {v / steps:9.0f} cyc/step  {100.0 * v / tot:5.1f}%")
+
+if __name__ == "__main__":
+    main()

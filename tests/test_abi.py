@@ -32,7 +32,7 @@ def test_struct_layouts_match_header():
     # 8 pointers + int64 + 3 int32 (+pad) ; see include/rl4co_b200.h
     assert C.sizeof(_lib.Cache) == 8 * 8 + 8 + 16
     assert _lib.RolloutArgs.seed.offset == 24 and _lib.RolloutArgs.inst_offset.offset == 32
-    assert C.sizeof(_lib.RolloutArgs) == 168 and _lib.RolloutArgs.err.offset == 152
+    assert C.sizeof(_lib.RolloutArgs) == 176 and _lib.RolloutArgs.err.offset == 152
     assert _lib.RolloutArgs.impl.offset == 160
 
 
