@@ -279,6 +279,15 @@ __device__ __forceinline__ void shift_mask16(uint32_t& a0, uint32_t& a1, uint32_
     a3 >>= 16;
 }
 
+#define R4_STAMP(k)                                       \
+    do {                                                  \
+        if (prof != nullptr) {                            \
+            const long long now__ = clock64();            \
+            prof[k] += now__ - tprev;                     \
+            tprev = now__;                                \
+        }                                                 \
+    } while (0)
+
 // masked max of one 16-column chunk (two chains)
 __device__ __forceinline__ void chunk_max(const uint32_t (&v)[16], uint32_t bits, float& m0, float& m1) {
 #pragma unroll
@@ -315,6 +324,47 @@ __device__ __forceinline__ void load_tail(uint32_t addr, int tq, uint32_t (&v)[1
     for (int i = 12; i < 16; ++i) v[i] = 0u;
 }
 
+// One-pass masked softmax numerator of one (row, head), in place: S (fp32, NPAD columns) -> P (fp16 hi/lo).
+// TMEM reads are the scarce resource here (~128 B/clk/SM), so S is read ONCE: chunk c is exponentiated
+// against the running row maximum m_run of the chunks seen so far.  When a chunk's masked maximum exceeds
+// m_run by more than 10 (e^10 still fits fp16), the warp takes the rare rescale path: m_run is raised and
+// the chunks already written are multiplied by e^(m_old - m_new).  Any common reference cancels in
+// heads = (P V) / rowsum(P), and P >= e^(s - m_final), so nothing is lost against the two-pass form.
+__device__ __forceinline__ void rescale_chunk(uint32_t addr, float f) {
+    uint32_t w[16];
+    tmem_ld16(addr, w);
+    tc_wait_ld();
+    uint32_t hi[8], lo[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float2 h = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+        const float2 l = __half22float2(*reinterpret_cast<const __half2*>(&w[8 + i]));
+        split2((h.x + l.x) * f, (h.y + l.y) * f, hi[i], lo[i]);
+    }
+    tmem_st8(addr, hi);
+    tmem_st8(addr + 8u, lo);
+}
+
+__device__ __forceinline__ void softmax_chunk(uint32_t sp, int ch, const uint32_t (&v)[16], uint32_t bits,
+                                              float& m_run, float& l0, float& l1) {
+    float c0 = -INFINITY, c1 = -INFINITY;
+    chunk_max(v, bits, c0, c1);
+    const float cm = fmaxf(c0, c1);
+    const bool need = cm > m_run + 10.0f;          // also the first feasible chunk of the row (m_run = -inf)
+    if (__any_sync(kFull, need)) {
+        const float f = need ? ex2_approx((m_run - cm) * 1.4426950408889634f) : 1.0f;   // -inf -> 0
+        if (need) m_run = cm;
+        l0 *= f;
+        l1 *= f;
+        for (int pc = 0; pc < ch; ++pc) rescale_chunk(sp + 16u * pc, f);
+        tc_wait_st();
+    }
+    uint32_t hi[8], lo[8];
+    chunk_exp(v, bits, m_run * 1.4426950408889634f, l0, l1, hi, lo);
+    tmem_st8(sp + 16u * ch, hi);
+    tmem_st8(sp + 16u * ch + 8u, lo);
+}
+
 __device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int row, float* dbg_scores, int n) {
     const uint32_t w0 = x.s->maskw[0][row], w1 = x.s->maskw[1][row], w2 = x.s->maskw[2][row],
                    w3 = x.s->maskw[3][row];
@@ -322,12 +372,11 @@ __device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int 
     const int lastv = n - 16 * (x.nch - 1);
     const int tq = lastv <= 12 ? (lastv + 3) >> 2 : 0;
     const int nfull = tq ? x.nch - 1 : x.nch;
-    // pass 1: masked row maximum; the next chunk's TMEM load is in flight while one is reduced
-    float m0 = -INFINITY, m1 = -INFINITY;
+    float m_run = -INFINITY, l0 = 0.f, l1 = 0.f;
     uint32_t a0 = w0, a1 = w1, a2 = w2, a3 = w3;
     uint32_t va[16], vb[16];
     if (nfull > 0) tmem_ld16(sp, va);
-    for (int ch = 0; ch < nfull; ch += 2) {
+    for (int ch = 0; ch < nfull; ch += 2) {   // the next chunk's TMEM load is in flight while one is processed
         tc_wait_ld();
         if (ch + 1 < nfull) tmem_ld16(sp + 16u * (ch + 1), vb);
         if (dbg_scores != nullptr) {
@@ -335,7 +384,7 @@ __device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int 
             for (int i = 0; i < 16; ++i)
                 if (16 * ch + i < n) dbg_scores[16 * ch + i] = __uint_as_float(va[i]);
         }
-        chunk_max(va, a0, m0, m1);
+        softmax_chunk(sp, ch, va, a0, m_run, l0, l1);
         shift_mask16(a0, a1, a2, a3);
         if (ch + 1 < nfull) {
             tc_wait_ld();
@@ -345,7 +394,7 @@ __device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int 
                 for (int i = 0; i < 16; ++i)
                     if (16 * (ch + 1) + i < n) dbg_scores[16 * (ch + 1) + i] = __uint_as_float(vb[i]);
             }
-            chunk_max(vb, a0, m0, m1);
+            softmax_chunk(sp, ch + 1, vb, a0, m_run, l0, l1);
             shift_mask16(a0, a1, a2, a3);
         }
     }
@@ -357,42 +406,7 @@ __device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int 
             for (int i = 0; i < 12; ++i)
                 if (16 * nfull + i < n) dbg_scores[16 * nfull + i] = __uint_as_float(va[i]);
         }
-        chunk_max(va, a0, m0, m1);
-    }
-    float m = fmaxf(m0, m1);
-    if (m == -INFINITY) m = 0.f;
-    const float ml = m * 1.4426950408889634f;
-    // pass 2: P = exp(S - m) on feasible nodes, split to fp16 hi/lo, stored over S
-    float l0 = 0.f, l1 = 0.f;
-    a0 = w0; a1 = w1; a2 = w2; a3 = w3;
-    if (nfull > 0) tmem_ld16(sp, va);
-    for (int ch = 0; ch < nfull; ch += 2) {
-        tc_wait_ld();
-        if (ch + 1 < nfull) tmem_ld16(sp + 16u * (ch + 1), vb);
-        {
-            uint32_t hi[8], lo[8];
-            chunk_exp(va, a0, ml, l0, l1, hi, lo);
-            tmem_st8(sp + 16u * ch, hi);
-            tmem_st8(sp + 16u * ch + 8u, lo);
-        }
-        shift_mask16(a0, a1, a2, a3);
-        if (ch + 1 < nfull) {
-            tc_wait_ld();
-            if (ch + 2 < nfull) tmem_ld16(sp + 16u * (ch + 2), va);
-            uint32_t hi[8], lo[8];
-            chunk_exp(vb, a0, ml, l0, l1, hi, lo);
-            tmem_st8(sp + 16u * (ch + 1), hi);
-            tmem_st8(sp + 16u * (ch + 1) + 8u, lo);
-            shift_mask16(a0, a1, a2, a3);
-        }
-    }
-    if (tq) {
-        load_tail(sp + 16u * nfull, tq, va);
-        tc_wait_ld();
-        uint32_t hi[8], lo[8];
-        chunk_exp(va, a0, ml, l0, l1, hi, lo);   // mask bits beyond n are 0: the padding becomes exact zeros
-        tmem_st8(sp + 16u * nfull, hi);
-        tmem_st8(sp + 16u * nfull + 8u, lo);
+        softmax_chunk(sp, nfull, va, a0, m_run, l0, l1);   // mask bits beyond n are 0: padding -> exact zeros
     }
     tc_wait_st();
     const float l = l0 + l1;
@@ -402,15 +416,6 @@ __device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int 
 // All GEMM phases of one decoder step; on return the raw logits of the instance sit in TMEM
 // columns [kColLG, kColLG + n) (row = lane).  dbg_* (nullable) receive scores [S?,8,n] / heads [.,128]
 // of this thread's row for the parity tests.
-#define R4_STAMP(k)                                       \
-    do {                                                  \
-        if (prof != nullptr) {                            \
-            const long long now__ = clock64();            \
-            prof[k] += now__ - tprev;                     \
-            tprev = now__;                                \
-        }                                                 \
-    } while (0)
-
 template <int ENV>
 __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cache& c, int64_t b, int S,
                                                   uint32_t& mma_par, float* dbg_scores_row, float* dbg_heads_row,
@@ -498,21 +503,24 @@ __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_a
     const uint32_t lg = x.tmem + ((uint32_t)(32 * q) << 16) + kColLG;
     const int U = (n + 3) >> 2;
     const int u0 = (U * j) >> 2, u1 = (U * (j + 1)) >> 2;
+    // 28 columns from 4*u0 on, both accumulators (columns past this thread's range are ignored below)
     uint32_t raw[28], raw2[28];
+    {
+        uint32_t a16[16], b16[16], a8[8], b8[8], a4[4], b4[4];
+        tmem_ld16(lg + 4u * u0, a16);
+        tmem_ld16(lg + (kColLG2 - kColLG) + 4u * u0, b16);
+        tmem_ld8(lg + 4u * u0 + 16u, a8);
+        tmem_ld8(lg + (kColLG2 - kColLG) + 4u * u0 + 16u, b8);
+        tmem_ld4(lg + 4u * u0 + 24u, a4);
+        tmem_ld4(lg + (kColLG2 - kColLG) + 4u * u0 + 24u, b4);
+        tc_wait_ld();
 #pragma unroll
-    for (int k = 0; k < 7; ++k) {
-        uint32_t v4[4] = {0u, 0u, 0u, 0u}, y4[4] = {0u, 0u, 0u, 0u};
-        if (u0 + k < u1) {
-            tmem_ld4(lg + 4u * (u0 + k), v4);
-            tmem_ld4(lg + (kColLG2 - kColLG) + 4u * (u0 + k), y4);
-        }
+        for (int i = 0; i < 16; ++i) { raw[i] = a16[i]; raw2[i] = b16[i]; }
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            raw[4 * k + i] = v4[i];
-            raw2[4 * k + i] = y4[i];
-        }
+        for (int i = 0; i < 8; ++i) { raw[16 + i] = a8[i]; raw2[16 + i] = b8[i]; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { raw[24 + i] = a4[i]; raw2[24 + i] = b4[i]; }
     }
-    tc_wait_ld();
     const uint32_t w0 = s->maskw[0][row], w1 = s->maskw[1][row], w2 = s->maskw[2][row], w3 = s->maskw[3][row];
     const int sh = 4 * u0, wi = sh >> 5;
     const uint32_t lo = wi == 0 ? w0 : (wi == 1 ? w1 : (wi == 2 ? w2 : w3));
@@ -542,22 +550,27 @@ __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_a
 #pragma unroll
         for (int e = 0; e < 28; ++e) xv[e] = xv[e] / temp;
     }
+    // local max and local sum (relative to the local max) are exchanged together: one barrier
     float lmax = -INFINITY;
 #pragma unroll
     for (int e = 0; e < 28; ++e) lmax = fmaxf(lmax, xv[e]);
     if (nan_local && valid) err_bits |= RL4CO_ERR_NAN_LOGITS;
-    s->red_a[j][row] = lmax;
-    bar_sync(1 + q, 128);
-    const float mx = fmaxf(fmaxf(s->red_a[0][row], s->red_a[1][row]), fmaxf(s->red_a[2][row], s->red_a[3][row]));
+    const float lref = (lmax == -INFINITY) ? 0.f : lmax;
     float ls0 = 0.f, ls1 = 0.f;
 #pragma unroll
     for (int e = 0; e < 28; e += 2) {                               // exp(-inf) = 0
-        ls0 += ex2_approx((xv[e] - mx) * 1.4426950408889634f);
-        ls1 += ex2_approx((xv[e + 1] - mx) * 1.4426950408889634f);
+        ls0 += ex2_approx((xv[e] - lref) * 1.4426950408889634f);
+        ls1 += ex2_approx((xv[e + 1] - lref) * 1.4426950408889634f);
     }
+    s->red_a[j][row] = lmax;
     s->red_b[j][row] = ls0 + ls1;
     bar_sync(1 + q, 128);
-    const float logsum = logf(((s->red_b[0][row] + s->red_b[1][row]) + s->red_b[2][row]) + s->red_b[3][row]);
+    const float r0 = s->red_a[0][row], r1 = s->red_a[1][row], r2 = s->red_a[2][row], r3 = s->red_a[3][row];
+    const float mx = fmaxf(fmaxf(r0, r1), fmaxf(r2, r3));
+    const float kL2e = 1.4426950408889634f;
+    const float tot = ((s->red_b[0][row] * ex2_approx((r0 - mx) * kL2e) + s->red_b[1][row] * ex2_approx((r1 - mx) * kL2e)) +
+                       s->red_b[2][row] * ex2_approx((r2 - mx) * kL2e)) + s->red_b[3][row] * ex2_approx((r3 - mx) * kL2e);
+    const float logsum = logf(tot);
 #pragma unroll
     for (int e = 0; e < 28; ++e) xv[e] = (xv[e] - mx) - logsum;     // log_softmax :190 (xv now holds logp)
     if (a.logp_all != nullptr && valid) {

@@ -86,6 +86,27 @@ def test_tc_decode_step_stages(env_name, N, B, steps):
     assert e_lg < LOGIT_ATOL and e_32 < LOGIT_ATOL, (e_lg, e_32)
 
 
+@pytest.mark.parametrize("env_name,N,B", [("tsp", 100, 2), ("cvrp", 50, 2)])
+def test_tc_peaky_attention_takes_the_rescale_path(env_name, N, B):
+    """Glimpse keys scaled x12: attention scores spread over tens of units, so the one-pass softmax must raise
+    its running maximum (and rescale the chunks already written) many times.  Same answers as the fp32 kernel."""
+    inst, pol, w, env, td, h = _setup(env_name, N, B, seed=7)
+    with torch.no_grad():
+        pol.decoder.project_node_embeddings.weight[:128].mul_(12.0)
+    td, cache, num_starts = _mid_rollout_state(pol, env, td.clone(), h, N, 5)
+    dbg = {}
+    lg_tc, _ = pol.decoder(td, cache, num_starts, impl=_lib.IMPL_TC, debug=dbg)
+    lg_32, _ = pol.decoder(td, cache, num_starts, impl=_lib.IMPL_FP32)
+    sc_ref, hd_ref, lg_ref = _torch_stages(env_name, cache, td, B, N)
+    spread = (sc_ref.max() - sc_ref.min()).item()
+    e_hd = (dbg["heads"] - hd_ref).abs().max().item()
+    e_lg = (lg_tc - lg_ref).abs().max().item()
+    print(f"{env_name}{N} peaky: score spread={spread:.1f} |dheads|={e_hd:.2e} |dlogit|={e_lg:.2e} "
+          f"vs fp32 kernel={(lg_tc - lg_32).abs().max().item():.2e}")
+    assert spread > 30
+    assert e_hd < 5e-5 and e_lg < 5e-5
+
+
 @pytest.mark.parametrize("env_name,N,B", [("tsp", 20, 5), ("tsp", 100, 3), ("cvrp", 20, 5), ("cvrp", 100, 3)])
 @pytest.mark.parametrize("decode_type", ["multistart_greedy", "multistart_sampling"])
 def test_tc_rollout_matches_fp32_rollout_and_oracle(env_name, N, B, decode_type):
