@@ -288,24 +288,29 @@ __device__ __forceinline__ void shift_mask16(uint32_t& a0, uint32_t& a1, uint32_
         }                                                 \
     } while (0)
 
-// masked max of one 16-column chunk (two chains)
-__device__ __forceinline__ void chunk_max(const uint32_t (&v)[16], uint32_t bits, float& m0, float& m1) {
+// scores of one 16-column chunk with the infeasible nodes set to -inf (attention.py:308-322): one select
+// per element serves both the running maximum and the exponent (exp(-inf) = 0 exactly)
+__device__ __forceinline__ void chunk_mask(const uint32_t (&v)[16], uint32_t bits, float (&sv)[16]) {
 #pragma unroll
-    for (int i = 0; i < 16; i += 2) {
-        if (bits & (1u << i)) m0 = fmaxf(m0, __uint_as_float(v[i]));
-        if (bits & (2u << i)) m1 = fmaxf(m1, __uint_as_float(v[i + 1]));
+    for (int i = 0; i < 16; ++i) sv[i] = (bits & (1u << i)) ? __uint_as_float(v[i]) : -INFINITY;
+}
+__device__ __forceinline__ float chunk_max(const float (&sv)[16]) {
+    float m0 = fmaxf(sv[0], sv[1]), m1 = fmaxf(sv[2], sv[3]);
+#pragma unroll
+    for (int i = 4; i < 16; i += 2) {
+        m0 = fmaxf(m0, sv[i]);
+        m1 = fmaxf(m1, sv[i + 1]);
     }
+    return fmaxf(m0, m1);
 }
 // P of one 16-column chunk -> fp16 hi/lo words, row sums in two chains
-__device__ __forceinline__ void chunk_exp(const uint32_t (&v)[16], uint32_t bits, float ml, float& l0, float& l1,
+__device__ __forceinline__ void chunk_exp(const float (&sv)[16], float ml, float& l0, float& l1,
                                           uint32_t (&hi)[8], uint32_t (&lo)[8]) {
     const float kLog2e = 1.4426950408889634f;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        float p0 = ex2_approx(fmaf(__uint_as_float(v[2 * i]), kLog2e, -ml));
-        float p1 = ex2_approx(fmaf(__uint_as_float(v[2 * i + 1]), kLog2e, -ml));
-        p0 = (bits & (1u << (2 * i))) ? p0 : 0.f;
-        p1 = (bits & (2u << (2 * i))) ? p1 : 0.f;
+        const float p0 = ex2_approx(fmaf(sv[2 * i], kLog2e, -ml));
+        const float p1 = ex2_approx(fmaf(sv[2 * i + 1], kLog2e, -ml));
         l0 += p0;
         l1 += p1;
         split2(p0, p1, hi[i], lo[i]);
@@ -347,9 +352,9 @@ __device__ __forceinline__ void rescale_chunk(uint32_t addr, float f) {
 
 __device__ __forceinline__ void softmax_chunk(uint32_t sp, int ch, const uint32_t (&v)[16], uint32_t bits,
                                               float& m_run, float& l0, float& l1) {
-    float c0 = -INFINITY, c1 = -INFINITY;
-    chunk_max(v, bits, c0, c1);
-    const float cm = fmaxf(c0, c1);
+    float sv[16];
+    chunk_mask(v, bits, sv);
+    const float cm = chunk_max(sv);
     const bool need = cm > m_run + 10.0f;          // also the first feasible chunk of the row (m_run = -inf)
     if (__any_sync(kFull, need)) {
         const float f = need ? ex2_approx((m_run - cm) * 1.4426950408889634f) : 1.0f;   // -inf -> 0
@@ -360,7 +365,8 @@ __device__ __forceinline__ void softmax_chunk(uint32_t sp, int ch, const uint32_
         tc_wait_st();
     }
     uint32_t hi[8], lo[8];
-    chunk_exp(v, bits, m_run * 1.4426950408889634f, l0, l1, hi, lo);
+    // a row with no feasible node so far has m_run = -inf: reference 0 keeps exp(-inf - ref) = 0, not NaN
+    chunk_exp(sv, (m_run == -INFINITY ? 0.f : m_run) * 1.4426950408889634f, l0, l1, hi, lo);
     tmem_st8(sp + 16u * ch, hi);
     tmem_st8(sp + 16u * ch + 8u, lo);
 }

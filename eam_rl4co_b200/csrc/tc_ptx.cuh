@@ -35,10 +35,9 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 // Bounded wait: a copy or MMA that never completes (bad descriptor) traps instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    if (mbar_try_wait(bar, parity)) return;
-    const long long t0 = clock64();
-    while (!mbar_try_wait(bar, parity)) {
-        if (clock64() - t0 > 4000000000LL) __trap();
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {      // try_wait itself suspends the thread for a while
+        if (++spins > (1u << 24)) __trap();
     }
 }
 // TMA 1-D bulk copy global -> shared, completion counted on an mbarrier (SASS: UBLKCP)

@@ -66,7 +66,14 @@ class Normalization(nn.Module):
     def forward(self, x):
         if isinstance(self.normalizer, nn.BatchNorm1d):
             return self.normalizer(x.reshape(-1, x.size(-1))).view(*x.size())
-        return self.normalizer(x.permute(0, 2, 1)).permute(0, 2, 1)
+        # nn/ops.py:48-49: InstanceNorm1d over the node axis of [B, N, E].  Same statistics (biased variance,
+        # eps inside the sqrt, affine), computed in place on the [B, N, E] layout: the permute -> cuDNN
+        # batch-norm route of nn.InstanceNorm1d costs ~1 ms per call at B=1024 on a B200, 12 calls per encode.
+        nrm = self.normalizer
+        mean = x.mean(dim=1, keepdim=True)
+        xc = x - mean
+        var = (xc * xc).mean(dim=1, keepdim=True)
+        return xc * torch.rsqrt(var + nrm.eps) * nrm.weight + nrm.bias
 
 
 class MLP(nn.Module):
