@@ -7,7 +7,8 @@ instances are independent, each rank rolls out its own shard, no data-path colle
 One "step" = one full rollout of the batch = B*S rows x T=100 actions = 1.024e7 instance-steps.
 
   value : whole-job instance-steps/s, inputs (encoder output h, locs, weights) resident in HBM;
-          timed region = cache precompute GEMMs + the persistent rollout kernel, per step.
+          timed region = cache precompute GEMMs + operand pack kernel + the persistent tcgen05 rollout
+          kernel, per step.
   e2e   : the same metric through the public API `policy(td, env, decode_type=...)` with HOST buffers:
           pinned host locs -> H2D -> env.reset -> encoder -> rollout -> D2H of reward / log_likelihood /
           actions, every step.
@@ -42,13 +43,21 @@ WORKLOAD = "TSP100 POMO multistart greedy, S=100, B=1024 per GPU, random-init we
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=B_PER_GPU, help="instances per GPU")
     ap.add_argument("--cpu-sample", type=int, default=16, help="instances in the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
+
+
+def measured_traffic():
+    """DRAM bytes per launch of the rollout kernel from the committed `ncu --set full` capture."""
+    p = os.path.join(ROOT, "profiles", "r01_rollout_tc_traffic.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get("dram_bytes_per_launch")
+    return None
 
 
 def peaks():
@@ -70,7 +79,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:  # noqa: BLE001
             self.proc = None
@@ -206,7 +215,6 @@ def run_b200(args):
     barrier()
     ms_total = t0.elapsed_time(t1)
     kernel_ms = [a.elapsed_time(b) for a, b in events]
-    clocks = sampler.stop()
 
     # ---- e2e: public API, host buffers, H2D + D2H inside the timed region --------------------
     out_host = {"reward": torch.empty(rows, dtype=torch.float32).pin_memory(),
@@ -234,6 +242,7 @@ def run_b200(args):
     e1.record()
     barrier()
     e2e_ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()          # sampled over both timed regions (device-resident and end-to-end)
 
     if world > 1:
         t = torch.tensor([ms_total, e2e_ms, max(kernel_ms)], device=dev, dtype=torch.float64)
@@ -251,19 +260,21 @@ def run_b200(args):
                        "nodes": N_NODES, "decode_type": "multistart_greedy", "parallelism": f"dp{world}",
                        "instance_steps_per_step_per_gpu": isteps,
                        "l2": "inputs larger than L2 (tables 262 MB + outputs 123 MB per step)",
-                       "timed": "cache precompute GEMMs + persistent rollout kernel"},
+                       "timed": "cache precompute GEMMs + operand pack + persistent tcgen05 rollout kernel"},
             "e2e": {"value": world * isteps * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / K,
                     "includes": "H2D locs, env.reset, encoder (torch), cache precompute, rollout kernel, "
                                 "D2H reward+log_likelihood+actions"},
-            "gpu_launches": len(kernel_ms),
+            "gpu_launches": 2 * len(kernel_ms),      # per step: r4::tc::tc_pack_kernel + r4::tc::rollout_tc_kernel
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "kernel": "rollout_smem_kernel<TSP>", "kernel_ms": k_ms,
+                         "frac": achieved / peak, "traffic": measured_traffic(), "peak_source": peak_src,
+                         "kernel": "r4::tc::rollout_tc_kernel<TSP>", "kernel_ms": k_ms,
                          "algorithmic_bytes_per_launch": ALGO_BYTES_PER_INSTANCE_STEP * isteps,
                          "note": "algorithmic bytes per SURVEY.md §8(d) (K,V,L re-read every step); the "
-                                 "kernel keeps them in shared memory, so DRAM traffic is far lower and the "
-                                 "binding resource is on-chip (see DESIGN.md, profiles/)"},
+                                 "kernel keeps the operand tiles in shared memory for the whole rollout, so "
+                                 "DRAM traffic (`traffic`, ncu) is ~60x lower and the binding resources are "
+                                 "on-chip: CUDA-core issue + MUFU for the softmax/selection around the "
+                                 "tcgen05 MMAs (DESIGN.md, profiles/)"},
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:
