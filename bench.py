@@ -244,13 +244,12 @@ def run_b200(args):
     e2e_ms = e0.elapsed_time(e1)
     clocks = sampler.stop()          # sampled over both timed regions (device-resident and end-to-end)
 
-    if world > 1:
-        t = torch.tensor([ms_total, e2e_ms, max(kernel_ms)], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)      # max over ranks, device-timed
-        ms_total, e2e_ms = t[0].item(), t[1].item()
+    from eam_rl4co_b200 import sharding
+    k_mean = statistics.mean(kernel_ms)
+    ms_total, e2e_ms, k_mean = sharding.max_over_ranks([ms_total, e2e_ms, k_mean], device=dev)   # device-timed, MAX
     if rank == 0:
         peak, peak_src = peaks()
-        k_ms = statistics.mean(kernel_ms)
+        k_ms = k_mean
         achieved = ALGO_BYTES_PER_INSTANCE_STEP * isteps / (k_ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": world * isteps * K / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,

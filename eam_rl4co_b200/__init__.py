@@ -13,6 +13,7 @@ from .decoding import (DecodingStrategy, Greedy, Sampling, Evaluate, get_decodin
                        get_log_likelihood, calculate_entropy)
 from .encoder import AttentionModelEncoder
 from .policy import AttentionModelPolicy
+from . import sharding
 
 
 def POMOPolicy(env_name: str = "tsp", **kw) -> AttentionModelPolicy:
