@@ -309,8 +309,13 @@ __device__ __forceinline__ void chunk_exp(const float (&sv)[16], float ml, float
     const float kLog2e = 1.4426950408889634f;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
+#ifdef R4_X_NOMUFU
+        const float p0 = fmaf(fmaf(sv[2 * i], kLog2e, -ml), 1e-3f, 0.5f);
+        const float p1 = fmaf(fmaf(sv[2 * i + 1], kLog2e, -ml), 1e-3f, 0.5f);
+#else
         const float p0 = ex2_approx(fmaf(sv[2 * i], kLog2e, -ml));
         const float p1 = ex2_approx(fmaf(sv[2 * i + 1], kLog2e, -ml));
+#endif
         l0 += p0;
         l1 += p1;
         split2(p0, p1, hi[i], lo[i]);
@@ -356,7 +361,12 @@ __device__ __forceinline__ void softmax_chunk(uint32_t sp, int ch, const uint32_
     chunk_mask(v, bits, sv);
     const float cm = chunk_max(sv);
     const bool need = cm > m_run + 10.0f;          // also the first feasible chunk of the row (m_run = -inf)
+#ifdef R4_X_NOVOTE
+    if (ch == 0) m_run = cm;
+    if (false) {
+#else
     if (__any_sync(kFull, need)) {
+#endif
         const float f = need ? ex2_approx((m_run - cm) * 1.4426950408889634f) : 1.0f;   // -inf -> 0
         if (need) m_run = cm;
         l0 *= f;
@@ -367,8 +377,15 @@ __device__ __forceinline__ void softmax_chunk(uint32_t sp, int ch, const uint32_
     uint32_t hi[8], lo[8];
     // a row with no feasible node so far has m_run = -inf: reference 0 keeps exp(-inf - ref) = 0, not NaN
     chunk_exp(sv, (m_run == -INFINITY ? 0.f : m_run) * 1.4426950408889634f, l0, l1, hi, lo);
+#ifdef R4_X_NOST
+    if (l0 == 12345.f) {
+        tmem_st8(sp + 16u * ch, hi);
+        tmem_st8(sp + 16u * ch + 8u, lo);
+    }
+#else
     tmem_st8(sp + 16u * ch, hi);
     tmem_st8(sp + 16u * ch + 8u, lo);
+#endif
 }
 
 __device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int row, float* dbg_scores, int n) {
@@ -501,7 +518,26 @@ __device__ __forceinline__ float tanh_fast(float v) {
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(e2 + 1.0f));
     return fmaf(-2.0f, r, 1.0f);
 }
+// |v| <= 1: tanh(v) = v R(v^2), R of degree 6 (weighted least squares on Chebyshev nodes; absolute error
+// 1.1e-7 evaluated in fp32).  Eight FMA-pipe instructions and no MUFU: the selection phase is MUFU-bound
+// otherwise (ex2 + rcp for the tanh and ex2 for the softmax at 8 cycles per warp-instruction each).
+__device__ __forceinline__ float tanh_small(float v) {
+    const float u = v * v;
+    float r = 9.568327223e-04f;
+    r = fmaf(r, u, -5.928727333e-03f);
+    r = fmaf(r, u, 1.994509064e-02f);
+    r = fmaf(r, u, -5.324891955e-02f);
+    r = fmaf(r, u, 1.331909001e-01f);
+    r = fmaf(r, u, -3.333206773e-01f);
+    r = fmaf(r, u, 9.999996424e-01f);
+    return v * r;
+}
 
+// log_softmax needs log sum_e exp(x_e - ref) for ANY ref >= max_e x_e that keeps the sum a normal float.  With
+// tanh clipping (decoding.py:171-172) x = clip * tanh(.) / temperature <= clip / temperature, so ref is a
+// constant and the row needs no max exchange: greedy / evaluate take ONE 128-thread barrier per step.  Without
+// clipping the row maximum is exchanged first.  Greedy takes the argmax over x itself (log_softmax is monotone;
+// first index on exact ties as torch.argmax).
 __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_args& a, int n, int q, int j,
                                              int row, bool valid, int64_t grow, int t, int T, uint32_t nkey,
                                              int given, int& err_bits) {
@@ -536,100 +572,127 @@ __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_a
     const uint32_t win = __funnelshift_r(lo, hi, sh & 31) & inrange;  // feasible bits of nodes sh .. sh+27
 
     // every run-time-uniform option is hoisted out of the unrolled element loops: the loops stay
-    // branch-free so that the 28 independent MUFU / FMA chains of a thread overlap
-    float xv[28];
-    bool nan_local = false;
+    // branch-free so that the 28 independent chains of a thread overlap
+    const bool clipped = a.tanh_clipping > 0.f;                     // decoding.py:171-172
+    const float sc = (clipped ? a.tanh_clipping : 1.0f) / a.temperature;   // :179 folded into the clip scale
+    const float kL2e = 1.4426950408889634f;
+    float tv[28];                                                   // tanh(logit) (or the logit), -inf if infeasible
 #pragma unroll
-    for (int e = 0; e < 28; ++e) {
-        xv[e] = __uint_as_float(raw[e]) + __uint_as_float(raw2[e]);
-        nan_local |= ((win >> e) & 1u) && (xv[e] != xv[e]);         // attention.py:303-304
+    for (int e = 0; e < 28; ++e) tv[e] = __uint_as_float(raw[e]) + __uint_as_float(raw2[e]);
+    if (clipped) {
+        float am0 = 0.f, am1 = 0.f;
+#pragma unroll
+        for (int e = 0; e < 28; e += 2) {
+            am0 = fmaxf(am0, fabsf(tv[e]));
+            am1 = fmaxf(am1, fabsf(tv[e + 1]));
+        }
+        if (__all_sync(kFull, fmaxf(am0, am1) <= 1.0f)) {           // NaN fails the test -> MUFU path propagates it
+#pragma unroll
+            for (int e = 0; e < 28; ++e) tv[e] = tanh_small(tv[e]);
+        } else {
+#pragma unroll
+            for (int e = 0; e < 28; ++e) tv[e] = tanh_fast(tv[e]);
+        }
     }
-    if (a.tanh_clipping > 0.f) {                                    // decoding.py:171-172
-        const float clip = a.tanh_clipping;
 #pragma unroll
-        for (int e = 0; e < 28; ++e) xv[e] = tanh_fast(xv[e]) * clip;
+    for (int e = 0; e < 28; ++e) tv[e] = ((win >> e) & 1u) ? tv[e] : -INFINITY;   // :177
+
+    float ref;                                                      // >= every x of the row
+    if (clipped) {
+        ref = sc;
+    } else {
+        float lmax = -INFINITY;
+#pragma unroll
+        for (int e = 0; e < 28; ++e) lmax = fmaxf(lmax, tv[e]);
+        s->red_a[j][row] = lmax;
+        bar_sync(1 + q, 128);
+        const float m = fmaxf(fmaxf(s->red_a[0][row], s->red_a[1][row]), fmaxf(s->red_a[2][row], s->red_a[3][row]));
+        ref = (m == -INFINITY) ? 0.f : m * sc;
     }
-#pragma unroll
-    for (int e = 0; e < 28; ++e) xv[e] = ((win >> e) & 1u) ? xv[e] : -INFINITY;   // :177
-    if (a.temperature != 1.0f) {                                    // :179
-        const float temp = a.temperature;
-#pragma unroll
-        for (int e = 0; e < 28; ++e) xv[e] = xv[e] / temp;
-    }
-    // local max and local sum (relative to the local max) are exchanged together: one barrier
-    float lmax = -INFINITY;
-#pragma unroll
-    for (int e = 0; e < 28; ++e) lmax = fmaxf(lmax, xv[e]);
-    if (nan_local && valid) err_bits |= RL4CO_ERR_NAN_LOGITS;
-    const float lref = (lmax == -INFINITY) ? 0.f : lmax;
+    // sum_e exp(x_e - ref), x_e = sc * tv_e: one FFMA + MUFU + FADD per element (exp(-inf) = 0)
+    const float c1 = sc * kL2e, c0 = -ref * kL2e;
     float ls0 = 0.f, ls1 = 0.f;
 #pragma unroll
-    for (int e = 0; e < 28; e += 2) {                               // exp(-inf) = 0
-        ls0 += ex2_approx((xv[e] - lref) * 1.4426950408889634f);
-        ls1 += ex2_approx((xv[e + 1] - lref) * 1.4426950408889634f);
+    for (int e = 0; e < 28; e += 2) {
+        ls0 += ex2_approx(fmaf(tv[e], c1, c0));
+        ls1 += ex2_approx(fmaf(tv[e + 1], c1, c0));
     }
-    s->red_a[j][row] = lmax;
     s->red_b[j][row] = ls0 + ls1;
-    bar_sync(1 + q, 128);
-    const float r0 = s->red_a[0][row], r1 = s->red_a[1][row], r2 = s->red_a[2][row], r3 = s->red_a[3][row];
-    const float mx = fmaxf(fmaxf(r0, r1), fmaxf(r2, r3));
-    const float kL2e = 1.4426950408889634f;
-    const float tot = ((s->red_b[0][row] * ex2_approx((r0 - mx) * kL2e) + s->red_b[1][row] * ex2_approx((r1 - mx) * kL2e)) +
-                       s->red_b[2][row] * ex2_approx((r2 - mx) * kL2e)) + s->red_b[3][row] * ex2_approx((r3 - mx) * kL2e);
-    const float logsum = logf(tot);
+
+    float best = -INFINITY, best_x = -INFINITY;
+    int best_i = 0x7fffffff;
+    const bool sampling = a.mode == RL4CO_MODE_SAMPLING;
+    if (a.mode == RL4CO_MODE_EVALUATE) {
 #pragma unroll
-    for (int e = 0; e < 28; ++e) xv[e] = (xv[e] - mx) - logsum;     // log_softmax :190 (xv now holds logp)
+        for (int e = 0; e < 28; ++e) {
+            if (e < cnt && sh + e == given) {
+                best = 0.f;
+                best_i = given;
+                best_x = tv[e];
+            }
+        }
+    } else if (!sampling) {
+#pragma unroll
+        for (int e = 0; e < 28; ++e) {
+            if (tv[e] > best) {   // ascending node order + strict > = first max index (torch.argmax)
+                best = tv[e];
+                best_i = sh + e;
+            }
+        }
+        best_x = best;
+    }
+    if (!sampling) {
+        s->red_c[j][row] = best;
+        s->red_i[j][row] = best_i;
+        s->red_lp[j][row] = best_x;
+    }
+    bar_sync(1 + q, 128);
+    const float tot = (s->red_b[0][row] + s->red_b[1][row]) + (s->red_b[2][row] + s->red_b[3][row]);
+    if (tot != tot && valid) err_bits |= RL4CO_ERR_NAN_LOGITS;      // attention.py:303-304 (a feasible logit is NaN)
+    const float lse = logf(tot);                                    // log_softmax(x)_e = (x_e - ref) - lse  :190
     if (a.logp_all != nullptr && valid) {
 #pragma unroll
         for (int e = 0; e < 28; ++e)
-            if (e < cnt && sh + e < n) a.logp_all[(grow * T + t) * (int64_t)n + sh + e] = xv[e];
+            if (e < cnt && sh + e < n) a.logp_all[(grow * T + t) * (int64_t)n + sh + e] = (tv[e] * sc - ref) - lse;
     }
-    float cand[28];
-    if (a.mode == RL4CO_MODE_SAMPLING) {
-        if (a.gumbel != nullptr) {
+    if (sampling) {
+        // Gumbel-max over logp + g (decoding.py:403-420 restated with supplied noise)
 #pragma unroll
-            for (int e = 0; e < 28; ++e)
-                cand[e] = ((win >> e) & 1u) ? xv[e] + a.gumbel[(grow * T + t) * (int64_t)n + sh + e] : xv[e];
-        } else {
-#pragma unroll
-            for (int e = 0; e < 28; ++e) cand[e] = xv[e] + noise_gumbel(nkey, sh + e);   // -inf stays -inf
+        for (int e = 0; e < 28; ++e) {
+            const float lp = (tv[e] * sc - ref) - lse;              // -inf stays -inf
+            float g = 0.f;
+            if (a.gumbel != nullptr) {
+                if ((win >> e) & 1u) g = a.gumbel[(grow * T + t) * (int64_t)n + sh + e];
+            } else {
+                g = noise_gumbel(nkey, sh + e);
+            }
+            const float cand = lp + g;
+            if (cand > best) {
+                best = cand;
+                best_i = sh + e;
+                best_x = tv[e];
+            }
         }
-    } else if (a.mode == RL4CO_MODE_EVALUATE) {
-#pragma unroll
-        for (int e = 0; e < 28; ++e) cand[e] = (e < cnt && sh + e == given) ? 0.f : -INFINITY;
-    } else {
-#pragma unroll
-        for (int e = 0; e < 28; ++e) cand[e] = xv[e];
+        s->red_c[j][row] = best;
+        s->red_i[j][row] = best_i;
+        s->red_lp[j][row] = best_x;
+        bar_sync(1 + q, 128);
     }
-    float best = -INFINITY, best_lp = -INFINITY;
-    int best_i = 0x7fffffff;
-#pragma unroll
-    for (int e = 0; e < 28; ++e) {
-        if (cand[e] > best) {  // ascending node order + strict > = first max index (torch.argmax)
-            best = cand[e];
-            best_i = sh + e;
-            best_lp = xv[e];
-        }
-    }
-    s->red_c[j][row] = best;
-    s->red_i[j][row] = best_i;
-    s->red_lp[j][row] = best_lp;
-    bar_sync(1 + q, 128);
     float fb = s->red_c[0][row];
     int fi = s->red_i[0][row];
-    float flp = s->red_lp[0][row];
+    float fx = s->red_lp[0][row];
 #pragma unroll
     for (int jj = 1; jj < 4; ++jj) {
         const float cb = s->red_c[jj][row];
         if (cb > fb) {
             fb = cb;
             fi = s->red_i[jj][row];
-            flp = s->red_lp[jj][row];
+            fx = s->red_lp[jj][row];
         }
     }
     RowSel sel;
     sel.action = (fi == 0x7fffffff) ? 0 : fi;
-    sel.logp = flp;
+    sel.logp = (fx * sc - ref) - lse;
     if (valid && j == 0) {
         const uint32_t ww = (sel.action >> 5) == 0 ? w0 : ((sel.action >> 5) == 1 ? w1 : ((sel.action >> 5) == 2 ? w2 : w3));
         if (a.mode != RL4CO_MODE_EVALUATE && !((ww >> (sel.action & 31)) & 1u)) err_bits |= RL4CO_ERR_INFEASIBLE;

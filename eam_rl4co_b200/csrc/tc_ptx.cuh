@@ -146,12 +146,19 @@ __device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[8])
 // ---- fp32 -> (fp16 hi, fp16 lo) split, two values at a time ---------------------------------------
 // x = hi + lo up to 2^-22 |x| (or 2^-25 absolute, fp16 subnormal spacing); three products
 // hi*hi + hi*lo + lo*hi then reproduce an fp32 product to ~2^-22 relative.
+// The residual x - float(hi) is one mixed-precision add per value (sm_100 `add.f32.f16` -> FHADD; the negation
+// folds into the operand), so a pair costs 4 instructions: F2FP, 2 x FHADD, F2FP.
 __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
-    const __half2 h = __floats2half2_rn(a, b);
-    const float2 f = __half22float2(h);
-    const __half2 l = __floats2half2_rn(a - f.x, b - f.y);
-    hi = *reinterpret_cast<const uint32_t*>(&h);
-    lo = *reinterpret_cast<const uint32_t*>(&l);
+    asm("{\n\t.reg .b16 h0, h1;\n\t.reg .f32 d0, d1;\n\t"
+        "cvt.rn.f16x2.f32 %0, %3, %2;\n\t"
+        "mov.b32 {h0, h1}, %0;\n\t"
+        "neg.f16 h0, h0;\n\t"
+        "neg.f16 h1, h1;\n\t"
+        "add.rn.f32.f16 d0, h0, %2;\n\t"
+        "add.rn.f32.f16 d1, h1, %3;\n\t"
+        "cvt.rn.f16x2.f32 %1, d1, d0;\n\t}"
+        : "=&r"(hi), "=r"(lo)
+        : "f"(a), "f"(b));
 }
 
 __device__ __forceinline__ float ex2_approx(float x) {

@@ -23,7 +23,10 @@ def main():
     for it in range(3):
         pc = torch.zeros(16, dtype=torch.int64, device=dev)
         cfg = dict(temperature=1.0, tanh_clipping=10.0, mask_logits=True, store_all_logp=False, _phase_cycles=pc)
-        pol._forward_fused(td, env, h, "multistart_greedy", None, 10**6, False, cfg)
+        try:
+            pol._forward_fused(td, env, h, "multistart_greedy", None, 10**6, False, cfg)
+        except AssertionError as e:     # experiment builds with broken numerics still time correctly
+            print("assertion:", str(e)[:80])
         torch.cuda.synchronize()
     c = pc.tolist()
     n_inst = (B + 147) // 148
