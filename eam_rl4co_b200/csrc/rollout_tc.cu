@@ -64,17 +64,34 @@ struct Smem {
     uint32_t pad_;
 };
 
+// Shared-memory map: [Smem][Q hi][Q lo][K_hi][K_lo][L_hi][L_lo][Vt_hi][Vt_lo].  Everything but the tile size is a
+// compile-time offset from the dynamic shared-memory base, so the context costs three registers.
+constexpr uint32_t kOffQ = (uint32_t)((sizeof(Smem) + 127) / 128 * 128);
+constexpr uint32_t kOffTiles = kOffQ + 2u * kQTileBytes;
+
 struct Ctx {
-    uint32_t k_hi, k_lo, l_hi, l_lo, v_hi, v_lo, q_hi, q_lo;  // shared-window addresses of the tiles
-    unsigned char* q_hi_p;
-    unsigned char* q_lo_p;
-    Smem* s;
+    unsigned char* smem;
     uint32_t tmem;
-    int npad, nch;
-    uint32_t sbo_v;
+    int npad;
+    __device__ __forceinline__ Smem* s() const { return reinterpret_cast<Smem*>(smem); }
+    __device__ __forceinline__ unsigned char* q_hi_p() const { return smem + kOffQ; }
+    __device__ __forceinline__ unsigned char* q_lo_p() const { return smem + kOffQ + kQTileBytes; }
+    __device__ __forceinline__ unsigned char* tiles_p() const { return smem + kOffTiles; }
+    __device__ __forceinline__ uint32_t base() const { return smem_u32(smem); }
+    __device__ __forceinline__ uint32_t q_hi() const { return base() + kOffQ; }
+    __device__ __forceinline__ uint32_t q_lo() const { return base() + kOffQ + kQTileBytes; }
+    __device__ __forceinline__ uint32_t tile(int i) const { return base() + kOffTiles + (uint32_t)i * tile_bytes(npad); }
+    __device__ __forceinline__ uint32_t k_hi() const { return tile(0); }
+    __device__ __forceinline__ uint32_t k_lo() const { return tile(1); }
+    __device__ __forceinline__ uint32_t l_hi() const { return tile(2); }
+    __device__ __forceinline__ uint32_t l_lo() const { return tile(3); }
+    __device__ __forceinline__ uint32_t v_hi() const { return tile(4); }
+    __device__ __forceinline__ uint32_t v_lo() const { return tile(5); }
+    __device__ __forceinline__ int nch() const { return npad >> 4; }
+    __device__ __forceinline__ uint32_t sbo_v() const { return (uint32_t)npad * 16u; }
 };
 
-__host__ inline size_t smem_bytes(int npad) { return 6ull * tile_bytes(npad) + 2ull * kQTileBytes + sizeof(Smem); }
+__host__ inline size_t smem_bytes(int npad) { return (size_t)kOffTiles + 6ull * tile_bytes(npad); }
 
 // ---- operand image: fp32 cache tables -> fp16 hi/lo tiles in UMMA layout ------------------------------
 // image of instance b = [K_hi][K_lo][L_hi][L_lo][Vt_hi][Vt_lo], each npad*256 bytes:
@@ -170,9 +187,9 @@ __device__ __forceinline__ void build_q(const Ctx& x, const rl4co_cache& c, int6
         qb[it] = qa[it];
         rem[it] = 0.f;
         if (r < S) {
-            qb[it] = ld4(c.pb + (base + x.s->cur[r]) * kE + choff);
-            if (ENV == RL4CO_ENV_TSP) qa[it] = ld4(c.pa + (base + x.s->first[r]) * kE + choff);
-            else rem[it] = x.s->rem[r];
+            qb[it] = ld4(c.pb + (base + x.s()->cur[r]) * kE + choff);
+            if (ENV == RL4CO_ENV_TSP) qa[it] = ld4(c.pa + (base + x.s()->first[r]) * kE + choff);
+            else rem[it] = x.s()->rem[r];
         }
     }
     float4 wc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -180,7 +197,8 @@ __device__ __forceinline__ void build_q(const Ctx& x, const rl4co_cache& c, int6
 #pragma unroll
     for (int it = 0; it < ITERS; ++it) {
         const int r = 2 * (w + NW * it) + half;
-        if (r < S) {
+        if (r < kRows) {
+            // rows >= S: qa = qb = 0 -> zeros (the Q region doubles as the head stash, so they are rewritten)
             float4 q;
             if (ENV == RL4CO_ENV_TSP)
                 q = make_float4(qa[it].x + qb[it].x, qa[it].y + qb[it].y, qa[it].z + qb[it].z, qa[it].w + qb[it].w);
@@ -192,15 +210,15 @@ __device__ __forceinline__ void build_q(const Ctx& x, const rl4co_cache& c, int6
             split2(q.z, q.w, h1, l1);
             const uint32_t off = (uint32_t)(r >> 3) * kSBO_Q + (uint32_t)(l16 >> 1) * kLBO_Q +
                                  (uint32_t)(r & 7) * 16u + (uint32_t)(l16 & 1) * 8u;
-            *reinterpret_cast<uint2*>(x.q_hi_p + off) = make_uint2(h0, h1);
-            *reinterpret_cast<uint2*>(x.q_lo_p + off) = make_uint2(l0, l1);
+            *reinterpret_cast<uint2*>(x.q_hi_p() + off) = make_uint2(h0, h1);
+            *reinterpret_cast<uint2*>(x.q_lo_p() + off) = make_uint2(l0, l1);
         }
     }
     fence_proxy_async();
 }
 
 __device__ __forceinline__ void wait_mma(const Ctx& x, uint32_t& par) {
-    mbar_wait(&x.s->mma_bar, par);
+    mbar_wait(&x.s()->mma_bar, par);
     par ^= 1u;
     tc_fence_after();
 }
@@ -215,15 +233,15 @@ __device__ __forceinline__ void issue_scores(const Ctx& x, int g, int hg) {
     tc_fence_after();
     const uint32_t id = idesc_f16(kRows, x.npad);
     const int h = 4 * g + hg;
-    const uint64_t aq_hi = smem_desc(x.q_hi + 2u * hg * kLBO_Q, kLBO_Q, kSBO_Q);
-    const uint64_t aq_lo = smem_desc(x.q_lo + 2u * hg * kLBO_Q, kLBO_Q, kSBO_Q);
-    const uint64_t bk_hi = smem_desc(x.k_hi + 2u * h * kLBO, kLBO, kSBO_KL);
-    const uint64_t bk_lo = smem_desc(x.k_lo + 2u * h * kLBO, kLBO, kSBO_KL);
+    const uint64_t aq_hi = smem_desc(x.q_hi() + 2u * hg * kLBO_Q, kLBO_Q, kSBO_Q);
+    const uint64_t aq_lo = smem_desc(x.q_lo() + 2u * hg * kLBO_Q, kLBO_Q, kSBO_Q);
+    const uint64_t bk_hi = smem_desc(x.k_hi() + 2u * h * kLBO, kLBO, kSBO_KL);
+    const uint64_t bk_lo = smem_desc(x.k_lo() + 2u * h * kLBO, kLBO, kSBO_KL);
     const uint32_t d = x.tmem + kColSP + (uint32_t)(hg * x.npad);
     mma_ss(d, aq_hi, bk_hi, id, 0u);
     mma_ss(d, aq_hi, bk_lo, id, 1u);
     mma_ss(d, aq_lo, bk_hi, id, 1u);
-    tc_commit(&x.s->mma_bar);
+    tc_commit(&x.s()->mma_bar);
 }
 
 // O_hg = P_hg . V_h : A = P from TMEM (hi/lo pairs per 16-node chunk), B = V^T tile rows [16h, 16h+16)
@@ -231,11 +249,11 @@ __device__ __forceinline__ void issue_pv(const Ctx& x, int g, int hg) {
     tc_fence_after();
     const uint32_t id = idesc_f16(kRows, 16);
     const int h = 4 * g + hg;
-    uint64_t bv_hi = smem_desc(x.v_hi + 2u * h * x.sbo_v, kLBO, x.sbo_v);
-    uint64_t bv_lo = smem_desc(x.v_lo + 2u * h * x.sbo_v, kLBO, x.sbo_v);
+    uint64_t bv_hi = smem_desc(x.v_hi() + 2u * h * x.sbo_v(), kLBO, x.sbo_v());
+    uint64_t bv_lo = smem_desc(x.v_lo() + 2u * h * x.sbo_v(), kLBO, x.sbo_v());
     const uint32_t d = x.tmem + kColO + 16u * hg;
     uint32_t a = x.tmem + kColSP + (uint32_t)(hg * x.npad);
-    for (int jk = 0; jk < x.nch; ++jk) {
+    for (int jk = 0; jk < x.nch(); ++jk) {
         mma_ts(d, a, bv_hi, id, jk > 0 ? 1u : 0u);
         mma_ts(d, a, bv_lo, id, 1u);
         mma_ts(d, a + 8u, bv_hi, id, 1u);
@@ -243,7 +261,7 @@ __device__ __forceinline__ void issue_pv(const Ctx& x, int g, int hg) {
         bv_hi += (2u * kLBO) >> 4;   // next 16 nodes = two 16-byte K-chunks further
         bv_lo += (2u * kLBO) >> 4;
     }
-    tc_commit(&x.s->mma_bar);
+    tc_commit(&x.s()->mma_bar);
 }
 
 // logits = heads . (L W_out / sqrt(E))^T : A = heads from TMEM (k-step jk = head jk), B = L tile;
@@ -257,15 +275,15 @@ __device__ __forceinline__ void issue_logits(const Ctx& x, int par) {
 #pragma unroll
         for (int j2 = 0; j2 < 4; ++j2) {
             const int jk = 2 * j2 + par;
-            const uint64_t bl_hi = smem_desc(x.l_hi + 2u * jk * kLBO, kLBO, kSBO_KL);
-            const uint64_t bl_lo = smem_desc(x.l_lo + 2u * jk * kLBO, kLBO, kSBO_KL);
+            const uint64_t bl_hi = smem_desc(x.l_hi() + 2u * jk * kLBO, kLBO, kSBO_KL);
+            const uint64_t bl_lo = smem_desc(x.l_lo() + 2u * jk * kLBO, kLBO, kSBO_KL);
             const uint32_t a = x.tmem + kColHA + 8u * jk;
             mma_ts(d, a, bl_hi, id, j2 > 0 ? 1u : 0u);
             mma_ts(d, a, bl_lo, id, 1u);
             mma_ts(d, a + 64u, bl_hi, id, 1u);
         }
     }
-    tc_commit(&x.s->mma_bar);
+    tc_commit(&x.s()->mma_bar);
 }
 
 // Masked softmax numerator of one (row, head): S (fp32, NPAD columns of TMEM) -> P = exp(S - max) on
@@ -309,13 +327,8 @@ __device__ __forceinline__ void chunk_exp(const float (&sv)[16], float ml, float
     const float kLog2e = 1.4426950408889634f;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-#ifdef R4_X_NOMUFU
-        const float p0 = fmaf(fmaf(sv[2 * i], kLog2e, -ml), 1e-3f, 0.5f);
-        const float p1 = fmaf(fmaf(sv[2 * i + 1], kLog2e, -ml), 1e-3f, 0.5f);
-#else
         const float p0 = ex2_approx(fmaf(sv[2 * i], kLog2e, -ml));
         const float p1 = ex2_approx(fmaf(sv[2 * i + 1], kLog2e, -ml));
-#endif
         l0 += p0;
         l1 += p1;
         split2(p0, p1, hi[i], lo[i]);
@@ -355,46 +368,44 @@ __device__ __forceinline__ void rescale_chunk(uint32_t addr, float f) {
     tmem_st8(addr + 8u, lo);
 }
 
-__device__ __forceinline__ void softmax_chunk(uint32_t sp, int ch, const uint32_t (&v)[16], uint32_t bits,
-                                              float& m_run, float& l0, float& l1) {
+// One 16-node chunk.  spec (CTA-uniform): the reference refl2 (= ref * log2e) is the caller's and there is no
+// maximum, vote or rescale between the TMEM load and the exponentials; otherwise the exact online form.
+__device__ __forceinline__ void softmax_chunk(uint32_t sp, int ch, const uint32_t (&v)[16], uint32_t bits, bool spec,
+                                              float& refl2, float& m_run, float& l0, float& l1) {
     float sv[16];
     chunk_mask(v, bits, sv);
-    const float cm = chunk_max(sv);
-    const bool need = cm > m_run + 10.0f;          // also the first feasible chunk of the row (m_run = -inf)
-#ifdef R4_X_NOVOTE
-    if (ch == 0) m_run = cm;
-    if (false) {
-#else
-    if (__any_sync(kFull, need)) {
-#endif
-        const float f = need ? ex2_approx((m_run - cm) * 1.4426950408889634f) : 1.0f;   // -inf -> 0
+    if (!spec) {
+        const float cm = chunk_max(sv);
+        const bool need = cm > m_run + 10.0f;          // also the first feasible chunk of the row (m_run = -inf)
+        const bool resc = need && m_run != -INFINITY;  // a row with no feasible node so far wrote exact zeros only
+        if (__any_sync(kFull, resc)) {
+            const float f = resc ? ex2_approx((m_run - cm) * 1.4426950408889634f) : 1.0f;
+            l0 *= f;
+            l1 *= f;
+            for (int pc = 0; pc < ch; ++pc) rescale_chunk(sp + 16u * pc, f);
+            tc_wait_st();
+        }
         if (need) m_run = cm;
-        l0 *= f;
-        l1 *= f;
-        for (int pc = 0; pc < ch; ++pc) rescale_chunk(sp + 16u * pc, f);
-        tc_wait_st();
+        // a row with no feasible node so far has m_run = -inf: reference 0 keeps exp(-inf - ref) = 0, not NaN
+        refl2 = (m_run == -INFINITY ? 0.f : m_run) * 1.4426950408889634f;
     }
     uint32_t hi[8], lo[8];
-    // a row with no feasible node so far has m_run = -inf: reference 0 keeps exp(-inf - ref) = 0, not NaN
-    chunk_exp(sv, (m_run == -INFINITY ? 0.f : m_run) * 1.4426950408889634f, l0, l1, hi, lo);
-#ifdef R4_X_NOST
-    if (l0 == 12345.f) {
-        tmem_st8(sp + 16u * ch, hi);
-        tmem_st8(sp + 16u * ch + 8u, lo);
-    }
-#else
+    chunk_exp(sv, refl2, l0, l1, hi, lo);
     tmem_st8(sp + 16u * ch, hi);
     tmem_st8(sp + 16u * ch + 8u, lo);
-#endif
 }
 
-__device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int row, float* dbg_scores, int n) {
-    const uint32_t w0 = x.s->maskw[0][row], w1 = x.s->maskw[1][row], w2 = x.s->maskw[2][row],
-                   w3 = x.s->maskw[3][row];
+// spec = false: exact online form, returns rowsum(P) and the reference m_out it is relative to.
+// spec = true : P = exp(S - ref) against the caller's reference (ref * log2e in refl2); the caller checks the
+//               returned row sum and falls back to the exact form when it left the safe window.
+__device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int row, float* dbg_scores, int n,
+                                                 bool spec, float refl2, float& m_out) {
+    const uint32_t w0 = x.s()->maskw[0][row], w1 = x.s()->maskw[1][row], w2 = x.s()->maskw[2][row],
+                   w3 = x.s()->maskw[3][row];
     // full 16-column chunks, then an optional short tail (n = 100: 6 chunks + 4 columns)
-    const int lastv = n - 16 * (x.nch - 1);
+    const int lastv = n - 16 * (x.nch() - 1);
     const int tq = lastv <= 12 ? (lastv + 3) >> 2 : 0;
-    const int nfull = tq ? x.nch - 1 : x.nch;
+    const int nfull = tq ? x.nch() - 1 : x.nch();
     float m_run = -INFINITY, l0 = 0.f, l1 = 0.f;
     uint32_t a0 = w0, a1 = w1, a2 = w2, a3 = w3;
     uint32_t va[16], vb[16];
@@ -407,7 +418,7 @@ __device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int 
             for (int i = 0; i < 16; ++i)
                 if (16 * ch + i < n) dbg_scores[16 * ch + i] = __uint_as_float(va[i]);
         }
-        softmax_chunk(sp, ch, va, a0, m_run, l0, l1);
+        softmax_chunk(sp, ch, va, a0, spec, refl2, m_run, l0, l1);
         shift_mask16(a0, a1, a2, a3);
         if (ch + 1 < nfull) {
             tc_wait_ld();
@@ -417,7 +428,7 @@ __device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int 
                 for (int i = 0; i < 16; ++i)
                     if (16 * (ch + 1) + i < n) dbg_scores[16 * (ch + 1) + i] = __uint_as_float(vb[i]);
             }
-            softmax_chunk(sp, ch + 1, vb, a0, m_run, l0, l1);
+            softmax_chunk(sp, ch + 1, vb, a0, spec, refl2, m_run, l0, l1);
             shift_mask16(a0, a1, a2, a3);
         }
     }
@@ -429,26 +440,41 @@ __device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int 
             for (int i = 0; i < 12; ++i)
                 if (16 * nfull + i < n) dbg_scores[16 * nfull + i] = __uint_as_float(va[i]);
         }
-        softmax_chunk(sp, nfull, va, a0, m_run, l0, l1);   // mask bits beyond n are 0: padding -> exact zeros
+        softmax_chunk(sp, nfull, va, a0, spec, refl2, m_run, l0, l1);   // mask bits beyond n are 0: padding -> exact zeros
     }
     tc_wait_st();
-    const float l = l0 + l1;
-    return l > 0.f ? 1.0f / l : 0.f;
+    m_out = m_run;
+    return l0 + l1;
 }
 
 // All GEMM phases of one decoder step; on return the raw logits of the instance sit in TMEM
 // columns [kColLG, kColLG + n) (row = lane).  dbg_* (nullable) receive scores [S?,8,n] / heads [.,128]
 // of this thread's row for the parity tests.
+// Speculative softmax reference.  P only has to be exp(S - ref) for SOME ref that keeps the row sum l inside
+// the window where the fp16 hi/lo split is accurate relative to l (l >= 12.5: the 2^-25 absolute floor of the
+// lo halves stays below 2^-22 l over 100 nodes) and finite (l < 6e4 bounds every element by fp16's maximum).
+// The row's log-sum-exp moves slowly from one decode step to the next, so each (row, head) keeps lse of the
+// previous step and aims the next row sum at 2^10: the window is lse_new - lse_old in (-4.4, +4.1).  A miss
+// anywhere in the CTA (block-wide vote that replaces the barrier after the softmax) re-issues the score MMAs
+// of the group and takes the exact online form.  The first step of an instance has no reference yet.
+constexpr float kSpecTargetLn = 6.931471805599453f;   // ln 1024
+constexpr float kSpecLMin = 12.5f, kSpecLMax = 6.0e4f;
+
 template <int ENV>
 __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cache& c, int64_t b, int S,
                                                   uint32_t& mma_par, float* dbg_scores_row, float* dbg_heads_row,
-                                                  long long* prof, long long& tprev) {
+                                                  long long* prof, long long& tprev, float (&lse)[2],
+                                                  bool have_ref) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q = warp & 3, j = warp >> 2, row = 32 * q + lane;
     const uint32_t lane_base = x.tmem + ((uint32_t)(32 * q) << 16);
     const int n = c.n_nodes;
     const bool issuer = (warp < 4) && (lane == 0);   // issuer `warp` owns accumulator chain `warp`
-    float hv[2][16];
+    const float kLog2e = 1.4426950408889634f;
+    // heads of group 0 wait in shared memory while group 1 is processed: the Q region is idle between the end
+    // of scores(1) and the next step's Q build (word-interleaved over the CTA: conflict-free)
+    float* stash = reinterpret_cast<float*>(x.q_hi_p()) + threadIdx.x;
+    float hv[16];
     build_q<ENV, 0>(x, c, b, S, 0, warp, lane);
     __syncthreads();
     R4_STAMP(0);
@@ -457,40 +483,74 @@ __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cach
     for (int g = 0; g < 2; ++g) {
         wait_mma(x, mma_par);                          // scores of group g
         R4_STAMP(1 + 5 * g);
-        const float inv_l = softmax_inplace(x, lane_base + kColSP + (uint32_t)(j * x.npad), row,
-                                            dbg_scores_row ? dbg_scores_row + (4 * g + j) * n : nullptr, n);
-        tc_fence_before();
-        __syncthreads();
+        if (g == 1) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) stash[i * kThreads] = hv[i];
+        }
+        const uint32_t sp = lane_base + kColSP + (uint32_t)(j * x.npad);
+        float* dbg = dbg_scores_row ? dbg_scores_row + (4 * g + j) * n : nullptr;
+        float l, m;
+        bool spec = have_ref;
+        const float ref = lse[g] - kSpecTargetLn;
+        for (;;) {
+            l = softmax_inplace(x, sp, row, dbg, n, spec, ref * kLog2e, m);
+            if (spec) m = ref;
+            // l == 0: row without feasible nodes (padding rows)
+            const bool ok = !spec || (l == 0.f) || (l >= kSpecLMin && l < kSpecLMax);
+            tc_fence_before();
+            if (__syncthreads_and(ok)) break;
+            // rare: the reference missed somewhere in the CTA -> scores again, then the exact form
+            spec = false;
+            if (g == 1) {                              // the stash sits on the Q tile the MMAs need: rebuild it
+#pragma unroll
+                for (int i = 0; i < 16; ++i) hv[i] = stash[i * kThreads];
+                __syncthreads();
+                build_q<ENV, 0>(x, c, b, S, 1, warp, lane);
+                __syncthreads();
+            }
+            if (issuer) issue_scores(x, g, warp);
+            wait_mma(x, mma_par);
+            if (g == 1) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) stash[i * kThreads] = hv[i];
+            }
+        }
+        const float inv_l = l > 0.f ? 1.0f / l : 0.f;
+        lse[g] = l > 0.f ? m + __logf(l) : 0.f;
         R4_STAMP(2 + 5 * g);
         if (issuer) issue_pv(x, g, warp);
         if (g == 0) build_q<ENV, 4>(x, c, b, S, 1, warp, lane);   // Q of heads 4..7 while PV(0) runs (scores(0) is done)
         R4_STAMP(3 + 5 * g);
         wait_mma(x, mma_par);                          // PV of group g
         R4_STAMP(4 + 5 * g);
+        if (g == 0) {                                  // scores(1) run while O(0) is drained
+            __syncthreads();
+            if (issuer) issue_scores(x, 1, warp);
+        }
         uint32_t o[16];
         tmem_ld16(lane_base + kColO + 16u * j, o);
         tc_wait_ld();
 #pragma unroll
-        for (int i = 0; i < 16; ++i) hv[g][i] = __uint_as_float(o[i]) * inv_l;
+        for (int i = 0; i < 16; ++i) hv[i] = __uint_as_float(o[i]) * inv_l;
         tc_fence_before();
-        if (g == 0) {
-            __syncthreads();
-            if (issuer) issue_scores(x, 1, warp);
-            R4_STAMP(5);
-        }
+        if (g == 0) R4_STAMP(5);
     }
     // heads -> A operand in TMEM (fp16 hi/lo), k-step = head
 #pragma unroll
-    for (int g = 0; g < 2; ++g) {
+    for (int g = 1; g >= 0; --g) {
         const int h = 4 * g + j;
+        if (g == 0) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) hv[i] = stash[i * kThreads];
+        }
         uint32_t hi[8], lo[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) split2(hv[g][2 * i], hv[g][2 * i + 1], hi[i], lo[i]);
+        for (int i = 0; i < 8; ++i) split2(hv[2 * i], hv[2 * i + 1], hi[i], lo[i]);
         tmem_st8(lane_base + kColHA + 8u * h, hi);
         tmem_st8(lane_base + kColHA + 64u + 8u * h, lo);
         if (dbg_heads_row != nullptr) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) dbg_heads_row[16 * h + i] = hv[g][i];
+            for (int i = 0; i < 16; ++i) dbg_heads_row[16 * h + i] = hv[i];
         }
     }
     tc_wait_st();
@@ -541,27 +601,32 @@ __device__ __forceinline__ float tanh_small(float v) {
 __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_args& a, int n, int q, int j,
                                              int row, bool valid, int64_t grow, int t, int T, uint32_t nkey,
                                              int given, int& err_bits) {
-    Smem* s = x.s;
+    Smem* s = x.s();
     const uint32_t lg = x.tmem + ((uint32_t)(32 * q) << 16) + kColLG;
     const int U = (n + 3) >> 2;
     const int u0 = (U * j) >> 2, u1 = (U * (j + 1)) >> 2;
-    // 28 columns from 4*u0 on, both accumulators (columns past this thread's range are ignored below)
-    uint32_t raw[28], raw2[28];
+    // 28 columns from 4*u0 on, the two accumulators summed (columns past this thread's range are ignored
+    // below); two rounds of loads keep the register peak at 16 + 16 + 28
+    float tv[28];                                                   // tanh(logit) (or the logit), -inf if infeasible
     {
-        uint32_t a16[16], b16[16], a8[8], b8[8], a4[4], b4[4];
+        uint32_t a16[16], b16[16];
         tmem_ld16(lg + 4u * u0, a16);
         tmem_ld16(lg + (kColLG2 - kColLG) + 4u * u0, b16);
+        tc_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) tv[i] = __uint_as_float(a16[i]) + __uint_as_float(b16[i]);
+    }
+    {
+        uint32_t a8[8], b8[8], a4[4], b4[4];
         tmem_ld8(lg + 4u * u0 + 16u, a8);
         tmem_ld8(lg + (kColLG2 - kColLG) + 4u * u0 + 16u, b8);
         tmem_ld4(lg + 4u * u0 + 24u, a4);
         tmem_ld4(lg + (kColLG2 - kColLG) + 4u * u0 + 24u, b4);
         tc_wait_ld();
 #pragma unroll
-        for (int i = 0; i < 16; ++i) { raw[i] = a16[i]; raw2[i] = b16[i]; }
+        for (int i = 0; i < 8; ++i) tv[16 + i] = __uint_as_float(a8[i]) + __uint_as_float(b8[i]);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) { raw[16 + i] = a8[i]; raw2[16 + i] = b8[i]; }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { raw[24 + i] = a4[i]; raw2[24 + i] = b4[i]; }
+        for (int i = 0; i < 4; ++i) tv[24 + i] = __uint_as_float(a4[i]) + __uint_as_float(b4[i]);
     }
     const uint32_t w0 = s->maskw[0][row], w1 = s->maskw[1][row], w2 = s->maskw[2][row], w3 = s->maskw[3][row];
     const int sh = 4 * u0, wi = sh >> 5;
@@ -576,9 +641,6 @@ __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_a
     const bool clipped = a.tanh_clipping > 0.f;                     // decoding.py:171-172
     const float sc = (clipped ? a.tanh_clipping : 1.0f) / a.temperature;   // :179 folded into the clip scale
     const float kL2e = 1.4426950408889634f;
-    float tv[28];                                                   // tanh(logit) (or the logit), -inf if infeasible
-#pragma unroll
-    for (int e = 0; e < 28; ++e) tv[e] = __uint_as_float(raw[e]) + __uint_as_float(raw2[e]);
     if (clipped) {
         float am0 = 0.f, am1 = 0.f;
 #pragma unroll
@@ -715,7 +777,7 @@ template <int ENV>
 __device__ __forceinline__ void apply_action(const Ctx& x, const rl4co_rollout_args& a, RowState& st, int n, int q,
                                              int j, int row, bool valid, int64_t grow, int t, int T, int act,
                                              float lpa) {
-    Smem* s = x.s;
+    Smem* s = x.s();
     if (j == 0 && valid) {
         a.actions[grow * T + t] = act;
         a.logp[grow * T + t] = lpa;
@@ -777,22 +839,8 @@ __device__ __forceinline__ void apply_action(const Ctx& x, const rl4co_rollout_a
 // ---- context set-up shared by the kernels --------------------------------------------------------------
 __device__ __forceinline__ Ctx make_ctx(unsigned char* smem, int npad) {
     Ctx x;
-    const uint32_t tb = tile_bytes(npad);
-    const uint32_t base = smem_u32(smem);
-    x.k_hi = base;
-    x.k_lo = base + tb;
-    x.l_hi = base + 2u * tb;
-    x.l_lo = base + 3u * tb;
-    x.v_hi = base + 4u * tb;
-    x.v_lo = base + 5u * tb;
-    x.q_hi = base + 6u * tb;
-    x.q_lo = x.q_hi + kQTileBytes;
-    x.q_hi_p = smem + 6ull * tb;
-    x.q_lo_p = x.q_hi_p + kQTileBytes;
-    x.s = reinterpret_cast<Smem*>(x.q_lo_p + kQTileBytes);
+    x.smem = smem;
     x.npad = npad;
-    x.nch = npad / 16;
-    x.sbo_v = (uint32_t)(npad / 8) * 128u;
     x.tmem = 0;
     return x;
 }
@@ -801,37 +849,37 @@ __device__ __forceinline__ Ctx make_ctx(unsigned char* smem, int npad) {
 __device__ __forceinline__ void cta_setup(Ctx& x) {
     const int warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) {
-        mbar_init(&x.s->tma_bar, 1);
-        mbar_init(&x.s->mma_bar, 4);   // four MMA issuer threads commit per phase
+        mbar_init(&x.s()->tma_bar, 1);
+        mbar_init(&x.s()->mma_bar, 4);   // four MMA issuer threads commit per phase
         fence_mbar_init();
     }
     __syncwarp();
-    if (warp == 0) tmem_alloc(&x.s->tmem_ptr, kTmemCols);
+    if (warp == 0) tmem_alloc(&x.s()->tmem_ptr, kTmemCols);
     for (uint32_t i = threadIdx.x; i < 2u * kQTileBytes / 16u; i += kThreads)
-        reinterpret_cast<uint4*>(x.q_hi_p)[i] = make_uint4(0, 0, 0, 0);
+        reinterpret_cast<uint4*>(x.q_hi_p())[i] = make_uint4(0, 0, 0, 0);
     for (int i = threadIdx.x; i < kRows; i += kThreads) {
-        x.s->newvis[i] = 0;
-        x.s->cur[i] = 0;
-        x.s->first[i] = 0;
-        x.s->rem[i] = 0.f;
-        x.s->demand[i] = 0.f;
-        x.s->locs[i] = make_float2(0.f, 0.f);
+        x.s()->newvis[i] = 0;
+        x.s()->cur[i] = 0;
+        x.s()->first[i] = 0;
+        x.s()->rem[i] = 0.f;
+        x.s()->demand[i] = 0.f;
+        x.s()->locs[i] = make_float2(0.f, 0.f);
     }
     fence_proxy_async();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    x.tmem = x.s->tmem_ptr;
+    x.tmem = x.s()->tmem_ptr;
 }
 
 // the instance's six operand tiles: one TMA bulk copy each, one mbarrier phase
 __device__ __forceinline__ void load_tiles(const Ctx& x, unsigned char* smem, const unsigned char* img, int64_t b) {
     const uint32_t tb = tile_bytes(x.npad);
     fence_proxy_async();
-    mbar_expect_tx(&x.s->tma_bar, 6u * tb);
+    mbar_expect_tx(&x.s()->tma_bar, 6u * tb);
     const unsigned char* src = img + b * 6ull * tb;
 #pragma unroll
-    for (int i = 0; i < 6; ++i) bulk_g2s(smem + (size_t)i * tb, src + (size_t)i * tb, tb, &x.s->tma_bar);
+    for (int i = 0; i < 6; ++i) bulk_g2s(x.tiles_p() + (size_t)i * tb, src + (size_t)i * tb, tb, &x.s()->tma_bar);
 }
 
 // ---- persistent fused rollout (constructive/base.py:221-263), tensor path ------------------------------
@@ -841,7 +889,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     extern __shared__ __align__(128) unsigned char smem[];
     Ctx x = make_ctx(smem, npad);
     cta_setup(x);
-    Smem* s = x.s;
+    Smem* s = x.s();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q = warp & 3, j = warp >> 2, row = 32 * q + lane;
     const int n = c.n_nodes, S = a.num_starts, T = a.max_steps;
@@ -894,12 +942,13 @@ __global__ void __launch_bounds__(kThreads, 1)
         int all_done = __syncthreads_and(!valid || j != 0 || st.done);
         R4_STAMP(14);
 
+        float lse[2] = {0.f, 0.f};   // log-sum-exp of this thread's two (row, head) score rows, previous step
         for (int t = 1; !all_done; ++t) {
             if (t >= T) {
                 if (valid && j == 0 && !st.done) err_bits |= RL4CO_ERR_MAX_STEPS;
                 break;
             }
-            decode_step_gemms<ENV>(x, c, b, S, mma_par, nullptr, nullptr, prof, tprev);
+            decode_step_gemms<ENV>(x, c, b, S, mma_par, nullptr, nullptr, prof, tprev, lse, t > 1);
             int given = 0;
             if (a.mode == RL4CO_MODE_EVALUATE && valid) {
                 given = (t < a.actions_in_T) ? (int)a.actions_in[grow * a.actions_in_stride + t] : 0;
@@ -947,7 +996,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     extern __shared__ __align__(128) unsigned char smem[];
     Ctx x = make_ctx(smem, npad);
     cta_setup(x);
-    Smem* s = x.s;
+    Smem* s = x.s();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q = warp & 3, j = warp >> 2, row = 32 * q + lane;
     const int n = c.n_nodes;
@@ -973,10 +1022,11 @@ __global__ void __launch_bounds__(kThreads, 1)
         tma_par ^= 1u;
         __syncthreads();
         long long tprev = 0;
+        float lse[2] = {0.f, 0.f};
         decode_step_gemms<ENV>(x, c, b, S, mma_par,
                                (dbg_scores != nullptr && valid) ? dbg_scores + grow * (int64_t)(8 * n) : nullptr,
                                (dbg_heads != nullptr && valid) ? dbg_heads + grow * (int64_t)kE : nullptr, nullptr,
-                               tprev);
+                               tprev, lse, false);
         // this thread's quarter of the logit columns
         const uint32_t lg = x.tmem + ((uint32_t)(32 * q) << 16) + kColLG;
         const int U = (n + 3) >> 2;

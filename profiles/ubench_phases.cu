@@ -13,16 +13,15 @@ __device__ __forceinline__ uint32_t hash32(uint32_t x) {
 }
 
 // MODE 0: refill only; 1: refill + softmax_inplace; 2: refill + select_row (greedy)
-template <int MODE>
+template <int MODE, bool SPECB = false>
 __global__ void __launch_bounds__(kThreads, 1) phase_kernel(long long* out, float* sink, int reps, int feasible_pct, int big_logits,
                                                             rl4co_rollout_args a) {
     extern __shared__ __align__(1024) unsigned char smem[];
     Smem* s = reinterpret_cast<Smem*>(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, q = warp & 3, j = warp >> 2, row = 32 * q + lane;
     Ctx x;
-    x.s = s;
+    x.smem = smem;
     x.npad = 112;
-    x.nch = 7;
     if (warp == 0) tmem_alloc(&s->tmem_ptr, kTmemCols);
     const int n = 100;
     for (int w = 0; w < 4; ++w) {
@@ -62,7 +61,8 @@ __global__ void __launch_bounds__(kThreads, 1) phase_kernel(long long* out, floa
         __syncthreads();
         tc_fence_after();
         if (MODE == 1) {
-            acc += softmax_inplace(x, lane_base + kColSP + (uint32_t)(j * x.npad), row, nullptr, n);
+            float m;
+            acc += softmax_inplace(x, lane_base + kColSP + (uint32_t)(j * x.npad), row, nullptr, n, SPECB, -8.0f, m);
             tc_fence_before();
             __syncthreads();
         } else if (MODE == 2) {
@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(kThreads, 1) phase_kernel(long long* out, floa
     if (warp == 0) tmem_dealloc(x.tmem, kTmemCols);
 }
 
-template <int MODE>
+template <int MODE, bool SPECB = false>
 static double run(const char* name, int pct, double base, int big = 0) {
     long long* out;
     float* sink;
@@ -90,9 +90,9 @@ static double run(const char* name, int pct, double base, int big = 0) {
     a.tanh_clipping = 10.f;
     a.temperature = 1.f;
     const int reps = 200;
-    const size_t smem = sizeof(Smem) + 1024;
-    cudaFuncSetAttribute(phase_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    phase_kernel<MODE><<<148, kThreads, smem>>>(out, sink, reps, pct, big, a);
+    const size_t smem = kOffTiles;
+    cudaFuncSetAttribute(phase_kernel<MODE, SPECB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    phase_kernel<MODE, SPECB><<<148, kThreads, smem>>>(out, sink, reps, pct, big, a);
     cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { printf("%s: %s\n", name, cudaGetErrorString(e)); return 0; }
     long long h;
@@ -107,7 +107,8 @@ static double run(const char* name, int pct, double base, int big = 0) {
 int main() {
     for (int pct : {100, 50, 15}) {
         const double b1 = run<0>("refill (112 cols)", pct, 0);
-        run<1>("softmax_inplace", pct, b1);
+        run<1>("softmax exact (online)", pct, b1);
+        run<1, true>("softmax speculative", pct, b1);
         run<2>("select_row greedy |v|<1", pct, b1 * 0.5);
         run<2>("select_row greedy |v|>1", pct, b1 * 0.5, 1);
     }
