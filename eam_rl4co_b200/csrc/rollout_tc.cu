@@ -37,9 +37,13 @@ constexpr uint32_t kColLG2 = 240;// logits accumulators, odd k-steps (two chains
 // K-major, no-swizzle operand tiles (see tc_ptx.cuh::smem_desc)
 constexpr uint32_t kLBO = 128;                 // static tiles: the K-chunks of a row group are contiguous
 constexpr uint32_t kSBO_KL = 16 * kLBO;        // K / L tiles: 16 chunks (128 channels) per row group
-constexpr uint32_t kLBO_Q = 144;               // Q tile: chunk stride padded by 16 B (bank spread)
-constexpr uint32_t kSBO_Q = 8 * kLBO_Q;        // 8 chunks (64 channels) per row group
-constexpr uint32_t kQTileBytes = (kRows / 8) * kSBO_Q;
+// Q tiles: one per team (head slot) = 128 rows x 16 channels, hi then lo; a row group is its two K-chunks
+constexpr uint32_t kLBO_Q = 128;
+constexpr uint32_t kSBO_Q = 2 * kLBO_Q;
+constexpr uint32_t kQHalfBytes = (kRows / 8) * kSBO_Q;   // 4 KB: the hi (or lo) half of a team's tile
+constexpr uint32_t kQTeamBytes = 2 * kQHalfBytes;        // 8 KB = 128 threads x 16 words (also the head stash)
+constexpr uint32_t kQTileBytes = 2 * kQTeamBytes;        // (x 2 = all four teams, see kOffTiles)
+constexpr int kTeamBar = 5;                              // named barriers 5..8: the four warps of a team
 
 __host__ __device__ inline int npad_of(int n) { return (n + 15) & ~15; }
 __host__ __device__ inline uint32_t tile_bytes(int npad) { return (uint32_t)npad * 256u; }
@@ -59,7 +63,8 @@ struct Smem {
     float2 locs[kRows];
     float demand[kRows];        // indexed by node (node 0 unused)
     uint64_t tma_bar;
-    uint64_t mma_bar;
+    uint64_t mma_bar;           // logits MMAs (4 arrivals)
+    uint64_t team_bar[4];       // scores / PV MMAs of one team (1 arrival)
     uint32_t tmem_ptr;
     uint32_t pad_;
 };
@@ -74,12 +79,11 @@ struct Ctx {
     uint32_t tmem;
     int npad;
     __device__ __forceinline__ Smem* s() const { return reinterpret_cast<Smem*>(smem); }
-    __device__ __forceinline__ unsigned char* q_hi_p() const { return smem + kOffQ; }
-    __device__ __forceinline__ unsigned char* q_lo_p() const { return smem + kOffQ + kQTileBytes; }
+    __device__ __forceinline__ unsigned char* q_p(int team) const { return smem + kOffQ + (uint32_t)team * kQTeamBytes; }
+    __device__ __forceinline__ uint32_t q_hi(int team) const { return base() + kOffQ + (uint32_t)team * kQTeamBytes; }
+    __device__ __forceinline__ uint32_t q_lo(int team) const { return q_hi(team) + kQHalfBytes; }
     __device__ __forceinline__ unsigned char* tiles_p() const { return smem + kOffTiles; }
     __device__ __forceinline__ uint32_t base() const { return smem_u32(smem); }
-    __device__ __forceinline__ uint32_t q_hi() const { return base() + kOffQ; }
-    __device__ __forceinline__ uint32_t q_lo() const { return base() + kOffQ + kQTileBytes; }
     __device__ __forceinline__ uint32_t tile(int i) const { return base() + kOffTiles + (uint32_t)i * tile_bytes(npad); }
     __device__ __forceinline__ uint32_t k_hi() const { return tile(0); }
     __device__ __forceinline__ uint32_t k_lo() const { return tile(1); }
@@ -164,25 +168,27 @@ __global__ void __launch_bounds__(256) tc_pack_kernel(rl4co_cache c, unsigned ch
 // the thread owns row 32q + lane and, within the row, head j of the current group, mask word j,
 // and the j-th quarter of the logit columns.
 
-// Q tile of head group g (channels [64g, 64g+64)) for rows [0,S): context.py:118-140 (TSP,
-// pa[first] + pb[cur]) / :70-74,155-157 (CVRP, pb[cur] + (cap - used) * wcap), split to fp16 hi/lo.
-template <int ENV, int FIRST_WARP>
-__device__ __forceinline__ void build_q(const Ctx& x, const rl4co_cache& c, int64_t b, int S, int g, int warp,
-                                        int lane) {
-    // warps [FIRST_WARP, 16) take part (the MMA issuer warps are left out while they issue PV)
-    constexpr int NW = kWarps - FIRST_WARP;
-    constexpr int ITERS = (kRows / 2 + NW - 1) / NW;
-    if (warp < FIRST_WARP) return;
-    const int w = warp - FIRST_WARP;
-    const int l16 = lane & 15, half = lane >> 4;
+// Teams.  The four warps {4j .. 4j+3} (one per scheduler / TMEM lane quadrant) form team j and own head slot j:
+// heads j and 4+j, the score / probability columns [j NPAD, (j+1) NPAD), the PV accumulator [16j, 16j+16), a
+// private Q tile, a private mbarrier and named barrier 5+j.  Between the step's first instruction and the
+// logits GEMM a team synchronises only with itself, so the teams drift apart and one team's MMA / L2 waits
+// are covered by the softmax arithmetic of the others (every scheduler holds one warp of each team).
+
+// Q tile of head h (channels [16h, 16h+16)) by the team's four warps: context.py:118-140 (TSP, pa[first] +
+// pb[cur]) / :70-74,155-157 (CVRP, pb[cur] + (cap - used) * wcap), split to fp16 hi/lo.  Warp q covers rows
+// [32q, 32q+32) in four passes of 8 rows; four lanes read the 64 contiguous bytes of a row (whole sectors).
+// Rows >= S are written as zeros.
+template <int ENV>
+__device__ __forceinline__ void build_q(const Ctx& x, const rl4co_cache& c, int64_t b, int S, int h, int team,
+                                        int q, int lane) {
     const int64_t base = b * (int64_t)c.n_nodes;
-    const int choff = 64 * g + 4 * l16;
-    // kRows / 2 row pairs over NW warps: issue every gather first (L2 latency overlaps)
-    float4 qa[ITERS], qb[ITERS];
-    float rem[ITERS];
+    const int pc = lane & 3;                           // 4-channel piece of the head's 16 channels
+    const int choff = 16 * h + 4 * pc;
+    float4 qa[4], qb[4];
+    float rem[4];
 #pragma unroll
-    for (int it = 0; it < ITERS; ++it) {
-        const int r = 2 * (w + NW * it) + half;
+    for (int it = 0; it < 4; ++it) {                   // every gather first: the L2 latencies overlap
+        const int r = 32 * q + 8 * it + (lane >> 2);
         qa[it] = make_float4(0.f, 0.f, 0.f, 0.f);
         qb[it] = qa[it];
         rem[it] = 0.f;
@@ -195,64 +201,68 @@ __device__ __forceinline__ void build_q(const Ctx& x, const rl4co_cache& c, int6
     float4 wc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (ENV == RL4CO_ENV_CVRP) wc = ld4(c.wcap + choff);
 #pragma unroll
-    for (int it = 0; it < ITERS; ++it) {
-        const int r = 2 * (w + NW * it) + half;
-        if (r < kRows) {
-            // rows >= S: qa = qb = 0 -> zeros (the Q region doubles as the head stash, so they are rewritten)
-            float4 q;
-            if (ENV == RL4CO_ENV_TSP)
-                q = make_float4(qa[it].x + qb[it].x, qa[it].y + qb[it].y, qa[it].z + qb[it].z, qa[it].w + qb[it].w);
-            else
-                q = make_float4(fmaf(rem[it], wc.x, qb[it].x), fmaf(rem[it], wc.y, qb[it].y),
-                                fmaf(rem[it], wc.z, qb[it].z), fmaf(rem[it], wc.w, qb[it].w));
-            uint32_t h0, l0, h1, l1;
-            split2(q.x, q.y, h0, l0);
-            split2(q.z, q.w, h1, l1);
-            const uint32_t off = (uint32_t)(r >> 3) * kSBO_Q + (uint32_t)(l16 >> 1) * kLBO_Q +
-                                 (uint32_t)(r & 7) * 16u + (uint32_t)(l16 & 1) * 8u;
-            *reinterpret_cast<uint2*>(x.q_hi_p() + off) = make_uint2(h0, h1);
-            *reinterpret_cast<uint2*>(x.q_lo_p() + off) = make_uint2(l0, l1);
-        }
+    for (int it = 0; it < 4; ++it) {
+        const int r = 32 * q + 8 * it + (lane >> 2);
+        float4 v;
+        if (ENV == RL4CO_ENV_TSP)
+            v = make_float4(qa[it].x + qb[it].x, qa[it].y + qb[it].y, qa[it].z + qb[it].z, qa[it].w + qb[it].w);
+        else
+            v = make_float4(fmaf(rem[it], wc.x, qb[it].x), fmaf(rem[it], wc.y, qb[it].y),
+                            fmaf(rem[it], wc.z, qb[it].z), fmaf(rem[it], wc.w, qb[it].w));
+        uint32_t h0, l0, h1, l1;
+        split2(v.x, v.y, h0, l0);
+        split2(v.z, v.w, h1, l1);
+        unsigned char* t = x.q_p(team) + (uint32_t)(r >> 3) * kSBO_Q + (uint32_t)(pc >> 1) * kLBO_Q +
+                           (uint32_t)(r & 7) * 16u + (uint32_t)(pc & 1) * 8u;
+        *reinterpret_cast<uint2*>(t) = make_uint2(h0, h1);
+        *reinterpret_cast<uint2*>(t + kQHalfBytes) = make_uint2(l0, l1);
     }
     fence_proxy_async();
 }
 
-__device__ __forceinline__ void wait_mma(const Ctx& x, uint32_t& par) {
-    mbar_wait(&x.s()->mma_bar, par);
+__device__ __forceinline__ void wait_mma(uint64_t* bar, uint32_t& par) {
+    mbar_wait(bar, par);
     par ^= 1u;
     tc_fence_after();
 }
 
-// MMA issue is spread over four threads (lane 0 of warps 0..3, one per scheduler): issuer `hg` owns the
-// accumulator chain of head hg of the group (scores, PV) or of one k-step parity (logits), so the four
-// chains are issued concurrently and pipeline in the tensor core; each issuer commits to the same
-// mbarrier (count 4).  Descriptors are advanced by adding to their low word.
+// barrier of the 128 threads of a team, and the same with an AND-vote
+__device__ __forceinline__ void team_sync(int team) { bar_sync(kTeamBar + team, 128); }
+__device__ __forceinline__ bool team_all(int team, bool pred) {
+    uint32_t r;
+    asm volatile(
+        "{\n\t.reg .pred p, r;\n\tsetp.ne.u32 p, %1, 0;\n\tbar.red.and.pred r, %2, 128, p;\n\t"
+        "selp.u32 %0, 1, 0, r;\n\t}"
+        : "=r"(r)
+        : "r"((uint32_t)pred), "r"(kTeamBar + team)
+        : "memory");
+    return r != 0u;
+}
 
-// scores of head hg of group g: S_hg = Q_hg . K_h^T, three MMAs (hi*hi + hi*lo + lo*hi)
-__device__ __forceinline__ void issue_scores(const Ctx& x, int g, int hg) {
+// scores of head h in slot `team`: S = Q_h . K_h^T, three MMAs (hi*hi + hi*lo + lo*hi); issued by one thread
+// of the team, completion on the team's mbarrier
+__device__ __forceinline__ void issue_scores(const Ctx& x, int h, int team) {
     tc_fence_after();
     const uint32_t id = idesc_f16(kRows, x.npad);
-    const int h = 4 * g + hg;
-    const uint64_t aq_hi = smem_desc(x.q_hi() + 2u * hg * kLBO_Q, kLBO_Q, kSBO_Q);
-    const uint64_t aq_lo = smem_desc(x.q_lo() + 2u * hg * kLBO_Q, kLBO_Q, kSBO_Q);
+    const uint64_t aq_hi = smem_desc(x.q_hi(team), kLBO_Q, kSBO_Q);
+    const uint64_t aq_lo = smem_desc(x.q_lo(team), kLBO_Q, kSBO_Q);
     const uint64_t bk_hi = smem_desc(x.k_hi() + 2u * h * kLBO, kLBO, kSBO_KL);
     const uint64_t bk_lo = smem_desc(x.k_lo() + 2u * h * kLBO, kLBO, kSBO_KL);
-    const uint32_t d = x.tmem + kColSP + (uint32_t)(hg * x.npad);
+    const uint32_t d = x.tmem + kColSP + (uint32_t)(team * x.npad);
     mma_ss(d, aq_hi, bk_hi, id, 0u);
     mma_ss(d, aq_hi, bk_lo, id, 1u);
     mma_ss(d, aq_lo, bk_hi, id, 1u);
-    tc_commit(&x.s()->mma_bar);
+    tc_commit(&x.s()->team_bar[team]);
 }
 
-// O_hg = P_hg . V_h : A = P from TMEM (hi/lo pairs per 16-node chunk), B = V^T tile rows [16h, 16h+16)
-__device__ __forceinline__ void issue_pv(const Ctx& x, int g, int hg) {
+// O = P . V_h : A = P from TMEM (hi/lo pairs per 16-node chunk), B = V^T tile rows [16h, 16h+16)
+__device__ __forceinline__ void issue_pv(const Ctx& x, int h, int team) {
     tc_fence_after();
     const uint32_t id = idesc_f16(kRows, 16);
-    const int h = 4 * g + hg;
     uint64_t bv_hi = smem_desc(x.v_hi() + 2u * h * x.sbo_v(), kLBO, x.sbo_v());
     uint64_t bv_lo = smem_desc(x.v_lo() + 2u * h * x.sbo_v(), kLBO, x.sbo_v());
-    const uint32_t d = x.tmem + kColO + 16u * hg;
-    uint32_t a = x.tmem + kColSP + (uint32_t)(hg * x.npad);
+    const uint32_t d = x.tmem + kColO + 16u * team;
+    uint32_t a = x.tmem + kColSP + (uint32_t)(team * x.npad);
     for (int jk = 0; jk < x.nch(); ++jk) {
         mma_ts(d, a, bv_hi, id, jk > 0 ? 1u : 0u);
         mma_ts(d, a, bv_lo, id, 1u);
@@ -261,7 +271,7 @@ __device__ __forceinline__ void issue_pv(const Ctx& x, int g, int hg) {
         bv_hi += (2u * kLBO) >> 4;   // next 16 nodes = two 16-byte K-chunks further
         bv_lo += (2u * kLBO) >> 4;
     }
-    tc_commit(&x.s()->mma_bar);
+    tc_commit(&x.s()->team_bar[team]);
 }
 
 // logits = heads . (L W_out / sqrt(E))^T : A = heads from TMEM (k-step jk = head jk), B = L tile;
@@ -462,33 +472,36 @@ constexpr float kSpecLMin = 12.5f, kSpecLMax = 6.0e4f;
 
 template <int ENV>
 __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cache& c, int64_t b, int S,
-                                                  uint32_t& mma_par, float* dbg_scores_row, float* dbg_heads_row,
-                                                  long long* prof, long long& tprev, float (&lse)[2],
-                                                  bool have_ref) {
+                                                  uint32_t& mma_par, uint32_t& team_par, float* dbg_scores_row,
+                                                  float* dbg_heads_row, long long* prof, long long& tprev,
+                                                  float (&lse)[2], bool have_ref) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q = warp & 3, j = warp >> 2, row = 32 * q + lane;
     const uint32_t lane_base = x.tmem + ((uint32_t)(32 * q) << 16);
     const int n = c.n_nodes;
-    const bool issuer = (warp < 4) && (lane == 0);   // issuer `warp` owns accumulator chain `warp`
+    // the team's MMAs are issued by one elected lane of its warp on scheduler j: one issuing warp per scheduler
+    const bool issuer_warp = (q == j);
+    uint64_t* tbar = &x.s()->team_bar[j];
     const float kLog2e = 1.4426950408889634f;
-    // heads of group 0 wait in shared memory while group 1 is processed: the Q region is idle between the end
-    // of scores(1) and the next step's Q build (word-interleaved over the CTA: conflict-free)
-    float* stash = reinterpret_cast<float*>(x.q_hi_p()) + threadIdx.x;
+    // heads of round 0 wait in the team's Q tile while round 1 is processed: the tile is idle between the end
+    // of scores(1) and the next step's Q build (8 KB = 128 threads x 16 words, conflict-free)
+    float* stash = reinterpret_cast<float*>(x.q_p(j)) + (threadIdx.x & 127);
     float hv[16];
-    build_q<ENV, 0>(x, c, b, S, 0, warp, lane);
-    __syncthreads();
+    build_q<ENV>(x, c, b, S, j, j, q, lane);
+    team_sync(j);
     R4_STAMP(0);
-    if (issuer) issue_scores(x, 0, warp);
+    if (issuer_warp) { if (elect_one()) issue_scores(x, j, j); }
 #pragma unroll
     for (int g = 0; g < 2; ++g) {
-        wait_mma(x, mma_par);                          // scores of group g
+        const int h = 4 * g + j;
+        wait_mma(tbar, team_par);                      // scores of round g
         R4_STAMP(1 + 5 * g);
         if (g == 1) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) stash[i * kThreads] = hv[i];
+            for (int i = 0; i < 16; ++i) stash[i * 128] = hv[i];
         }
         const uint32_t sp = lane_base + kColSP + (uint32_t)(j * x.npad);
-        float* dbg = dbg_scores_row ? dbg_scores_row + (4 * g + j) * n : nullptr;
+        float* dbg = dbg_scores_row ? dbg_scores_row + h * n : nullptr;
         float l, m;
         bool spec = have_ref;
         const float ref = lse[g] - kSpecTargetLn;
@@ -498,34 +511,34 @@ __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cach
             // l == 0: row without feasible nodes (padding rows)
             const bool ok = !spec || (l == 0.f) || (l >= kSpecLMin && l < kSpecLMax);
             tc_fence_before();
-            if (__syncthreads_and(ok)) break;
-            // rare: the reference missed somewhere in the CTA -> scores again, then the exact form
+            if (team_all(j, ok)) break;
+            // rare: the reference missed somewhere in the team -> scores again, then the exact form
             spec = false;
             if (g == 1) {                              // the stash sits on the Q tile the MMAs need: rebuild it
 #pragma unroll
-                for (int i = 0; i < 16; ++i) hv[i] = stash[i * kThreads];
-                __syncthreads();
-                build_q<ENV, 0>(x, c, b, S, 1, warp, lane);
-                __syncthreads();
+                for (int i = 0; i < 16; ++i) hv[i] = stash[i * 128];
+                team_sync(j);
+                build_q<ENV>(x, c, b, S, h, j, q, lane);
+                team_sync(j);
             }
-            if (issuer) issue_scores(x, g, warp);
-            wait_mma(x, mma_par);
+            if (issuer_warp) { if (elect_one()) issue_scores(x, h, j); }
+            wait_mma(tbar, team_par);
             if (g == 1) {
 #pragma unroll
-                for (int i = 0; i < 16; ++i) stash[i * kThreads] = hv[i];
+                for (int i = 0; i < 16; ++i) stash[i * 128] = hv[i];
             }
         }
         const float inv_l = l > 0.f ? 1.0f / l : 0.f;
         lse[g] = l > 0.f ? m + __logf(l) : 0.f;
         R4_STAMP(2 + 5 * g);
-        if (issuer) issue_pv(x, g, warp);
-        if (g == 0) build_q<ENV, 4>(x, c, b, S, 1, warp, lane);   // Q of heads 4..7 while PV(0) runs (scores(0) is done)
+        if (issuer_warp) { if (elect_one()) issue_pv(x, h, j); }
+        if (g == 0) build_q<ENV>(x, c, b, S, 4 + j, j, q, lane);   // next round's Q while PV runs (scores(0) is done)
         R4_STAMP(3 + 5 * g);
-        wait_mma(x, mma_par);                          // PV of group g
+        wait_mma(tbar, team_par);                      // PV of round g
         R4_STAMP(4 + 5 * g);
         if (g == 0) {                                  // scores(1) run while O(0) is drained
-            __syncthreads();
-            if (issuer) issue_scores(x, 1, warp);
+            team_sync(j);
+            if (issuer_warp) { if (elect_one()) issue_scores(x, 4 + j, j); }
         }
         uint32_t o[16];
         tmem_ld16(lane_base + kColO + 16u * j, o);
@@ -535,13 +548,16 @@ __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cach
         tc_fence_before();
         if (g == 0) R4_STAMP(5);
     }
+    // every team is done with its probabilities: the head operand and the logits accumulators reuse those columns
+    __syncthreads();
+    tc_fence_after();
     // heads -> A operand in TMEM (fp16 hi/lo), k-step = head
 #pragma unroll
     for (int g = 1; g >= 0; --g) {
         const int h = 4 * g + j;
         if (g == 0) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) hv[i] = stash[i * kThreads];
+            for (int i = 0; i < 16; ++i) hv[i] = stash[i * 128];
         }
         uint32_t hi[8], lo[8];
 #pragma unroll
@@ -557,8 +573,8 @@ __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cach
     tc_fence_before();
     __syncthreads();
     R4_STAMP(10);
-    if (issuer) issue_logits(x, warp);
-    wait_mma(x, mma_par);
+    if (warp < 4) { if (elect_one()) issue_logits(x, warp); }
+    wait_mma(&x.s()->mma_bar, mma_par);
     R4_STAMP(11);
 }
 
@@ -850,13 +866,14 @@ __device__ __forceinline__ void cta_setup(Ctx& x) {
     const int warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) {
         mbar_init(&x.s()->tma_bar, 1);
-        mbar_init(&x.s()->mma_bar, 4);   // four MMA issuer threads commit per phase
+        mbar_init(&x.s()->mma_bar, 4);   // four issuer threads commit the logits MMAs
+        for (int i = 0; i < 4; ++i) mbar_init(&x.s()->team_bar[i], 1);
         fence_mbar_init();
     }
     __syncwarp();
     if (warp == 0) tmem_alloc(&x.s()->tmem_ptr, kTmemCols);
     for (uint32_t i = threadIdx.x; i < 2u * kQTileBytes / 16u; i += kThreads)
-        reinterpret_cast<uint4*>(x.q_hi_p())[i] = make_uint4(0, 0, 0, 0);
+        reinterpret_cast<uint4*>(x.q_p(0))[i] = make_uint4(0, 0, 0, 0);
     for (int i = threadIdx.x; i < kRows; i += kThreads) {
         x.s()->newvis[i] = 0;
         x.s()->cur[i] = 0;
@@ -894,7 +911,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     const int q = warp & 3, j = warp >> 2, row = 32 * q + lane;
     const int n = c.n_nodes, S = a.num_starts, T = a.max_steps;
     const bool valid = row < S;
-    uint32_t tma_par = 0, mma_par = 0;
+    uint32_t tma_par = 0, mma_par = 0, team_par = 0;
     // optional phase timing (debug): thread 0 of CTA 0 accumulates clock64 deltas per phase
     long long* prof = (a.phase_cycles != nullptr && blockIdx.x == 0 && threadIdx.x == 0) ? a.phase_cycles : nullptr;
     long long tprev = clock64();
@@ -948,7 +965,7 @@ __global__ void __launch_bounds__(kThreads, 1)
                 if (valid && j == 0 && !st.done) err_bits |= RL4CO_ERR_MAX_STEPS;
                 break;
             }
-            decode_step_gemms<ENV>(x, c, b, S, mma_par, nullptr, nullptr, prof, tprev, lse, t > 1);
+            decode_step_gemms<ENV>(x, c, b, S, mma_par, team_par, nullptr, nullptr, prof, tprev, lse, t > 1);
             int given = 0;
             if (a.mode == RL4CO_MODE_EVALUATE && valid) {
                 given = (t < a.actions_in_T) ? (int)a.actions_in[grow * a.actions_in_stride + t] : 0;
@@ -1001,7 +1018,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     const int q = warp & 3, j = warp >> 2, row = 32 * q + lane;
     const int n = c.n_nodes;
     const bool valid = row < S;
-    uint32_t tma_par = 0, mma_par = 0;
+    uint32_t tma_par = 0, mma_par = 0, team_par = 0;
     for (int64_t b = blockIdx.x; b < c.B; b += gridDim.x) {
         if (threadIdx.x == 0) load_tiles(x, smem, img, b);
         const int64_t grow = (int64_t)row * c.B + b;
@@ -1023,7 +1040,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         __syncthreads();
         long long tprev = 0;
         float lse[2] = {0.f, 0.f};
-        decode_step_gemms<ENV>(x, c, b, S, mma_par,
+        decode_step_gemms<ENV>(x, c, b, S, mma_par, team_par,
                                (dbg_scores != nullptr && valid) ? dbg_scores + grow * (int64_t)(8 * n) : nullptr,
                                (dbg_heads != nullptr && valid) ? dbg_heads + grow * (int64_t)kE : nullptr, nullptr,
                                tprev, lse, false);

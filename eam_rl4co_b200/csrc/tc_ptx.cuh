@@ -161,6 +161,15 @@ __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t&
         : "f"(a), "f"(b));
 }
 
+// One thread of a converged warp.  tcgen05.mma must be issued as `if (<warp-uniform>) { if (elect_one()) ... }`:
+// behind a per-thread predicate (threadIdx.x == k) ptxas wraps every UTCHMMA in an ELECT / BRA.U.ANY loop over
+// the active lanes and the issue cost is ~60 cycles per MMA instead of ~20 (profiles/ubench_mma.cu).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0u;
+}
+
 __device__ __forceinline__ float ex2_approx(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));

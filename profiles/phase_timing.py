@@ -7,9 +7,9 @@ import torch
 import eam_rl4co_b200 as P
 import bench
 
-NAMES = ["Q(0) build+sync", "wait scores(0)", "softmax(0) +sync", "issue PV(0)+Q(1) build", "wait PV(0)",
-         "drain O(0)+sync+issue scores(1)", "wait scores(1)", "softmax(1) +sync", "issue PV(1)", "wait PV(1)",
-         "drain O(1)+heads->TMEM+sync", "logits issue+wait", "select", "env step+sync", "instance prologue", "-"]
+NAMES = ["Q(0) build+team sync", "wait scores(0)", "softmax(0) +team vote", "issue PV(0)+Q(1) build", "wait PV(0)",
+         "team sync+issue scores(1)+drain O(0)", "wait scores(1)", "softmax(1) +team vote", "issue PV(1)", "wait PV(1)",
+         "drain O(1)+CTA sync+heads->TMEM+sync", "logits issue+wait", "select", "env step+sync", "instance prologue", "-"]
 
 def main():
     B = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
