@@ -11,7 +11,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librl4co_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["capi.cu", "env_kernels.cu", "decode_kernels.cu", "rollout_kernel.cu", "rollout_tc.cu"]
+SOURCES = ["capi.cu", "env_kernels.cu", "decode_kernels.cu", "rollout_kernel.cu", "rollout_tc.cu", "encoder_tc.cu"]
 
 ENV_TSP, ENV_CVRP = 0, 1
 MODE_GREEDY, MODE_SAMPLING, MODE_EVALUATE = 0, 1, 2
@@ -25,12 +25,14 @@ ERR_MESSAGES = [  # (bit, reference assertion text); first match is raised
     (32, "Exceeded maximum number of steps during decoding"),
 ]
 IMPL_AUTO, IMPL_FP32, IMPL_TC = 0, 1, 2
+ENC_EPI_PLAIN, ENC_EPI_RELU, ENC_EPI_RES_NORM = 0, 1, 2
 ABI_VERSION = 2
 
 EXPORTS = [
     "rl4co_b200_abi_version", "rl4co_last_error", "rl4co_tsp_step", "rl4co_cvrp_step_mask",
     "rl4co_cvrp_action_mask", "rl4co_tour_reward", "rl4co_select", "rl4co_decode_step",
     "rl4co_rollout", "rl4co_noise_gumbel", "rl4co_tc_image_bytes", "rl4co_tc_pack", "rl4co_tc_decode_step",
+    "rl4co_enc_packed_bytes", "rl4co_enc_pack_weight", "rl4co_enc_linear", "rl4co_enc_attention",
 ]
 
 
@@ -85,6 +87,7 @@ def lib():
         for name in EXPORTS:
             getattr(L, name)  # fail loudly on a missing symbol
         L.rl4co_tc_image_bytes.restype = C.c_int64
+        L.rl4co_enc_packed_bytes.restype = C.c_int64
         if L.rl4co_b200_abi_version() != ABI_VERSION:
             raise RuntimeError("librl4co_b200.so ABI version mismatch")
         _lib = L

@@ -1,15 +1,24 @@
-"""Graph-attention encoder of the AttentionModel, plain PyTorch.
+"""Graph-attention encoder of the AttentionModel.
 
-NOT part of the hot path: it runs once per rollout and produces
-the node embeddings `h [B, N', E]` the rollout kernels consume.  It is restated here only so
-that the policy is usable stand-alone; module / parameter names follow the reference
+It runs once per rollout and produces the node embeddings `h [B, N', E]` the rollout kernels consume
+(§8f rank 3 is its kernel path).  Module / parameter names follow the reference
 (rl4co/models/zoo/am/encoder.py:70-91, nn/graph/attnnet.py:16-103, nn/attention.py:66-136,
 nn/ops.py:32-56, nn/mlp.py, nn/env_embeddings/init.py:55-68,115-138) so that reference
 state_dicts load unchanged.
+
+Two executions of the same arithmetic:
+  * the plain-PyTorch modules below (differentiable: training, and any configuration the kernels do not cover);
+  * `GraphAttentionNetwork._forward_kernels`: under `torch.no_grad()` on CUDA with instance normalisation,
+    embed_dim 128, 8 heads and N' <= 128 the layers run on the tcgen05 kernels of csrc/encoder_tc.cu (split-fp16
+    GEMMs with the residual + instance norm fused into their epilogues, fp32 attention) - 5 launches per layer.
 """
+import ctypes as C
+
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
+
+from . import _lib
 
 
 class TSPInitEmbedding(nn.Module):
@@ -96,7 +105,60 @@ class GraphAttentionNetwork(nn.Module):
                 Normalization(embed_dim, normalization),
             ) for _ in range(num_layers)))
 
+        self.num_heads, self.embed_dim, self.normalization = num_heads, embed_dim, normalization
+        self.feedforward_hidden = feedforward_hidden
+        self.use_kernels = True        # set False to force the PyTorch modules
+        self._packed = {}              # id(weight) -> (version, packed tiles)
+
+    def kernels_apply(self, x):
+        return (self.use_kernels and x.is_cuda and not torch.is_grad_enabled() and x.dtype == torch.float32
+                and self.normalization == "instance" and self.embed_dim == 128 and self.num_heads == 8
+                and self.feedforward_hidden % 128 == 0 and self.feedforward_hidden <= 512 and x.shape[1] <= 128)
+
+    def _pack(self, w):
+        """nn.Linear weight -> MMA tiles; cached per parameter version (in-place optimiser steps bump it)."""
+        key, ver = id(w), w._version
+        hit = self._packed.get(key)
+        if hit is not None and hit[0] == ver and hit[1].device == w.device:
+            return hit[1]
+        n_out, k = w.shape
+        L = _lib.lib()
+        buf = torch.empty(L.rl4co_enc_packed_bytes(n_out, k), dtype=torch.uint8, device=w.device)
+        _lib.check(L.rl4co_enc_pack_weight(_lib.ptr(w.detach().contiguous()), n_out, k, _lib.ptr(buf), _lib.stream_ptr()),
+                   "rl4co_enc_pack_weight")
+        self._packed[key] = (ver, buf)
+        return buf
+
+    def _linear(self, x, lin, epi, out_ch, residual=None, norm=None):
+        L = _lib.lib()
+        B, n, k = x.shape
+        y = torch.empty(B, n, out_ch, dtype=torch.float32, device=x.device)
+        nrm = norm.normalizer if norm is not None else None
+        _lib.check(L.rl4co_enc_linear(
+            _lib.ptr(x), _lib.ptr(self._pack(lin.weight)), _lib.ptr(lin.bias.detach()),
+            _lib.ptr(residual), _lib.ptr(nrm.weight.detach() if nrm is not None else None),
+            _lib.ptr(nrm.bias.detach() if nrm is not None else None), C.c_float(nrm.eps if nrm is not None else 0.0),
+            _lib.ptr(y), C.c_int64(B), n, k, out_ch, epi, _lib.stream_ptr()), "rl4co_enc_linear")
+        return y
+
+    def _forward_kernels(self, x):
+        L = _lib.lib()
+        x = x.contiguous()
+        B, n, E = x.shape
+        for layer in self.layers:
+            mha, norm1, mlp, norm2 = layer[0].module, layer[1], layer[2].module, layer[3]
+            qkv = self._linear(x, mha.Wqkv, _lib.ENC_EPI_PLAIN, 3 * E)
+            heads = torch.empty(B, n, E, dtype=torch.float32, device=x.device)
+            _lib.check(L.rl4co_enc_attention(_lib.ptr(qkv), _lib.ptr(heads), C.c_int64(B), n, _lib.stream_ptr()),
+                       "rl4co_enc_attention")
+            x = self._linear(heads, mha.out_proj, _lib.ENC_EPI_RES_NORM, E, residual=x, norm=norm1)
+            f = self._linear(x, mlp.lins[0], _lib.ENC_EPI_RELU, self.feedforward_hidden)
+            x = self._linear(f, mlp.lins[1], _lib.ENC_EPI_RES_NORM, E, residual=x, norm=norm2)
+        return x
+
     def forward(self, x):
+        if self.kernels_apply(x):
+            return self._forward_kernels(x)
         return self.layers(x)
 
 

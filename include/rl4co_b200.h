@@ -190,6 +190,24 @@ int rl4co_tc_decode_step(int32_t env, const rl4co_cache* cache, const int64_t* f
                          const float* vehicle_capacity, const uint8_t* mask, float* logits_out,
                          float* dbg_scores, float* dbg_heads, int32_t* err, int64_t rows, void* stream);
 
+/* ---- Graph-attention encoder (the caller of the rollout path) on tcgen05 -----------------
+ * rl/zoo/am/encoder.py:70-91 -> nn/graph/attnnet.py:16-103: per layer
+ *   qkv = h Wqkv^T + b (attention.py:113) ; a = MHA(qkv) (:114-131) ; h = IN(h + a Wo^T + bo) (attnnet.py:43-49,
+ *   ops.py:32-56) ; h = IN(h + W2 relu(W1 h + b1) + b2) (attnnet.py:50-60).
+ * All tensors fp32, contiguous, [B, n, channels] with n <= 128 nodes; one CTA owns an instance, so the instance
+ * norm (statistics over the node axis) is part of the GEMM epilogue.                                              */
+#define RL4CO_ENC_EPI_PLAIN 0    /* Y = X W^T + bias                                                   */
+#define RL4CO_ENC_EPI_RELU 1     /* Y = relu(X W^T + bias)                                             */
+#define RL4CO_ENC_EPI_RES_NORM 2 /* Y = InstanceNorm(residual + X W^T + bias) * gamma + beta, n_out=128 */
+int64_t rl4co_enc_packed_bytes(int32_t n_out, int32_t k); /* 0 = unsupported (both must be multiples of 128) */
+/* nn.Linear weight W [n_out, k] -> fp16 hi/lo MMA tiles (once per forward / weight version) */
+int rl4co_enc_pack_weight(const float* W, int32_t n_out, int32_t k, void* packed, void* stream);
+int rl4co_enc_linear(const float* X, const void* Wpacked, const float* bias, const float* residual,
+                     const float* gamma, const float* beta, float eps, float* Y, int64_t B, int32_t n,
+                     int32_t k, int32_t n_out, int32_t epilogue, void* stream);
+/* qkv [B, n, 384] = (q | k | v) x (8 heads x 16) -> heads [B, n, 128] (input of out_proj), no mask */
+int rl4co_enc_attention(const float* qkv, float* out, int64_t B, int32_t n, void* stream);
+
 /* counter-noise reference values, for tests: gumbel [rows, n_nodes] at step t */
 int rl4co_noise_gumbel(uint32_t seed, int64_t inst_offset, int64_t B, int32_t t, float* out,
                        int64_t rows, int32_t n_nodes, void* stream);
