@@ -262,8 +262,8 @@ def run_b200(args):
                        "timed": "cache precompute GEMMs + operand pack + persistent tcgen05 rollout kernel"},
             "e2e": {"value": world * isteps * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / K,
-                    "includes": "H2D locs, env.reset, encoder (torch), cache precompute, rollout kernel, "
-                                "D2H reward+log_likelihood+actions"},
+                    "includes": "H2D locs, env.reset, encoder (tcgen05 kernels: 4 GEMMs + attention per layer), "
+                                "cache precompute, rollout kernel, D2H reward+log_likelihood+actions"},
             "gpu_launches": 2 * len(kernel_ms),      # per step: r4::tc::tc_pack_kernel + r4::tc::rollout_tc_kernel
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": measured_traffic(), "peak_source": peak_src,

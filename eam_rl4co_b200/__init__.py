@@ -14,6 +14,7 @@ from .decoding import (DecodingStrategy, Greedy, Sampling, Evaluate, get_decodin
 from .encoder import AttentionModelEncoder
 from .policy import AttentionModelPolicy
 from . import sharding
+from . import train
 
 
 def POMOPolicy(env_name: str = "tsp", **kw) -> AttentionModelPolicy:

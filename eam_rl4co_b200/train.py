@@ -1,0 +1,146 @@
+"""POMO / REINFORCE training step on top of the rollout kernels.
+
+Reference flow (pomo/model.py:89-114, reinforce.py:73-115, baselines.py:57-61): one differentiable
+`policy(td, env, phase="train")` call that samples a multistart rollout while recording log-probabilities,
+then `loss = -((reward - reward.mean(over starts)) * log_likelihood).mean()`.
+
+Here the sampling rollout runs on the fused kernel (no autograd), and the log-likelihood of the sampled
+actions is re-evaluated by `evaluate_log_likelihood`: the same arithmetic as the reference's evaluate mode
+(`decoding.py:452-465`, `constructive/base.py:204-206,221-229`), but teacher-forced over ALL decoding steps at
+once - with the actions known, every step's context (first / current node, remaining capacity) and feasibility
+mask follows from the action prefix, so the T sequential decoder steps become one batched masked attention that
+PyTorch autograd differentiates.  Same actions => same log-likelihood => same gradient as the reference's
+sample-while-recording pass.
+
+Multi-GPU: instances are sharded, the shared baseline is per instance and therefore local,
+and the step ends with ONE flat-buffer all-reduce of gradients + logged sums (`sharding.allreduce_mean_`).
+"""
+import math
+from typing import Dict, Optional
+
+import torch
+import torch.nn.functional as F
+
+from . import sharding
+from .tensordict_lite import batchify
+
+
+def _to_bs(x: torch.Tensor, S: int) -> torch.Tensor:
+    """start-major rows [S*B, ...] -> [B, S, ...] (ops.py:35-56)."""
+    return x.view(S, x.shape[0] // S, *x.shape[1:]).transpose(0, 1)
+
+
+@torch.no_grad()
+def teacher_forced_states(env, td, actions: torch.Tensor, num_starts: int) -> Dict[str, torch.Tensor]:
+    """Replay `actions` [S*B, T] through the env kernels (tsp/env.py:62-88, cvrp/env.py:68-144) and collect what the
+    decoder sees before every step t >= 1: current node, remaining capacity (CVRP) and the feasibility mask.
+    Column 0 is the multistart start action (decoding.py:305-327), taken before the first decoder step."""
+    S = int(num_starts)
+    if S <= 1:
+        raise NotImplementedError("evaluate_log_likelihood covers the multistart form (num_starts > 1)")
+    T = actions.shape[1]
+    cvrp = env.name == "cvrp"
+    tdb = batchify(td, S)
+    tdb.set("action", actions[:, 0].contiguous())
+    tdb = env.step(tdb)["next"]
+    cur, rem, mask = [], [], []
+    for t in range(1, T):
+        cur.append(tdb["current_node"].reshape(-1))
+        mask.append(tdb["action_mask"])
+        if cvrp:
+            rem.append((tdb["vehicle_capacity"] - tdb["used_capacity"]).reshape(-1))
+        tdb.set("action", actions[:, t].contiguous())
+        tdb = env.step(tdb)["next"]
+    out = {"first": _to_bs(actions[:, 0], S), "cur": _to_bs(torch.stack(cur, 1), S),
+           "mask": _to_bs(torch.stack(mask, 1), S), "taken": _to_bs(actions[:, 1:], S), "td": tdb}
+    if cvrp:
+        out["rem"] = _to_bs(torch.stack(rem, 1), S)
+    return out
+
+
+def batched_log_likelihood(decoder, h: torch.Tensor, states: Dict[str, torch.Tensor], tanh_clipping: float = 10.0,
+                           temperature: float = 1.0) -> torch.Tensor:
+    """Differentiable log p(action_t | prefix) for all (instance, start, step) at once -> [B, S, T-1].
+
+    am/decoder.py:133-198 (context -> glimpse query), attention.py:282-328 (masked MHA glimpse, project_out,
+    logits / sqrt(E)), decoding.py:140-190 (tanh clip, mask, temperature, log_softmax).  Pure PyTorch: runs on any
+    device and is what autograd differentiates; `h` is the encoder output with its graph attached."""
+    B, n, E = h.shape
+    H = decoder.num_heads
+    cur, mask, taken = states["cur"], states["mask"], states["taken"]
+    S, Tm = cur.shape[1], cur.shape[2]
+    R = S * Tm
+    Wk, Wv, Wl = decoder.project_node_embeddings.weight.chunk(3, dim=0)           # decoder.py:206-235
+    Wc = decoder.context_embedding.project_context.weight
+    gk, gv, lk = F.linear(h, Wk), F.linear(h, Wv), F.linear(h, Wl)
+    idx = lambda tab, i: tab.gather(1, i.reshape(B, -1, 1).expand(B, i[0].numel(), E))
+    if decoder.env_name == "tsp":                                                  # context.py:118-140
+        pa, pb = F.linear(h, Wc[:, :E]), F.linear(h, Wc[:, E:])
+        q = idx(pa, states["first"]).view(B, S, 1, E) + idx(pb, cur).view(B, S, Tm, E)
+    else:                                                                          # context.py:70-74,143-157
+        pb = F.linear(h, Wc[:, :E])
+        q = idx(pb, cur).view(B, S, Tm, E) + states["rem"].unsqueeze(-1) * Wc[:, E]
+    if decoder.use_graph_context:                                                  # decoder.py:223-224
+        q = q + F.linear(h.mean(1), decoder.project_fixed_context.weight).view(B, 1, 1, E)
+    heads = lambda x, L: x.reshape(B, L, H, E // H).transpose(1, 2)
+    am = mask.reshape(B, 1, R, n)
+    glimpse = F.scaled_dot_product_attention(heads(q, R), heads(gk, n), heads(gv, n), attn_mask=am)
+    glimpse = F.linear(glimpse.transpose(1, 2).reshape(B, R, E), decoder.pointer.project_out.weight)
+    logits = torch.bmm(glimpse, lk.transpose(1, 2)) / math.sqrt(E)                 # attention.py:299-301
+    if tanh_clipping > 0:
+        logits = torch.tanh(logits) * tanh_clipping
+    logits = logits.masked_fill(~mask.reshape(B, R, n), float("-inf")) / temperature
+    logp = F.log_softmax(logits, dim=-1)
+    return logp.gather(-1, taken.reshape(B, R, 1)).view(B, S, Tm)
+
+
+def evaluate_log_likelihood(policy, td, env, actions: torch.Tensor, num_starts: int,
+                            states: Optional[Dict[str, torch.Tensor]] = None) -> torch.Tensor:
+    """log-likelihood [S*B] (start-major, like `policy(...)["log_likelihood"]`) of given multistart `actions`,
+    with the autograd graph to every policy parameter (encoder included: the PyTorch modules run here)."""
+    if states is None:
+        states = teacher_forced_states(env, td, actions, num_starts)
+    with torch.enable_grad():
+        h, _ = policy.encoder(td)
+        logp = batched_log_likelihood(policy.decoder, h, states, policy.tanh_clipping, policy.temperature)
+    return logp.sum(-1).transpose(0, 1).reshape(-1)
+
+
+def reinforce_loss(reward: torch.Tensor, log_likelihood: torch.Tensor, num_starts: int):
+    """pomo/model.py:106-112 + baselines.py:57-61 (shared baseline = mean over the starts of an instance) +
+    reinforce.py:97-106.  reward, log_likelihood: [S*B] start-major.  Returns (loss, advantage [B,S])."""
+    r, ll = _to_bs(reward, num_starts), _to_bs(log_likelihood, num_starts)
+    adv = r - r.mean(dim=1, keepdim=True)
+    return -(adv * ll).mean(), adv
+
+
+def pomo_train_step(policy, env, td, optimizer=None, num_starts: Optional[int] = None, noise_seed: int = 0,
+                    instance_offset: int = 0, max_grad_norm: Optional[float] = 1.0, group=None) -> Dict[str, float]:
+    """One POMO training step on this rank's shard `td`: sampled multistart rollout (fused kernel), differentiable
+    re-evaluation, shared-baseline REINFORCE loss, backward, one all-reduce, clip, optimiser step."""
+    kw = {} if num_starts is None else {"num_starts": num_starts}
+    with torch.no_grad():
+        out = policy(td, env, decode_type="multistart_sampling", noise_seed=noise_seed,
+                     instance_offset=instance_offset, **kw)
+    S = out["actions"].shape[0] // td.batch_size[0]
+    ll = evaluate_log_likelihood(policy, td, env, out["actions"], S)
+    loss, _ = reinforce_loss(out["reward"], ll, S)
+    params = [p for p in policy.parameters() if p.requires_grad]
+    for p in params:
+        p.grad = None
+    loss.backward()
+    grads = []
+    for p in params:
+        if p.grad is None:
+            p.grad = torch.zeros_like(p)
+        grads.append(p.grad)
+    r = _to_bs(out["reward"], S)
+    extras = torch.stack([loss.detach(), r.mean(), r.max(1)[0].mean()])      # logged means (rl/common/base.py:233-240)
+    extras = sharding.allreduce_mean_(grads, extras, group=group)
+    if max_grad_norm is not None:
+        torch.nn.utils.clip_grad_norm_(params, max_grad_norm)
+    if optimizer is not None:
+        optimizer.step()
+    ll_gap = (ll.detach() - out["log_likelihood"]).abs().max()
+    return {"loss": extras[0].item(), "reward": extras[1].item(), "max_reward": extras[2].item(),
+            "ll_gap": ll_gap.item()}

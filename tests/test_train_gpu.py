@@ -1,0 +1,103 @@
+"""GPU: the POMO / REINFORCE training step (eam_rl4co_b200/train.py): states replayed through
+the env kernels, log-likelihood of the kernel-sampled actions re-evaluated with autograd, loss and gradients against
+autograd through the oracle's sequential evaluate (reference: pomo/model.py:89-114, reinforce.py:73-115)."""
+import pytest
+import torch
+
+import eam_rl4co_b200 as P
+from eam_rl4co_b200 import train
+from oracle import rollout_oracle as O
+from helpers import LL_RTOL, inst_to_env_td, rel_close
+from test_train_host import _oracle_states
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _setup(env_name, B, N, seed=0):
+    torch.manual_seed(100 + seed)
+    inst = O.generate_tsp(B, N) if env_name == "tsp" else O.generate_cvrp(B, N)
+    torch.manual_seed(200 + seed)
+    pol = P.POMOPolicy(env_name).to(DEV)
+    env, td = inst_to_env_td(P, env_name, inst, DEV)
+    return inst, pol, env, td
+
+
+@pytest.mark.parametrize("env_name,B,N", [("tsp", 4, 20), ("cvrp", 4, 20), ("tsp", 2, 100), ("cvrp", 2, 50)])
+def test_teacher_forced_states_are_bit_exact(env_name, B, N):
+    inst, pol, env, td = _setup(env_name, B, N)
+    with torch.no_grad():
+        out = pol(td.clone(), env, decode_type="multistart_sampling", noise_seed=3)
+    S = out["actions"].shape[0] // B
+    st = train.teacher_forced_states(env, td.clone(), out["actions"], S)
+    ref = _oracle_states(env_name, inst, out["actions"].cpu(), S)
+    for k in ("first", "cur", "mask", "taken"):
+        assert torch.equal(st[k].cpu(), ref[k]), k
+    if env_name == "cvrp":
+        assert torch.equal(st["rem"].cpu(), ref["rem"])
+
+
+@pytest.mark.parametrize("env_name,B,N", [("tsp", 4, 20), ("cvrp", 3, 20), ("tsp", 2, 100), ("cvrp", 2, 100)])
+def test_evaluate_log_likelihood_matches_the_sampling_kernel(env_name, B, N):
+    torch.backends.cuda.matmul.allow_tf32 = False
+    inst, pol, env, td = _setup(env_name, B, N, seed=1)
+    with torch.no_grad():
+        out = pol(td.clone(), env, decode_type="multistart_sampling", noise_seed=4)
+    S = out["actions"].shape[0] // B
+    ll = train.evaluate_log_likelihood(pol, td.clone(), env, out["actions"], S)
+    assert ll.requires_grad and ll.shape == out["log_likelihood"].shape
+    assert rel_close(ll.detach(), out["log_likelihood"], LL_RTOL)
+
+
+@pytest.mark.parametrize("env_name", ["tsp", "cvrp"])
+def test_train_step_gradients_match_oracle_autograd(env_name):
+    torch.backends.cuda.matmul.allow_tf32 = False
+    B, N = 3, 12
+    inst, pol, env, td = _setup(env_name, B, N, seed=2)
+    stats = train.pomo_train_step(pol, env, td.clone(), optimizer=None, noise_seed=6, max_grad_norm=None)
+    assert stats["ll_gap"] < 1e-4 and stats["loss"] == stats["loss"]
+    # the same step on the CPU: actions from the kernel, autograd through the oracle (encoder = the torch modules)
+    with torch.no_grad():
+        out = pol(td.clone(), env, decode_type="multistart_sampling", noise_seed=6)
+    S = out["actions"].shape[0] // B
+    cpu = P.POMOPolicy(env_name)
+    cpu.load_state_dict(pol.state_dict())
+    enc_in = dict(inst)
+    if env_name == "cvrp":
+        enc_in = {"locs": torch.cat((inst["depot"][:, None, :], inst["locs"]), 1), "demand": inst["demand"]}
+    h, _ = cpu.encoder(enc_in)
+    w = dict(cpu.decoder.named_parameters())
+    ev = O.rollout(env_name, inst, h, w, actions=out["actions"].cpu(), num_starts=S, use_graph_context=False)
+    loss, _ = O.reinforce_shared_baseline_loss(out["reward"].cpu(), ev["log_likelihood"], S)
+    loss.backward()
+    assert abs(loss.item() - stats["loss"]) <= 1e-4 * max(1.0, abs(loss.item()))
+    checked = 0
+    gmax = max(p.grad.abs().max().item() for p in cpu.parameters() if p.grad is not None)
+    for (k, p_gpu), (_, p_cpu) in zip(pol.named_parameters(), cpu.named_parameters()):
+        if p_cpu.grad is None:
+            continue
+        g, r = p_gpu.grad.cpu(), p_cpu.grad
+        # fp32 GPU vs fp32 CPU reductions; parameters whose exact gradient is zero (biases in front of an
+        # instance norm) hold rounding noise only, hence the floor relative to the largest gradient
+        scale = max(r.abs().max().item(), 1e-3 * gmax)
+        assert (g - r).abs().max().item() / scale < 2e-3, k
+        checked += 1
+    assert checked >= 20
+
+
+def test_train_step_with_optimizer_improves_the_sampled_objective():
+    inst, pol, env, td = _setup("tsp", 16, 20, seed=3)
+    opt = torch.optim.Adam(pol.parameters(), lr=1e-3)
+    before = [p.detach().clone() for p in pol.parameters()]
+    hist = [train.pomo_train_step(pol, env, td.clone(), optimizer=opt, noise_seed=i) for i in range(12)]
+    assert all(h["loss"] == h["loss"] and h["ll_gap"] < 1e-3 for h in hist)
+    assert any(not torch.equal(a, b) for a, b in zip(before, pol.parameters()))
+    # the encoder kernels pick up the updated weights (packed tiles are cached per parameter version)
+    with torch.no_grad():
+        net = pol.encoder.net
+        hk, _ = pol.encoder(td)
+        net.use_kernels = False
+        ht, _ = pol.encoder(td)
+        net.use_kernels = True
+    assert (hk - ht).abs().max().item() < 1e-4
+    assert sum(h["reward"] for h in hist[-4:]) / 4 > sum(h["reward"] for h in hist[:4]) / 4 - 0.05
