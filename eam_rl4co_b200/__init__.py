@@ -15,6 +15,8 @@ from .encoder import AttentionModelEncoder
 from .policy import AttentionModelPolicy
 from . import sharding
 from . import train
+from . import pomo
+from .pomo import StateAugmentation, best_of_starts, pomo_evaluate
 
 
 def POMOPolicy(env_name: str = "tsp", **kw) -> AttentionModelPolicy:

@@ -208,6 +208,15 @@ int rl4co_enc_linear(const float* X, const void* Wpacked, const float* bias, con
 /* qkv [B, n, 384] = (q | k | v) x (8 heads x 16) -> heads [B, n, 128] (input of out_proj), no mask */
 int rl4co_enc_attention(const float* qkv, float* out, int64_t B, int32_t n, void* stream);
 
+/* ---- POMO evaluation reduction after the rollout - pomo/model.py:115-145 (unbatchify ops.py:35-56, gather :59-71) ----
+ * reward [S*A*B] / actions [S*A*B, T] (nullable) of a multistart rollout over an A-fold augmented batch, rows start-major
+ * (row = s*A*B + a*B + b).  Outputs: max_reward [B,A], best_start [B,A] (first maximum over starts), the winning tours
+ * best_multistart_actions [B,A,T]; then over augmentations (nullable): max_aug_reward [B], best_aug [B],
+ * best_aug_actions [B,T].  n_aug = 1 for an un-augmented batch.                                                       */
+int rl4co_best_of_starts(const float* reward, const int64_t* actions, int64_t B, int32_t n_aug, int32_t n_start,
+                         int32_t T, float* max_reward, int64_t* best_start, int64_t* best_multistart_actions,
+                         float* max_aug_reward, int64_t* best_aug, int64_t* best_aug_actions, void* stream);
+
 /* counter-noise reference values, for tests: gumbel [rows, n_nodes] at step t */
 int rl4co_noise_gumbel(uint32_t seed, int64_t inst_offset, int64_t B, int32_t t, float* out,
                        int64_t rows, int32_t n_nodes, void* stream);
