@@ -16,6 +16,8 @@ from .policy import AttentionModelPolicy
 from . import sharding
 from . import train
 from . import pomo
+from . import data
+from .data import DeviceGenerator, load_data, load_npz_to_tensordict, save_tensordict_to_npz
 from .pomo import StateAugmentation, best_of_starts, pomo_evaluate
 
 

@@ -11,7 +11,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librl4co_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["capi.cu", "env_kernels.cu", "decode_kernels.cu", "rollout_kernel.cu", "rollout_tc.cu", "encoder_tc.cu", "reduce_kernels.cu"]
+SOURCES = ["capi.cu", "env_kernels.cu", "decode_kernels.cu", "rollout_kernel.cu", "rollout_tc.cu", "encoder_tc.cu", "reduce_kernels.cu", "data_kernels.cu"]
 
 ENV_TSP, ENV_CVRP = 0, 1
 MODE_GREEDY, MODE_SAMPLING, MODE_EVALUATE = 0, 1, 2
@@ -32,7 +32,7 @@ EXPORTS = [
     "rl4co_b200_abi_version", "rl4co_last_error", "rl4co_tsp_step", "rl4co_cvrp_step_mask",
     "rl4co_cvrp_action_mask", "rl4co_tour_reward", "rl4co_select", "rl4co_decode_step",
     "rl4co_rollout", "rl4co_noise_gumbel", "rl4co_tc_image_bytes", "rl4co_tc_pack", "rl4co_tc_decode_step",
-    "rl4co_enc_packed_bytes", "rl4co_enc_pack_weight", "rl4co_enc_linear", "rl4co_enc_attention", "rl4co_best_of_starts",
+    "rl4co_enc_packed_bytes", "rl4co_enc_pack_weight", "rl4co_enc_linear", "rl4co_enc_attention", "rl4co_best_of_starts", "rl4co_generate_instances",
 ]
 
 

@@ -217,6 +217,12 @@ int rl4co_best_of_starts(const float* reward, const int64_t* actions, int64_t B,
                          int32_t T, float* max_reward, int64_t* best_start, int64_t* best_multistart_actions,
                          float* max_aug_reward, int64_t* best_aug, int64_t* best_aug_actions, void* stream);
 
+/* ---- on-device instance generation: the input spec of tsp/generator.py:53-62 and cvrp/generator.py:120-147 -----------
+ * locs [B, n_loc, 2] uniform in [0,1); CVRP also depot [B,2] and demand [B, n_loc] = integer 1..9 / capacity.  Values come
+ * from the counter hash keyed (seed, inst_offset + b, element), so shards of a global batch agree with the whole.   */
+int rl4co_generate_instances(int32_t env, uint32_t seed, int64_t inst_offset, int64_t B, int32_t n_loc,
+                             float capacity, float* locs, float* depot, float* demand, void* stream);
+
 /* counter-noise reference values, for tests: gumbel [rows, n_nodes] at step t */
 int rl4co_noise_gumbel(uint32_t seed, int64_t inst_offset, int64_t B, int32_t t, float* out,
                        int64_t rows, int32_t n_nodes, void* stream);
