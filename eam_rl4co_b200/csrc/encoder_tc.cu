@@ -30,16 +30,21 @@ constexpr uint32_t kSBO = 16 * kLBO;        // 16 chunks = 128 channels per 8-ro
 constexpr uint32_t kHalf = (kRows / 8) * kSBO;   // 32 KB: the hi (or lo) half of a 128 x 128 tile
 constexpr uint32_t kTile = 2 * kHalf;       // 64 KB
 constexpr int kStage = 132;                 // fp32 staging row stride (floats): 16-byte row writes are conflict-free
+constexpr int kRing = 36;                   // store slot row stride: 32 output columns + 16 B pad (same bank argument)
 
 enum { EPI_PLAIN = 0, EPI_RELU = 1, EPI_RES_NORM = 2 };
 
 struct Smem {
     uint64_t tma_bar[2];
     uint64_t mma_bar[2];
+    uint64_t kdone_bar;    // the MMAs of a K block are complete (K > 128 only): its A tile may be overwritten
+    uint64_t done_bar;     // all MMAs of the instance are complete
     uint32_t tmem_ptr;
     uint32_t pad_;
-    float mean[kRows];
-    float rstd[kRows];
+    int next_chunk[2][4];  // [instance parity][TMEM lane quadrant]: next 32-column chunk of the epilogue to drain
+    alignas(16) float mean[kRows];
+    alignas(16) float rstd[kRows];
+    alignas(16) float part[2][4 * kRows];   // per-warp partial column sums (mean pass, variance pass)
 };
 constexpr uint32_t kOffX = 0, kOffW = kTile, kOffS = 3 * kTile;
 constexpr size_t kSmemBytes = kOffS + sizeof(Smem);
@@ -67,15 +72,16 @@ __global__ void __launch_bounds__(256) enc_pack_weight_kernel(const float* __res
 }
 
 // ---- activations: rows [0,n) of X[b] (fp32, row stride K), channels [128 kb, 128 kb + 128) -> A tile hi/lo ------
-// A warp pass covers 8 rows x 4 chunks: lanes write 512 contiguous bytes (conflict-free), read whole 32-byte sectors.
+// Run by the four producer warps (4..7).  A warp pass covers 8 rows x 4 chunks: lanes write 512 contiguous bytes
+// (conflict-free) and read whole 32-byte sectors.
 __device__ __forceinline__ void convert_x(const float* __restrict__ Xb, int n, int K, int kb, unsigned char* xs) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int pw = (threadIdx.x >> 5) - 4, lane = threadIdx.x & 31;
 #pragma unroll
-    for (int half = 0; half < 2; ++half) {
+    for (int part = 0; part < 4; ++part) {
         float4 a[4], b[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const int v = (half * 4 + i) * 8 + warp;          // 64 warp passes over 8 warps
+            const int v = (part * 4 + i) * 4 + pw;            // 64 warp passes over 4 warps
             const int r = 8 * (v >> 2) + (lane & 7), c = 4 * (v & 3) + (lane >> 3);
             a[i] = make_float4(0.f, 0.f, 0.f, 0.f);
             b[i] = a[i];
@@ -87,7 +93,7 @@ __device__ __forceinline__ void convert_x(const float* __restrict__ Xb, int n, i
         }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const int v = (half * 4 + i) * 8 + warp;
+            const int v = (part * 4 + i) * 4 + pw;
             const int rg = v >> 2, c = 4 * (v & 3) + (lane >> 3);
             uint32_t h[4], l[4];
             split2(a[i].x, a[i].y, h[0], l[0]);
@@ -118,9 +124,18 @@ __device__ __forceinline__ void issue_tile(uint32_t tmem, uint32_t dcol, uint32_
     }
 }
 
+#ifdef R4_ENC_PROF
+__device__ long long g_enc_prof[16];
+#define ENC_STAMP(k) do { if (blockIdx.x == 0 && threadIdx.x == PROF_T) { const long long now__ = clock64(); g_enc_prof[k] += now__ - tprev; tprev = now__; } } while (0)
+#else
+#define ENC_STAMP(k) do { } while (0)
+#endif
+
 // ---- Y[b] = epilogue(X[b] W^T + bias): one CTA per instance at a time, persistent over the batch ----------------
 // Tiles are walked K-block outer, N-block inner (the order enc_pack_weight_kernel stores them); the accumulators of
-// all N blocks stay in TMEM (n_out <= 512 columns), so X is read once.
+// all N blocks stay in TMEM (n_out <= 512 columns), so X is read once.  Warps 0..3 are the epilogue warps (one TMEM
+// lane quadrant each), warps 4..7 the producers: while the epilogue of instance b drains TMEM, the producers already
+// convert the A tile of instance b+1, and one elected producer lane streams the W tiles (TMA) and issues the MMAs.
 template <int EPI>
 __global__ void __launch_bounds__(kThreads, 1)
     enc_linear_kernel(const float* __restrict__ X, const unsigned char* __restrict__ Wp, const float* __restrict__ bias,
@@ -136,6 +151,9 @@ __global__ void __launch_bounds__(kThreads, 1)
             mbar_init(&s->tma_bar[i], 1);
             mbar_init(&s->mma_bar[i], 1);
         }
+        mbar_init(&s->kdone_bar, 1);
+        mbar_init(&s->done_bar, 1);
+        for (int i = 0; i < 8; ++i) s->next_chunk[i >> 2][i & 3] = 0;
         fence_mbar_init();
     }
     __syncwarp();
@@ -146,117 +164,181 @@ __global__ void __launch_bounds__(kThreads, 1)
     const uint32_t tmem = s->tmem_ptr;
     const uint32_t xs_a = smem_u32(xs), ws_a = smem_u32(wsm);
     const int nK = K / 128, nN = n_out / 128, T = nK * nN;
-    uint32_t use_tma[2] = {0u, 0u}, use_mma[2] = {0u, 0u};   // phases consumed per buffer (same in every thread)
-    const int q = warp & 3, hlf = warp >> 2, row = 32 * q + lane;
-    const uint32_t lane_base = tmem + ((uint32_t)(32 * q) << 16);
+    const bool producer = warp >= 4;
+    // phase counters (the same in every thread; tma/mma ones matter to the issuing lane only)
+    uint32_t n_tma0 = 0, n_tma1 = 0, n_mma0 = 0, n_mma1 = 0, n_kdone = 0, n_done = 0;
+    bool tile0_in_flight = false;   // issuing lane: W tile 0 of this instance was requested during the last epilogue
+    const int row = 32 * (warp & 3) + lane;                 // TMEM lane = node row (warps w and w+4 share a quadrant)
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * (warp & 3)) << 16);
 
+    if (producer && (int64_t)blockIdx.x < B) convert_x(X + (int64_t)blockIdx.x * n * K, n, K, 0, xs);
+    fence_proxy_async();
+    __syncthreads();
+
+#ifdef R4_ENC_PROF
+    constexpr int PROF_T = 0;
+    long long tprev = clock64();
+#endif
     for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
         const float* Xb = X + b * (int64_t)n * K;
-        if (warp == 0) {
-            if (elect_one()) {
-                mbar_expect_tx(&s->tma_bar[0], kTile);
-                bulk_g2s(wsm, Wp, kTile, &s->tma_bar[0]);
-            }
-            __syncwarp();
-        }
-        for (int t = 0; t < T; ++t) {
-            const int kb = t / nN, nb = t - kb * nN, buf = t & 1;
-            if (nb == 0) {
-                if (kb > 0) {   // the MMAs of the previous K block still read the A tile
-                    // (barrier first: a parity wait is only meaningful for a thread at most one phase behind, and
-                    // the warps that issue nothing run ahead of the issuing warp)
-                    __syncthreads();
-                    mbar_wait(&s->mma_bar[buf ^ 1], (use_mma[buf ^ 1] - 1u) & 1u);
-                    tc_fence_after();
-                }
-                convert_x(Xb, n, K, kb, xs);
+        for (int kb = 0; kb < nK; ++kb) {
+            if (kb > 0) {   // the MMAs of the previous K block read the A tile: wait, then convert the next block
+                mbar_wait(&s->kdone_bar, n_kdone & 1u);
+                ++n_kdone;
+                tc_fence_after();
+                if (producer) convert_x(Xb, n, K, kb, xs);
                 fence_proxy_async();
                 __syncthreads();
             }
-            if (warp == 0) {
+            if (warp == 4) {
                 if (elect_one()) {
-                    if (t + 1 < T) {   // next W tile into the other buffer once its previous reader (tile t-1) is done
-                        if (t >= 1) mbar_wait(&s->mma_bar[buf ^ 1], (use_mma[buf ^ 1] - 1u) & 1u);
-                        mbar_expect_tx(&s->tma_bar[buf ^ 1], kTile);
-                        bulk_g2s(wsm + (size_t)(buf ^ 1) * kTile, Wp + (size_t)(t + 1) * kTile, kTile,
-                                 &s->tma_bar[buf ^ 1]);
+                    for (int nb = 0; nb < nN; ++nb) {
+                        const int t = kb * nN + nb, buf = t & 1;
+                        if (t == 0 && !tile0_in_flight) {
+                            mbar_expect_tx(&s->tma_bar[0], kTile);
+                            bulk_g2s(wsm, Wp, kTile, &s->tma_bar[0]);
+                        }
+                        if (t + 1 < T) {   // next W tile into the other buffer once its previous reader (tile t-1) is done
+                            if (t >= 1) {
+                                mbar_wait(&s->mma_bar[buf ^ 1], ((buf ? n_mma0 : n_mma1) - 1u) & 1u);
+                            }
+                            mbar_expect_tx(&s->tma_bar[buf ^ 1], kTile);
+                            bulk_g2s(wsm + (size_t)(buf ^ 1) * kTile, Wp + (size_t)(t + 1) * kTile, kTile,
+                                     &s->tma_bar[buf ^ 1]);
+                        }
+                        mbar_wait(&s->tma_bar[buf], (buf ? n_tma1 : n_tma0) & 1u);
+                        tc_fence_after();
+                        issue_tile(tmem, (uint32_t)nb * 128u, xs_a, ws_a + (uint32_t)buf * kTile, kb == 0);
+                        tc_commit(&s->mma_bar[buf]);
+                        if (buf) { ++n_tma1; ++n_mma1; } else { ++n_tma0; ++n_mma0; }
                     }
-                    mbar_wait(&s->tma_bar[buf], use_tma[buf] & 1u);
-                    tc_fence_after();
-                    issue_tile(tmem, (uint32_t)nb * 128u, xs_a, ws_a + (uint32_t)buf * kTile, kb == 0);
-                    tc_commit(&s->mma_bar[buf]);
+                    tc_commit(kb + 1 < nK ? &s->kdone_bar : &s->done_bar);
                 }
                 __syncwarp();
             }
-            use_tma[buf]++;
-            use_mma[buf]++;
         }
-        // every MMA of the instance is complete when the last commit arrives (barrier first, as above)
-        __syncthreads();
-        mbar_wait(&s->mma_bar[(T - 1) & 1], (use_mma[(T - 1) & 1] - 1u) & 1u);
+        ENC_STAMP(0);
+        mbar_wait(&s->done_bar, n_done & 1u);
+        ++n_done;
         tc_fence_after();
+        ENC_STAMP(1);
 
-        if (EPI != EPI_RES_NORM) {
-            float* Yb = Y + b * (int64_t)n * n_out;
-            for (int nb = 0; nb < nN; ++nb) {
-#pragma unroll
-                for (int cc = 0; cc < 64; cc += 16) {
-                    const int col = nb * 128 + hlf * 64 + cc;
-                    uint32_t v[16];
-                    tmem_ld16(lane_base + (uint32_t)col, v);
-                    tc_wait_ld();
-                    if (row < n) {
-#pragma unroll
-                        for (int i = 0; i < 16; i += 4) {
-                            const float4 bb = *reinterpret_cast<const float4*>(bias + col + i);
-                            float4 o = make_float4(__uint_as_float(v[i]) + bb.x, __uint_as_float(v[i + 1]) + bb.y,
-                                                   __uint_as_float(v[i + 2]) + bb.z, __uint_as_float(v[i + 3]) + bb.w);
-                            if (EPI == EPI_RELU)
-                                o = make_float4(fmaxf(o.x, 0.f), fmaxf(o.y, 0.f), fmaxf(o.z, 0.f), fmaxf(o.w, 0.f));
-                            *reinterpret_cast<float4*>(Yb + (size_t)row * n_out + col + i) = o;
-                        }
+        if (producer) {
+            // A tile of the next instance while the epilogue warps drain TMEM (all MMAs that read xs are complete);
+            // its first W tile too when W buffer 0 is not part of the epilogue's staging area
+            const int64_t bn = b + gridDim.x;
+            if (EPI != EPI_RES_NORM && warp == 4) {
+                if (elect_one()) {
+                    tile0_in_flight = bn < B;
+                    if (tile0_in_flight) {
+                        mbar_expect_tx(&s->tma_bar[0], kTile);
+                        bulk_g2s(wsm, Wp, kTile, &s->tma_bar[0]);
                     }
                 }
+                __syncwarp();
             }
-        } else {
+            if (bn < B) convert_x(X + bn * (int64_t)n * K, n, K, 0, xs);
+            fence_proxy_async();
+        }
+        if (EPI != EPI_RES_NORM) {
+            // TMEM -> registers -> (+bias, relu) -> the warp's staging slot (thread = row) -> coalesced stores (8 lanes
+            // per 128-byte row segment).  Lane-per-row stores straight from registers cost one L1 transaction per
+            // 16 bytes and made this epilogue 70 % of the kernel; through the slot it is one per 128 bytes.  A warp
+            // only reads rows its own lanes wrote: __syncwarp is the only synchronisation.  The phase is latency
+            // bound, so both warps of a lane quadrant pull 32-column chunks from a shared counter (the producer warp
+            // joins when its conversion is done).
+            float* slot = reinterpret_cast<float*>(wsm + kTile) + warp * 32 * kRing;
+            float* Yb = Y + b * (int64_t)n * n_out;
+            const int sub = lane >> 3, piece = lane & 7, q = warp & 3;
+            for (;;) {
+                int c = 0;
+                if (lane == 0) c = atomicAdd(&s->next_chunk[n_done & 1u][q], 1);
+                c = __shfl_sync(kFull, c, 0);
+                const int c32 = 32 * c;
+                if (c32 >= n_out) break;
+                uint32_t v0[16], v1[16];
+                tmem_ld16(lane_base + (uint32_t)c32, v0);
+                tmem_ld16(lane_base + (uint32_t)c32 + 16u, v1);
+                tc_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 16; i += 4) {
+                    const float4 b0 = *reinterpret_cast<const float4*>(bias + c32 + i);
+                    const float4 b1 = *reinterpret_cast<const float4*>(bias + c32 + 16 + i);
+                    float4 o0 = make_float4(__uint_as_float(v0[i]) + b0.x, __uint_as_float(v0[i + 1]) + b0.y,
+                                            __uint_as_float(v0[i + 2]) + b0.z, __uint_as_float(v0[i + 3]) + b0.w);
+                    float4 o1 = make_float4(__uint_as_float(v1[i]) + b1.x, __uint_as_float(v1[i + 1]) + b1.y,
+                                            __uint_as_float(v1[i + 2]) + b1.z, __uint_as_float(v1[i + 3]) + b1.w);
+                    if (EPI == EPI_RELU) {
+                        o0 = make_float4(fmaxf(o0.x, 0.f), fmaxf(o0.y, 0.f), fmaxf(o0.z, 0.f), fmaxf(o0.w, 0.f));
+                        o1 = make_float4(fmaxf(o1.x, 0.f), fmaxf(o1.y, 0.f), fmaxf(o1.z, 0.f), fmaxf(o1.w, 0.f));
+                    }
+                    *reinterpret_cast<float4*>(slot + lane * kRing + i) = o0;
+                    *reinterpret_cast<float4*>(slot + lane * kRing + 16 + i) = o1;
+                }
+                __syncwarp();
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                    const int r = 4 * it + sub, grow = 32 * q + r;
+                    const float4 o = *reinterpret_cast<const float4*>(slot + r * kRing + 4 * piece);
+                    if (grow < n) *reinterpret_cast<float4*>(Yb + (size_t)grow * n_out + c32 + 4 * piece) = o;
+                }
+                __syncwarp();
+            }
+        } else if (!producer) {
             // residual + InstanceNorm over the node axis (nn/ops.py:48-49; biased variance, eps inside the sqrt)
             float* st = reinterpret_cast<float*>(wsm);   // [128][kStage] fp32: the W buffers are idle now
             const float* Rb = R + b * (int64_t)n * 128;
-#pragma unroll
-            for (int cc = 0; cc < 64; cc += 16) {
-                const int col = hlf * 64 + cc;
+#pragma unroll 2
+            for (int col = 0; col < 128; col += 16) {
                 uint32_t v[16];
                 tmem_ld16(lane_base + (uint32_t)col, v);
                 tc_wait_ld();
 #pragma unroll
                 for (int i = 0; i < 16; i += 4) {
-                    float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (row < n) {
-                        const float4 bb = *reinterpret_cast<const float4*>(bias + col + i);
-                        const float4 rr = *reinterpret_cast<const float4*>(Rb + (size_t)row * 128 + col + i);
-                        o = make_float4(rr.x + (__uint_as_float(v[i]) + bb.x), rr.y + (__uint_as_float(v[i + 1]) + bb.y),
-                                        rr.z + (__uint_as_float(v[i + 2]) + bb.z), rr.w + (__uint_as_float(v[i + 3]) + bb.w));
-                    }
-                    *reinterpret_cast<float4*>(st + row * kStage + col + i) = o;
+                    const float4 bb = *reinterpret_cast<const float4*>(bias + col + i);
+                    *reinterpret_cast<float4*>(st + row * kStage + col + i) =
+                        make_float4(__uint_as_float(v[i]) + bb.x, __uint_as_float(v[i + 1]) + bb.y,
+                                    __uint_as_float(v[i + 2]) + bb.z, __uint_as_float(v[i + 3]) + bb.w);
                 }
             }
-            __syncthreads();
-            if (threadIdx.x < 128) {
-                const int c = threadIdx.x;
-                float sum = 0.f;
-                for (int r = 0; r < n; ++r) sum += st[r * kStage + c];
-                const float mean = sum / (float)n;
-                float sq = 0.f;
-                for (int r = 0; r < n; ++r) {
-                    const float d = st[r * kStage + c] - mean;
-                    sq = fmaf(d, d, sq);
+            bar_sync(1, 128);                            // the four epilogue warps
+            {
+                // column statistics, two passes (mean, then biased variance).  A warp takes every fourth node row
+                // and a lane four channels: the residual rows are read as coalesced 512-byte segments, all of a
+                // warp's loads are in flight together, and the four partial sums meet in shared memory.
+                float* part = s->part[0];
+                const int c4 = 4 * lane;
+                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+                for (int r = warp; r < n; r += 4) {
+                    const float4 rr = *reinterpret_cast<const float4*>(Rb + (size_t)r * 128 + c4);
+                    float4 v = *reinterpret_cast<const float4*>(st + r * kStage + c4);
+                    v = make_float4(rr.x + v.x, rr.y + v.y, rr.z + v.z, rr.w + v.w);
+                    *reinterpret_cast<float4*>(st + r * kStage + c4) = v;
+                    acc = make_float4(acc.x + v.x, acc.y + v.y, acc.z + v.z, acc.w + v.w);
                 }
+                *reinterpret_cast<float4*>(part + warp * 128 + c4) = acc;
+                bar_sync(1, 128);
+                const int c = threadIdx.x;
+                const float mean = ((part[c] + part[128 + c]) + (part[256 + c] + part[384 + c])) / (float)n;
                 s->mean[c] = mean;
+                bar_sync(1, 128);
+                const float4 m4 = *reinterpret_cast<const float4*>(s->mean + c4);
+                acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+                for (int r = warp; r < n; r += 4) {
+                    const float4 v = *reinterpret_cast<const float4*>(st + r * kStage + c4);
+                    const float dx = v.x - m4.x, dy = v.y - m4.y, dz = v.z - m4.z, dw = v.w - m4.w;
+                    acc = make_float4(fmaf(dx, dx, acc.x), fmaf(dy, dy, acc.y), fmaf(dz, dz, acc.z), fmaf(dw, dw, acc.w));
+                }
+                *reinterpret_cast<float4*>(part + 512 + warp * 128 + c4) = acc;
+                bar_sync(1, 128);
+                const float sq = (part[512 + c] + part[640 + c]) + (part[768 + c] + part[896 + c]);
                 s->rstd[c] = rsqrtf(sq / (float)n + eps);
             }
-            __syncthreads();
+            bar_sync(1, 128);
             float* Yb = Y + b * (int64_t)n * 128;
-            for (int idx = threadIdx.x; idx < n * 32; idx += kThreads) {
+            for (int idx = threadIdx.x; idx < n * 32; idx += 128) {
                 const int r = idx >> 5, c4 = (idx & 31) * 4;
                 const float4 xv = *reinterpret_cast<const float4*>(st + r * kStage + c4);
                 const float4 g = *reinterpret_cast<const float4*>(gamma + c4);
@@ -270,88 +352,121 @@ __global__ void __launch_bounds__(kThreads, 1)
             }
             fence_proxy_async();   // the staging area is the next instance's TMA destination
         }
+        ENC_STAMP(2);
+        // the other parity's counters were last used one instance ago: reset them for the next one
+        if (threadIdx.x < 4) s->next_chunk[(n_done & 1u) ^ 1u][threadIdx.x] = 0;
         tc_fence_before();
         __syncthreads();
+        ENC_STAMP(3);
     }
     if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
 // ---- multi-head self-attention of one instance, fp32 on the CUDA cores (nn/attention.py:66-136) -------------------
 // qkv [n, 384] = (q | k | v) x (8 heads x 16); out [n, 128] = heads concatenated (the input of out_proj).  No mask
-// (the encoder attends over all nodes).  K and V of the instance sit in shared memory; a thread owns (row, head)
-// tasks and runs an online softmax over the keys, four keys per maximum update.
-constexpr int kAttnThreads = 256;
+// (the encoder attends over all nodes).  K and V of the instance sit in shared memory; a thread owns (head, two
+// rows) tasks and runs an online softmax over the keys, four keys per maximum update.  The kernel is bound by the
+// shared-memory pipe (a 128-bit broadcast load still costs four passes), hence two query rows per K / V load.
+constexpr int kAttnMaxThreads = 512;
+constexpr int kRPT = 2;   // query rows per thread
 
-__global__ void __launch_bounds__(kAttnThreads) enc_attention_kernel(const float* __restrict__ qkv,
-                                                                      float* __restrict__ out, int64_t B, int n) {
+__global__ void __launch_bounds__(kAttnMaxThreads) enc_attention_kernel(const float* __restrict__ qkv,
+                                                                         float* __restrict__ out, int64_t B, int n) {
     extern __shared__ __align__(16) float kv[];    // K [n][128] then V [n][128]
     float* Ks = kv;
     float* Vs = kv + (size_t)n * 128;
     const float kScale = 0.25f * 1.4426950408889634f;   // 1/sqrt(16), exponentials in base 2
+    const int npair = (n + kRPT - 1) / kRPT;
     for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
         const float* base = qkv + b * (int64_t)n * 384;
         __syncthreads();
-        for (int i = threadIdx.x; i < n * 32; i += kAttnThreads) {
+        for (int i = threadIdx.x; i < n * 32; i += blockDim.x) {
             const int r = i >> 5, c4 = (i & 31) * 4;
             *reinterpret_cast<float4*>(Ks + r * 128 + c4) = *reinterpret_cast<const float4*>(base + (size_t)r * 384 + 128 + c4);
             *reinterpret_cast<float4*>(Vs + r * 128 + c4) = *reinterpret_cast<const float4*>(base + (size_t)r * 384 + 256 + c4);
         }
         __syncthreads();
-        // lanes of a warp take consecutive rows of the SAME head: their K / V reads are warp-wide broadcasts
-        for (int task = threadIdx.x; task < n * 8; task += kAttnThreads) {
-            const int h = task / n, r = task - h * n;
-            float q[16], acc[16];
+        // lanes of a warp take consecutive row pairs of the SAME head: their K / V reads are warp-wide broadcasts
+        for (int task = threadIdx.x; task < npair * 8; task += blockDim.x) {
+            const int h = task / npair, r0 = kRPT * (task - h * npair);
+            float q[kRPT][16], acc[kRPT][16], m[kRPT], l[kRPT];
 #pragma unroll
-            for (int i = 0; i < 16; i += 4) {
-                const float4 t = *reinterpret_cast<const float4*>(base + (size_t)r * 384 + 16 * h + i);
-                q[i] = t.x * kScale; q[i + 1] = t.y * kScale; q[i + 2] = t.z * kScale; q[i + 3] = t.w * kScale;
+            for (int a = 0; a < kRPT; ++a) {
+                const int r = min(r0 + a, n - 1);
+#pragma unroll
+                for (int i = 0; i < 16; i += 4) {
+                    const float4 t = *reinterpret_cast<const float4*>(base + (size_t)r * 384 + 16 * h + i);
+                    q[a][i] = t.x * kScale; q[a][i + 1] = t.y * kScale; q[a][i + 2] = t.z * kScale; q[a][i + 3] = t.w * kScale;
+                }
+#pragma unroll
+                for (int i = 0; i < 16; ++i) acc[a][i] = 0.f;
+                m[a] = -INFINITY;
+                l[a] = 0.f;
             }
-#pragma unroll
-            for (int i = 0; i < 16; ++i) acc[i] = 0.f;
-            float m = -INFINITY, l = 0.f;
             for (int j0 = 0; j0 < n; j0 += 4) {
-                float sc[4];
+                float sc[kRPT][4];
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
-                    const int jj = min(j0 + u, n - 1);
-                    const float* kr = Ks + jj * 128 + 16 * h;
-                    float d0 = 0.f, d1 = 0.f;
+                    const float* kr = Ks + min(j0 + u, n - 1) * 128 + 16 * h;
+                    float d[kRPT][2];
+#pragma unroll
+                    for (int a = 0; a < kRPT; ++a) d[a][0] = d[a][1] = 0.f;
 #pragma unroll
                     for (int i = 0; i < 16; i += 4) {
                         const float4 t = *reinterpret_cast<const float4*>(kr + i);
-                        d0 = fmaf(q[i], t.x, d0);
-                        d1 = fmaf(q[i + 1], t.y, d1);
-                        d0 = fmaf(q[i + 2], t.z, d0);
-                        d1 = fmaf(q[i + 3], t.w, d1);
-                    }
-                    sc[u] = (j0 + u < n) ? d0 + d1 : -INFINITY;
-                }
-                const float mn = fmaxf(fmaxf(m, fmaxf(sc[0], sc[1])), fmaxf(sc[2], sc[3]));
-                const float corr = ex2_approx(m - mn);     // exp2(-inf) = 0 on the first block
-                m = mn;
-                l *= corr;
 #pragma unroll
-                for (int i = 0; i < 16; ++i) acc[i] *= corr;
+                        for (int a = 0; a < kRPT; ++a) {
+                            d[a][0] = fmaf(q[a][i], t.x, d[a][0]);
+                            d[a][1] = fmaf(q[a][i + 1], t.y, d[a][1]);
+                            d[a][0] = fmaf(q[a][i + 2], t.z, d[a][0]);
+                            d[a][1] = fmaf(q[a][i + 3], t.w, d[a][1]);
+                        }
+                    }
+#pragma unroll
+                    for (int a = 0; a < kRPT; ++a) sc[a][u] = (j0 + u < n) ? d[a][0] + d[a][1] : -INFINITY;
+                }
+                float p[kRPT][4];
+#pragma unroll
+                for (int a = 0; a < kRPT; ++a) {
+                    const float mn = fmaxf(fmaxf(m[a], fmaxf(sc[a][0], sc[a][1])), fmaxf(sc[a][2], sc[a][3]));
+                    const float corr = ex2_approx(m[a] - mn);     // exp2(-inf) = 0 on the first block
+                    m[a] = mn;
+                    l[a] *= corr;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) acc[a][i] *= corr;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        p[a][u] = ex2_approx(sc[a][u] - mn);
+                        l[a] += p[a][u];
+                    }
+                }
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
-                    const float p = ex2_approx(sc[u] - mn);
-                    l += p;
                     const float* vr = Vs + min(j0 + u, n - 1) * 128 + 16 * h;
 #pragma unroll
                     for (int i = 0; i < 16; i += 4) {
                         const float4 t = *reinterpret_cast<const float4*>(vr + i);
-                        acc[i] = fmaf(p, t.x, acc[i]);
-                        acc[i + 1] = fmaf(p, t.y, acc[i + 1]);
-                        acc[i + 2] = fmaf(p, t.z, acc[i + 2]);
-                        acc[i + 3] = fmaf(p, t.w, acc[i + 3]);
+#pragma unroll
+                        for (int a = 0; a < kRPT; ++a) {
+                            acc[a][i] = fmaf(p[a][u], t.x, acc[a][i]);
+                            acc[a][i + 1] = fmaf(p[a][u], t.y, acc[a][i + 1]);
+                            acc[a][i + 2] = fmaf(p[a][u], t.z, acc[a][i + 2]);
+                            acc[a][i + 3] = fmaf(p[a][u], t.w, acc[a][i + 3]);
+                        }
                     }
                 }
             }
-            const float inv = 1.0f / l;
-            float* o = out + (b * (int64_t)n + r) * 128 + 16 * h;
 #pragma unroll
-            for (int i = 0; i < 16; i += 4)
-                *reinterpret_cast<float4*>(o + i) = make_float4(acc[i] * inv, acc[i + 1] * inv, acc[i + 2] * inv, acc[i + 3] * inv);
+            for (int a = 0; a < kRPT; ++a) {
+                if (r0 + a < n) {
+                    const float inv = 1.0f / l[a];
+                    float* o = out + (b * (int64_t)n + r0 + a) * 128 + 16 * h;
+#pragma unroll
+                    for (int i = 0; i < 16; i += 4)
+                        *reinterpret_cast<float4*>(o + i) = make_float4(acc[a][i] * inv, acc[a][i + 1] * inv,
+                                                                         acc[a][i + 2] * inv, acc[a][i + 3] * inv);
+                }
+            }
         }
     }
 }
@@ -361,6 +476,15 @@ __global__ void __launch_bounds__(kAttnThreads) enc_attention_kernel(const float
 
 // ---- C ABI ---------------------------------------------------------------------------------------------------------
 using namespace r4;
+
+#ifdef R4_ENC_PROF
+extern "C" int rl4co_enc_debug_prof(long long* out16, int reset) {
+    if (reset) { long long z[16] = {0}; cudaMemcpyToSymbol(r4::enc::g_enc_prof, z, sizeof(z)); return 0; }
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out16, r4::enc::g_enc_prof, 16 * sizeof(long long));
+    return 0;
+}
+#endif
 
 extern "C" int64_t rl4co_enc_packed_bytes(int32_t n_out, int32_t k) {
     if (n_out <= 0 || k <= 0 || n_out % 128 || k % 128) return 0;
@@ -441,7 +565,10 @@ extern "C" int rl4co_enc_attention(const float* qkv, float* out, int64_t B, int3
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int64_t want = 2LL * sms;
     const unsigned grid = (unsigned)(B < want ? B : want);
-    enc::enc_attention_kernel<<<grid, enc::kAttnThreads, smem, stream>>>(qkv, out, B, n);
+    // 8 * ceil(n / 2) (head, row pair) tasks: size the CTA so that its warp-tasks split into two full rounds
+    const int warp_tasks = (8 * ((n + enc::kRPT - 1) / enc::kRPT) + 31) / 32;
+    const int threads = 32 * ((warp_tasks + 1) / 2);
+    enc::enc_attention_kernel<<<grid, threads, smem, stream>>>(qkv, out, B, n);
     R4_CHECK_LAUNCH("enc_attention");
     return RL4CO_OK;
 }
