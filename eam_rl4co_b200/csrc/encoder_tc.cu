@@ -471,6 +471,202 @@ __global__ void __launch_bounds__(kAttnMaxThreads) enc_attention_kernel(const fl
     }
 }
 
+// ---- multi-head self-attention of one instance on tcgen05 (n <= 112) ----------------------------------------------
+// Same structure as the glimpse of the rollout kernel: S_h = Q_h K_h^T (M = 128 query rows, N = NPAD keys, K = 16) into
+// TMEM, softmax in registers (thread = query row, warp w -> lane quadrant w % 4, head w / 4 of the current group of
+// four), P written back in place as fp16 hi/lo, O_h = P_h V_h with P as the TMEM A operand.  Q, K: the X-tile layout
+// of the linear kernel (head h = K-chunks 2h, 2h+1); V^T: channels x keys.  512 threads, one instance per CTA.
+constexpr int kAT = 512;
+constexpr uint32_t kColO = 448;
+
+struct AttnSmem {
+    uint64_t mma_bar;
+    uint32_t tmem_ptr;
+    uint32_t pad_;
+};
+
+__global__ void __launch_bounds__(kAT, 1) enc_attention_tc_kernel(const float* __restrict__ qkv, float* __restrict__ out,
+                                                                  int64_t B, int n, int npad) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned char* qs = smem;                 // Q tile hi | lo (64 KB)
+    unsigned char* ks = smem + kTile;         // K tile
+    unsigned char* vs = smem + 2 * kTile;     // V^T tile: byte(ch, key) = (ch/8) sbo_v + (key/8) 128 + (ch%8) 16 + (key%8) 2
+    AttnSmem* s = reinterpret_cast<AttnSmem*>(smem + 3 * kTile);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = warp & 3, j = warp >> 2, row = 32 * q + lane;
+    const uint32_t sbo_v = (uint32_t)(npad / 8) * 128u;
+    const int nch = npad / 16;
+    if (threadIdx.x == 0) {
+        mbar_init(&s->mma_bar, 4);
+        fence_mbar_init();
+    }
+    __syncwarp();
+    if (warp == 0) tmem_alloc(&s->tmem_ptr, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s->tmem_ptr;
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * q) << 16);
+    const uint32_t qs_a = smem_u32(qs), ks_a = smem_u32(ks), vs_a = smem_u32(vs);
+    uint32_t par = 0;
+    const float kLog2e = 1.4426950408889634f;
+
+    for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
+        const float* base = qkv + b * (int64_t)n * 384;
+        // ---- operands: Q (pre-scaled by 1/sqrt(16), exact), K, V^T as fp16 hi/lo tiles -----------------------------
+        for (int v = warp; v < 2 * 64; v += 16) {            // 64 warp passes (8 rows x 4 chunks) per tile, Q then K
+            const int which = v >> 6, vv = v & 63;
+            const int rg = vv >> 2, c = 4 * (vv & 3) + (lane >> 3), r = 8 * rg + (lane & 7);
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bq = a;
+            if (r < n) {
+                const float* src = base + (size_t)r * 384 + which * 128 + 8 * c;
+                a = *reinterpret_cast<const float4*>(src);
+                bq = *reinterpret_cast<const float4*>(src + 4);
+            }
+            const float sc = which == 0 ? 0.25f : 1.0f;
+            uint32_t h4[4], l4[4];
+            split2(a.x * sc, a.y * sc, h4[0], l4[0]);
+            split2(a.z * sc, a.w * sc, h4[1], l4[1]);
+            split2(bq.x * sc, bq.y * sc, h4[2], l4[2]);
+            split2(bq.z * sc, bq.w * sc, h4[3], l4[3]);
+            unsigned char* dst = (which == 0 ? qs : ks) + (uint32_t)rg * kSBO + (uint32_t)c * kLBO + (uint32_t)(lane & 7) * 16u;
+            *reinterpret_cast<uint4*>(dst) = make_uint4(h4[0], h4[1], h4[2], h4[3]);
+            *reinterpret_cast<uint4*>(dst + kHalf) = make_uint4(l4[0], l4[1], l4[2], l4[3]);
+        }
+        for (int it = threadIdx.x; it < (npad / 8) * 128; it += kAT) {   // (8-key chunk, channel): lanes over channels
+            const int rc = it >> 7, ch = it & 127;
+            float vv[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int r = rc * 8 + i;
+                vv[i] = (r < n) ? base[(size_t)r * 384 + 256 + ch] : 0.f;
+            }
+            uint32_t vh[4], vl[4];
+#pragma unroll
+            for (int p = 0; p < 4; ++p) split2(vv[2 * p], vv[2 * p + 1], vh[p], vl[p]);
+            const uint32_t off = (uint32_t)(ch >> 3) * sbo_v + (uint32_t)rc * 128u + (uint32_t)(ch & 7) * 16u;
+            *reinterpret_cast<uint4*>(vs + off) = make_uint4(vh[0], vh[1], vh[2], vh[3]);
+            *reinterpret_cast<uint4*>(vs + kHalf + off) = make_uint4(vl[0], vl[1], vl[2], vl[3]);
+        }
+        fence_proxy_async();
+        __syncthreads();
+
+        float o_keep[16];
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+            const int h = 4 * g + j;
+            // scores of head h into columns [j NPAD, (j+1) NPAD): one k-step, hi*hi + hi*lo + lo*hi
+            if (q == j) {
+                if (elect_one()) {
+                    tc_fence_after();
+                    const uint32_t id = idesc_f16(kRows, npad);
+                    const uint64_t a_hi = smem_desc(qs_a + 2u * h * kLBO, kLBO, kSBO);
+                    const uint64_t a_lo = smem_desc(qs_a + kHalf + 2u * h * kLBO, kLBO, kSBO);
+                    const uint64_t b_hi = smem_desc(ks_a + 2u * h * kLBO, kLBO, kSBO);
+                    const uint64_t b_lo = smem_desc(ks_a + kHalf + 2u * h * kLBO, kLBO, kSBO);
+                    const uint32_t d = tmem + (uint32_t)(j * npad);
+                    mma_ss(d, a_hi, b_hi, id, 0u);
+                    mma_ss(d, a_hi, b_lo, id, 1u);
+                    mma_ss(d, a_lo, b_hi, id, 1u);
+                    tc_commit(&s->mma_bar);
+                }
+                __syncwarp();
+            }
+            mbar_wait(&s->mma_bar, par);
+            par ^= 1u;
+            tc_fence_after();
+            // softmax over the n keys of this thread's (row, head): pass 1 maximum, pass 2 exp / split / store in place
+            const uint32_t sp = lane_base + (uint32_t)(j * npad);
+            float m = -INFINITY;
+            for (int c = 0; c < nch; ++c) {
+                uint32_t v[16];
+                tmem_ld16(sp + 16u * c, v);
+                tc_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                    if (16 * c + i < n) m = fmaxf(m, __uint_as_float(v[i]));
+            }
+            const float ml = m * kLog2e;
+            float l0 = 0.f, l1 = 0.f;
+            for (int c = 0; c < nch; ++c) {
+                uint32_t v[16], hi[8], lo[8];
+                tmem_ld16(sp + 16u * c, v);
+                tc_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int k0 = 16 * c + 2 * i;
+                    const float p0 = (k0 < n) ? ex2_approx(fmaf(__uint_as_float(v[2 * i]), kLog2e, -ml)) : 0.f;
+                    const float p1 = (k0 + 1 < n) ? ex2_approx(fmaf(__uint_as_float(v[2 * i + 1]), kLog2e, -ml)) : 0.f;
+                    l0 += p0;
+                    l1 += p1;
+                    split2(p0, p1, hi[i], lo[i]);
+                }
+                tmem_st8(sp + 16u * c, hi);
+                tmem_st8(sp + 16u * c + 8u, lo);
+            }
+            tc_wait_st();
+            const float inv_l = 1.0f / (l0 + l1);
+            tc_fence_before();
+            __syncthreads();
+            if (q == j) {
+                if (elect_one()) {
+                    tc_fence_after();
+                    const uint32_t id = idesc_f16(kRows, 16);
+                    uint64_t bv_hi = smem_desc(vs_a + 2u * h * sbo_v, 128u, sbo_v);
+                    uint64_t bv_lo = smem_desc(vs_a + kHalf + 2u * h * sbo_v, 128u, sbo_v);
+                    const uint32_t d = tmem + kColO + 16u * j;
+                    uint32_t a = tmem + (uint32_t)(j * npad);
+                    for (int jk = 0; jk < nch; ++jk) {
+                        mma_ts(d, a, bv_hi, id, jk > 0 ? 1u : 0u);
+                        mma_ts(d, a, bv_lo, id, 1u);
+                        mma_ts(d, a + 8u, bv_hi, id, 1u);
+                        a += 16u;
+                        bv_hi += (2u * 128u) >> 4;
+                        bv_lo += (2u * 128u) >> 4;
+                    }
+                    tc_commit(&s->mma_bar);
+                }
+                __syncwarp();
+            }
+            mbar_wait(&s->mma_bar, par);
+            par ^= 1u;
+            tc_fence_after();
+            uint32_t o[16];
+            tmem_ld16(lane_base + kColO + 16u * j, o);
+            tc_wait_ld();
+            if (g == 0) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) o_keep[i] = __uint_as_float(o[i]) * inv_l;
+                tc_fence_before();
+                __syncthreads();          // every warp has drained O and is done with P before the columns are reused
+            } else {
+                // all MMAs are complete: Q and K tiles are free -> fp32 staging [128][kStage] for coalesced stores
+                float* st = reinterpret_cast<float*>(smem);
+#pragma unroll
+                for (int i = 0; i < 16; i += 4) {
+                    *reinterpret_cast<float4*>(st + row * kStage + 16 * j + i) =
+                        make_float4(o_keep[i], o_keep[i + 1], o_keep[i + 2], o_keep[i + 3]);
+                    *reinterpret_cast<float4*>(st + row * kStage + 64 + 16 * j + i) =
+                        make_float4(__uint_as_float(o[i]) * inv_l, __uint_as_float(o[i + 1]) * inv_l,
+                                    __uint_as_float(o[i + 2]) * inv_l, __uint_as_float(o[i + 3]) * inv_l);
+                }
+            }
+        }
+        tc_fence_before();
+        __syncthreads();
+        {
+            const float* st = reinterpret_cast<const float*>(smem);
+            float* ob = out + b * (int64_t)n * 128;
+            for (int idx = threadIdx.x; idx < n * 32; idx += kAT) {
+                const int r = idx >> 5, c4 = (idx & 31) * 4;
+                *reinterpret_cast<float4*>(ob + (size_t)r * 128 + c4) = *reinterpret_cast<const float4*>(st + r * kStage + c4);
+            }
+        }
+        __syncthreads();
+    }
+    if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
 }  // namespace enc
 }  // namespace r4
 
@@ -550,6 +746,26 @@ extern "C" int rl4co_enc_attention(const float* qkv, float* out, int64_t B, int3
     cudaStream_t stream = (cudaStream_t)stream_;
     R4_CHECK_ARG(qkv && out && B >= 0 && n >= 1 && n <= enc::kRows, "enc_attention: bad args (nodes = %d)", n);
     if (B == 0) return RL4CO_OK;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int npad = (n + 15) & ~15;
+    if (npad <= 112) {   // tensor-core kernel: four heads of NPAD score columns + 64 output columns fit the 512 of TMEM
+        const size_t smem = 3 * (size_t)enc::kTile + sizeof(enc::AttnSmem);
+        static bool prepared_tc = false;
+        if (!prepared_tc) {
+            if (cudaFuncSetAttribute(enc::enc_attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem) != cudaSuccess) {
+                set_error("enc_attention: cannot reserve %zu bytes of shared memory", smem);
+                return RL4CO_E_LAUNCH;
+            }
+            prepared_tc = true;
+        }
+        const unsigned grid = (unsigned)(B < sms ? B : sms);
+        enc::enc_attention_tc_kernel<<<grid, enc::kAT, smem, stream>>>(qkv, out, B, n, npad);
+        R4_CHECK_LAUNCH("enc_attention (tcgen05)");
+        return RL4CO_OK;
+    }
     const size_t smem = (size_t)n * 128 * 2 * sizeof(float);
     static bool prepared = false;
     if (!prepared) {
@@ -560,9 +776,6 @@ extern "C" int rl4co_enc_attention(const float* qkv, float* out, int64_t B, int3
         }
         prepared = true;
     }
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int64_t want = 2LL * sms;
     const unsigned grid = (unsigned)(B < want ? B : want);
     // 8 * ceil(n / 2) (head, row pair) tasks: size the CTA so that its warp-tasks split into two full rounds

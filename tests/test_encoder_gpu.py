@@ -71,7 +71,7 @@ def test_enc_linear_matches_torch(which, n, B):
     assert err < 2e-6, err           # fp32-level agreement (tolerance written here: 2e-6 of the output range)
 
 
-@pytest.mark.parametrize("n,B", [(100, 3), (21, 4), (128, 2), (51, 300)])
+@pytest.mark.parametrize("n,B", [(100, 3), (21, 4), (128, 2), (51, 300), (112, 2), (101, 150), (113, 2), (5, 3)])
 def test_enc_attention_matches_sdpa(n, B):
     g = torch.Generator(device=DEV).manual_seed(n + B)
     qkv = torch.randn(B, n, 384, device=DEV, generator=g) * 1.5
