@@ -107,6 +107,40 @@ __device__ __forceinline__ void convert_x(const float* __restrict__ Xb, int n, i
     }
 }
 
+// The same conversion by all eight warps, split into its global loads (64 registers per thread, issued while the
+// previous K block's MMAs still run) and the split + shared-memory stores (once those MMAs are done with the tile).
+__device__ __forceinline__ void load_x8(const float* __restrict__ Xb, int n, int K, int kb, float4 (&a)[8], float4 (&b)[8]) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int v = i * 8 + warp;                           // 64 warp passes over 8 warps
+        const int r = 8 * (v >> 2) + (lane & 7), c = 4 * (v & 3) + (lane >> 3);
+        a[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        b[i] = a[i];
+        if (r < n) {
+            const float* src = Xb + (size_t)r * K + kb * 128 + 8 * c;
+            a[i] = *reinterpret_cast<const float4*>(src);
+            b[i] = *reinterpret_cast<const float4*>(src + 4);
+        }
+    }
+}
+__device__ __forceinline__ void store_x8(const float4 (&a)[8], const float4 (&b)[8], unsigned char* xs) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int v = i * 8 + warp;
+        const int rg = v >> 2, c = 4 * (v & 3) + (lane >> 3);
+        uint32_t h[4], l[4];
+        split2(a[i].x, a[i].y, h[0], l[0]);
+        split2(a[i].z, a[i].w, h[1], l[1]);
+        split2(b[i].x, b[i].y, h[2], l[2]);
+        split2(b[i].z, b[i].w, h[3], l[3]);
+        const uint32_t off = (uint32_t)rg * kSBO + (uint32_t)c * kLBO + (uint32_t)(lane & 7) * 16u;
+        *reinterpret_cast<uint4*>(xs + off) = make_uint4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<uint4*>(xs + kHalf + off) = make_uint4(l[0], l[1], l[2], l[3]);
+    }
+}
+
 // 128 x 128 x 128 block product into TMEM columns [dcol, dcol + 128): 8 k-steps x (hi*hi + hi*lo + lo*hi)
 __device__ __forceinline__ void issue_tile(uint32_t tmem, uint32_t dcol, uint32_t xs, uint32_t ws, bool first) {
     const uint32_t id = idesc_f16(kRows, 128);
@@ -182,11 +216,13 @@ __global__ void __launch_bounds__(kThreads, 1)
     for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
         const float* Xb = X + b * (int64_t)n * K;
         for (int kb = 0; kb < nK; ++kb) {
-            if (kb > 0) {   // the MMAs of the previous K block read the A tile: wait, then convert the next block
+            if (kb > 0) {   // next K block: its loads fly while the MMAs of the previous block still read the A tile
+                float4 xa[8], xb[8];
+                load_x8(Xb, n, K, kb, xa, xb);
                 mbar_wait(&s->kdone_bar, n_kdone & 1u);
                 ++n_kdone;
                 tc_fence_after();
-                if (producer) convert_x(Xb, n, K, kb, xs);
+                store_x8(xa, xb, xs);
                 fence_proxy_async();
                 __syncthreads();
             }
