@@ -104,6 +104,8 @@ int main() {
     for (int n : {3, 12, 24}) {
         run<2>("1 thread, SS M128 N112 K16, one accumulator", n);
         run<4>("1 thread, TS M128 N112 K16, one accumulator", n);
+        run<4, true>("elect.sync: TS M128 N112 K16, one accumulator", n);
+        run<2, true>("elect.sync: SS M128 N112 K16, one accumulator", n);
     }
     return 0;
 }
