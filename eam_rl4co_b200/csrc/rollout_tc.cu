@@ -32,8 +32,7 @@ constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kColSP = 0;   // scores / probabilities of 4 heads: 4 x NPAD columns
 constexpr uint32_t kColO = 448;  // glimpse accumulators of 4 heads: 4 x 16 columns
 constexpr uint32_t kColHA = 0;   // heads as A operand: hi [0,64), lo [64,128)
-constexpr uint32_t kColLG = 128; // logits accumulators, even k-steps: NPAD columns
-constexpr uint32_t kColLG2 = 240;// logits accumulators, odd k-steps (two chains pipeline in the tensor core)
+constexpr uint32_t kColLG = 128; // logits accumulator: NPAD columns
 // K-major, no-swizzle operand tiles (see tc_ptx.cuh::smem_desc)
 constexpr uint32_t kLBO = 128;                 // static tiles: the K-chunks of a row group are contiguous
 constexpr uint32_t kSBO_KL = 16 * kLBO;        // K / L tiles: 16 chunks (128 channels) per row group
@@ -63,7 +62,7 @@ struct Smem {
     float2 locs[kRows];
     float demand[kRows];        // indexed by node (node 0 unused)
     uint64_t tma_bar;
-    uint64_t mma_bar;           // logits MMAs (4 arrivals)
+    uint64_t mma_bar;           // logits MMAs (one commit)
     uint64_t team_bar[4];       // scores / PV MMAs of one team (1 arrival)
     uint32_t tmem_ptr;
     uint32_t pad_;
@@ -274,24 +273,21 @@ __device__ __forceinline__ void issue_pv(const Ctx& x, int h, int team) {
     tc_commit(&x.s()->team_bar[team]);
 }
 
-// logits = heads . (L W_out / sqrt(E))^T : A = heads from TMEM (k-step jk = head jk), B = L tile;
-// issuer par in {0,1} takes the k-steps of that parity and accumulates in kColLG / kColLG2 (summed by
-// the readers); issuers 2, 3 only arrive.
-__device__ __forceinline__ void issue_logits(const Ctx& x, int par) {
+// logits = heads . (L W_out / sqrt(E))^T : A = heads from TMEM (k-step jk = head jk), B = L tile; one chain of
+// 24 dependent MMAs into kColLG (profiles/ubench_mma.cu: as fast as two half-chains, and the readers load one
+// accumulator instead of summing two).
+__device__ __forceinline__ void issue_logits(const Ctx& x) {
     tc_fence_after();
-    if (par < 2) {
-        const uint32_t id = idesc_f16(kRows, x.npad);
-        const uint32_t d = x.tmem + (par ? kColLG2 : kColLG);
+    const uint32_t id = idesc_f16(kRows, x.npad);
+    const uint32_t d = x.tmem + kColLG;
 #pragma unroll
-        for (int j2 = 0; j2 < 4; ++j2) {
-            const int jk = 2 * j2 + par;
-            const uint64_t bl_hi = smem_desc(x.l_hi() + 2u * jk * kLBO, kLBO, kSBO_KL);
-            const uint64_t bl_lo = smem_desc(x.l_lo() + 2u * jk * kLBO, kLBO, kSBO_KL);
-            const uint32_t a = x.tmem + kColHA + 8u * jk;
-            mma_ts(d, a, bl_hi, id, j2 > 0 ? 1u : 0u);
-            mma_ts(d, a, bl_lo, id, 1u);
-            mma_ts(d, a + 64u, bl_hi, id, 1u);
-        }
+    for (int jk = 0; jk < 8; ++jk) {
+        const uint64_t bl_hi = smem_desc(x.l_hi() + 2u * jk * kLBO, kLBO, kSBO_KL);
+        const uint64_t bl_lo = smem_desc(x.l_lo() + 2u * jk * kLBO, kLBO, kSBO_KL);
+        const uint32_t a = x.tmem + kColHA + 8u * jk;
+        mma_ts(d, a, bl_hi, id, jk > 0 ? 1u : 0u);
+        mma_ts(d, a, bl_lo, id, 1u);
+        mma_ts(d, a + 64u, bl_hi, id, 1u);
     }
     tc_commit(&x.s()->mma_bar);
 }
@@ -450,7 +446,33 @@ __device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int 
             for (int i = 0; i < 12; ++i)
                 if (16 * nfull + i < n) dbg_scores[16 * nfull + i] = __uint_as_float(va[i]);
         }
-        softmax_chunk(sp, nfull, va, a0, spec, refl2, m_run, l0, l1);   // mask bits beyond n are 0: padding -> exact zeros
+        if (spec) {
+            // only the tq 4-column groups that hold real nodes are exponentiated; the padding columns of the
+            // chunk (K of the PV MMA) are written as exact zeros
+            uint32_t hi[8], lo[8];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (k < tq) {
+#pragma unroll
+                    for (int i = 2 * k; i < 2 * k + 2; ++i) {
+                        const float s0 = (a0 & (1u << (2 * i))) ? __uint_as_float(va[2 * i]) : -INFINITY;
+                        const float s1 = (a0 & (1u << (2 * i + 1))) ? __uint_as_float(va[2 * i + 1]) : -INFINITY;
+                        const float p0 = ex2_approx(fmaf(s0, 1.4426950408889634f, -refl2));
+                        const float p1 = ex2_approx(fmaf(s1, 1.4426950408889634f, -refl2));
+                        l0 += p0;
+                        l1 += p1;
+                        split2(p0, p1, hi[i], lo[i]);
+                    }
+                } else {
+                    hi[2 * k] = hi[2 * k + 1] = 0u;
+                    lo[2 * k] = lo[2 * k + 1] = 0u;
+                }
+            }
+            tmem_st8(sp + 16u * nfull, hi);
+            tmem_st8(sp + 16u * nfull + 8u, lo);
+        } else {
+            softmax_chunk(sp, nfull, va, a0, false, refl2, m_run, l0, l1);   // mask bits beyond n are 0 -> exact zeros
+        }
     }
     tc_wait_st();
     m_out = m_run;
@@ -573,7 +595,7 @@ __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cach
     tc_fence_before();
     __syncthreads();
     R4_STAMP(10);
-    if (warp < 4) { if (elect_one()) issue_logits(x, warp); }
+    if (warp == 0) { if (elect_one()) issue_logits(x); }
     wait_mma(&x.s()->mma_bar, mma_par);
     R4_STAMP(11);
 }
@@ -621,28 +643,20 @@ __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_a
     const uint32_t lg = x.tmem + ((uint32_t)(32 * q) << 16) + kColLG;
     const int U = (n + 3) >> 2;
     const int u0 = (U * j) >> 2, u1 = (U * (j + 1)) >> 2;
-    // 28 columns from 4*u0 on, the two accumulators summed (columns past this thread's range are ignored
-    // below); two rounds of loads keep the register peak at 16 + 16 + 28
+    // 28 columns from 4*u0 on (columns past this thread's range are ignored below)
     float tv[28];                                                   // tanh(logit) (or the logit), -inf if infeasible
     {
-        uint32_t a16[16], b16[16];
+        uint32_t a16[16], a8[8], a4[4];
         tmem_ld16(lg + 4u * u0, a16);
-        tmem_ld16(lg + (kColLG2 - kColLG) + 4u * u0, b16);
-        tc_wait_ld();
-#pragma unroll
-        for (int i = 0; i < 16; ++i) tv[i] = __uint_as_float(a16[i]) + __uint_as_float(b16[i]);
-    }
-    {
-        uint32_t a8[8], b8[8], a4[4], b4[4];
         tmem_ld8(lg + 4u * u0 + 16u, a8);
-        tmem_ld8(lg + (kColLG2 - kColLG) + 4u * u0 + 16u, b8);
         tmem_ld4(lg + 4u * u0 + 24u, a4);
-        tmem_ld4(lg + (kColLG2 - kColLG) + 4u * u0 + 24u, b4);
         tc_wait_ld();
 #pragma unroll
-        for (int i = 0; i < 8; ++i) tv[16 + i] = __uint_as_float(a8[i]) + __uint_as_float(b8[i]);
+        for (int i = 0; i < 16; ++i) tv[i] = __uint_as_float(a16[i]);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) tv[24 + i] = __uint_as_float(a4[i]) + __uint_as_float(b4[i]);
+        for (int i = 0; i < 8; ++i) tv[16 + i] = __uint_as_float(a8[i]);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) tv[24 + i] = __uint_as_float(a4[i]);
     }
     const uint32_t w0 = s->maskw[0][row], w1 = s->maskw[1][row], w2 = s->maskw[2][row], w3 = s->maskw[3][row];
     const int sh = 4 * u0, wi = sh >> 5;
@@ -774,39 +788,53 @@ __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_a
     if (valid && j == 0) {
         const uint32_t ww = (sel.action >> 5) == 0 ? w0 : ((sel.action >> 5) == 1 ? w1 : ((sel.action >> 5) == 2 ? w2 : w3));
         if (a.mode != RL4CO_MODE_EVALUATE && !((ww >> (sel.action & 31)) & 1u)) err_bits |= RL4CO_ERR_INFEASIBLE;
-        if (!(sel.logp > -1000.f)) err_bits |= RL4CO_ERR_NEG_INF_LOGP;   // decoding.py:56-58
     }
+    // the log-probability is consumed by thread 1 of the row only (record_action): lse and this check sink there
+    if (valid && j == 1 && !(sel.logp > -1000.f)) err_bits |= RL4CO_ERR_NEG_INF_LOGP;   // decoding.py:56-58
     return sel;
 }
 
 // ---- env step (tsp/env.py:62-88, cvrp/env.py:68-100,132-144), 4 threads per row ------------------------
+// The row's bookkeeping is spread over its four threads so that no warp carries a long serial chain between the
+// selection and the step-end barrier: thread 0 owns what the next step needs (current / first node, done flag),
+// thread 1 the log-likelihood, thread 2 the tour length, thread 3 the action record.
 struct RowState {
     uint32_t word;   // TSP: feasible bits of word j; CVRP: visited bits of word j
     float used, cap; // CVRP (tracked redundantly by the 4 threads of the row)
-    // thread j == 0 only
-    float ll, len;
-    int prev, first_action, nvis, length;
-    bool done;
+    float ll;        // thread 1
+    float len;       // thread 2
+    int prev, first_action;   // thread 2
+    int nvis, length;         // thread 0
+    bool done;                // thread 0
 };
 
+// Outputs of the step that nothing in the next step waits for; called after the step-end barrier, where the
+// three short chains (logf, sqrt, scattered stores) of a row run in different warps under the next Q gathers.
 template <int ENV>
-__device__ __forceinline__ void apply_action(const Ctx& x, const rl4co_rollout_args& a, RowState& st, int n, int q,
-                                             int j, int row, bool valid, int64_t grow, int t, int T, int act,
-                                             float lpa) {
-    Smem* s = x.s();
-    if (j == 0 && valid) {
-        a.actions[grow * T + t] = act;
+__device__ __forceinline__ void record_action(const Ctx& x, const rl4co_rollout_args& a, RowState& st, int j,
+                                              bool valid, int64_t grow, int t, int T, int act, float lpa) {
+    if (!valid) return;
+    if (j == 1) {
         a.logp[grow * T + t] = lpa;
         st.ll += lpa;
+    } else if (j == 2) {
         // tour length so far (ops.py:82-95): edge prev -> act; CVRP starts at the depot
         const int from = (st.prev < 0) ? ((ENV == RL4CO_ENV_CVRP) ? 0 : act) : st.prev;
-        const float2 p0 = s->locs[from], p1 = s->locs[act];
+        const float2 p0 = x.s()->locs[from], p1 = x.s()->locs[act];
         const float dx = p1.x - p0.x, dy = p1.y - p0.y;
         st.len += sqrtf(dx * dx + dy * dy);
         if (st.prev < 0) st.first_action = act;
         st.prev = act;
-        s->cur[row] = act;
+    } else if (j == 3) {
+        a.actions[grow * T + t] = act;
     }
+}
+
+template <int ENV>
+__device__ __forceinline__ void apply_action(const Ctx& x, const rl4co_rollout_args& a, RowState& st, int n, int q,
+                                             int j, int row, bool valid, int t, int act) {
+    Smem* s = x.s();
+    if (j == 0 && valid) s->cur[row] = act;
     if (ENV == RL4CO_ENV_TSP) {
         if (valid && (act >> 5) == j) st.word &= ~(1u << (act & 31));
         s->maskw[j][row] = st.word;
@@ -866,7 +894,7 @@ __device__ __forceinline__ void cta_setup(Ctx& x) {
     const int warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) {
         mbar_init(&x.s()->tma_bar, 1);
-        mbar_init(&x.s()->mma_bar, 4);   // four issuer threads commit the logits MMAs
+        mbar_init(&x.s()->mma_bar, 1);   // the logits issuer's commit
         for (int i = 0; i < 4; ++i) mbar_init(&x.s()->team_bar[i], 1);
         fence_mbar_init();
     }
@@ -955,8 +983,9 @@ __global__ void __launch_bounds__(kThreads, 1)
         mbar_wait(&s->tma_bar, tma_par);
         tma_par ^= 1u;
         __syncthreads();
-        apply_action<ENV>(x, a, st, n, q, j, row, valid, grow, 0, T, act, 0.f);
+        apply_action<ENV>(x, a, st, n, q, j, row, valid, 0, act);
         int all_done = __syncthreads_and(!valid || j != 0 || st.done);
+        record_action<ENV>(x, a, st, j, valid, grow, 0, T, act, 0.f);
         R4_STAMP(14);
 
         float lse[2] = {0.f, 0.f};   // log-sum-exp of this thread's two (row, head) score rows, previous step
@@ -975,21 +1004,41 @@ __global__ void __launch_bounds__(kThreads, 1)
                 }
             }
             const uint32_t nkey = (a.mode == RL4CO_MODE_SAMPLING) ? noise_key(a.seed, a.inst_offset + b, row, t) : 0u;
+#ifdef R4_WARP_PROF   // experiment: per-warp select / env / step-end wait cycles of CTA 0 -> phase_cycles[16 + 4 warp + k]
+            const long long wp0 = clock64();
+#endif
             const RowSel sel = select_row(x, a, n, q, j, row, valid, grow, t, T, nkey, given, err_bits);
             R4_STAMP(12);
-            apply_action<ENV>(x, a, st, n, q, j, row, valid, grow, t, T, sel.action, sel.logp);
+#ifdef R4_WARP_PROF
+            const long long wp1 = clock64();
+#endif
+            apply_action<ENV>(x, a, st, n, q, j, row, valid, t, sel.action);
             tc_fence_before();
+#ifdef R4_WARP_PROF
+            const long long wp2 = clock64();
+#endif
             all_done = __syncthreads_and(!valid || j != 0 || st.done);
+#ifdef R4_WARP_PROF
+            if (a.phase_cycles != nullptr && blockIdx.x == 0 && lane == 0) {
+                const long long wp3 = clock64();
+                a.phase_cycles[16 + 4 * warp + 0] += wp1 - wp0;
+                a.phase_cycles[16 + 4 * warp + 1] += wp2 - wp1;
+                a.phase_cycles[16 + 4 * warp + 2] += wp3 - wp2;
+            }
+#endif
             R4_STAMP(13);
+            record_action<ENV>(x, a, st, j, valid, grow, t, T, sel.action, sel.logp);
         }
-        if (valid && j == 0) {
+        if (valid && j == 2) {
             // closing edge (roll(-1) wraps to the first element: TSP first action, CVRP depot)
             const int to = (ENV == RL4CO_ENV_CVRP) ? 0 : st.first_action;
             const float2 p0 = s->locs[st.prev], p1 = s->locs[to];
             const float dx = p1.x - p0.x, dy = p1.y - p0.y;
             st.len += sqrtf(dx * dx + dy * dy);
             a.reward[grow] = -st.len;
-            a.log_likelihood[grow] = st.ll;
+        }
+        if (valid && j == 1) a.log_likelihood[grow] = st.ll;
+        if (valid && j == 0) {
             const int len = st.done ? st.length : T;
             a.lengths[grow] = len;
             atomicMax(a.max_len, len);
@@ -1050,15 +1099,14 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int u0 = (U * j) >> 2, u1 = (U * (j + 1)) >> 2;
         bool nan_local = false;
         for (int u = u0; u < u1; ++u) {
-            uint32_t v4[4], y4[4];
+            uint32_t v4[4];
             tmem_ld4(lg + 4u * u, v4);
-            tmem_ld4(lg + (kColLG2 - kColLG) + 4u * u, y4);
             tc_wait_ld();
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const int node = 4 * u + i;
                 if (valid && node < n) {
-                    const float v = __uint_as_float(v4[i]) + __uint_as_float(y4[i]);
+                    const float v = __uint_as_float(v4[i]);
                     logits_out[grow * n + node] = v;
                     nan_local |= (v != v);
                 }

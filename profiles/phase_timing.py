@@ -21,7 +21,7 @@ def main():
     with torch.no_grad():
         h, _ = pol.encoder(td)
     for it in range(3):
-        pc = torch.zeros(16, dtype=torch.int64, device=dev)
+        pc = torch.zeros(16 + 64, dtype=torch.int64, device=dev)
         cfg = dict(temperature=1.0, tanh_clipping=10.0, mask_logits=True, store_all_logp=False, _phase_cycles=pc)
         try:
             pol._forward_fused(td, env, h, "multistart_greedy", None, 10**6, False, cfg)
@@ -31,10 +31,14 @@ def main():
     c = pc.tolist()
     n_inst = (B + 147) // 148
     steps = n_inst * (bench.N_NODES - 1)
-    tot = sum(c)
+    tot = sum(c[:16])
     print(f"CTA 0: {n_inst} instances, {steps} decode steps, {tot} cycles total, {tot / steps:.0f} cycles/step")
     for name, v in zip(NAMES, c):
         print(f"  {name:34s} {v / steps:9.0f} cyc/step  {100.0 * v / tot:5.1f}%")
+    if any(c[16:]):     # -DR4_WARP_PROF builds: per-warp select / env step / wait at the step-end barrier
+        for w in range(16):
+            sel, envs, wait = (c[16 + 4 * w + k] / steps for k in range(3))
+            print(f"  warp {w:2d} (q={w % 4}, j={w // 4}): select {sel:6.0f}  env {envs:6.0f}  step-end wait {wait:6.0f}")
 
 if __name__ == "__main__":
     main()

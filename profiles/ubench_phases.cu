@@ -43,9 +43,9 @@ __global__ void __launch_bounds__(kThreads, 1) phase_kernel(long long* out, floa
     const long long t0 = clock64();
     for (int r = 0; r < reps; ++r) {
         // refill: scores of this thread's (row, head j) / logits quarter
-        const uint32_t dst = (MODE == 2) ? lane_base + kColLG + 56u * (j & 1) + (j >> 1) * (kColLG2 - kColLG)
+        const uint32_t dst = (MODE == 2) ? lane_base + kColLG + 28u * (uint32_t)j
                                          : lane_base + kColSP + (uint32_t)(j * x.npad);
-        const int ncol = (MODE == 2) ? 56 : 112;
+        const int ncol = (MODE == 2) ? 32 : 112;   // 28 logit columns per thread (8-column stores; overlaps rewritten)
         uint32_t lcg = (uint32_t)(row * 977 + r * 31 + j * 13) * 2654435761u;
         for (int c = 0; c < ncol; c += 8) {
             uint32_t w8[8];
