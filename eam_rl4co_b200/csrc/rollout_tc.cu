@@ -66,6 +66,7 @@ struct Smem {
     uint64_t team_bar[4];       // scores / PV MMAs of one team (1 arrival)
     uint32_t tmem_ptr;
     uint32_t pad_;
+    float lnf[4][kRows];        // ln(#feasible nodes) of the row at the previous step, one private copy per thread
 };
 
 // Shared-memory map: [Smem][Q hi][Q lo][K_hi][K_lo][L_hi][L_lo][Vt_hi][Vt_lo].  Everything but the tile size is a
@@ -513,6 +514,19 @@ __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cach
     team_sync(j);
     R4_STAMP(0);
     if (issuer_warp) { if (elect_one()) issue_scores(x, j, j); }
+    // The feasible set can change by two orders of magnitude in one step (CVRP: a vehicle with no fitting customer
+    // returns to the depot and every unvisited customer opens up).  With near-uniform attention the log-sum-exp
+    // follows ln(#feasible), with peaked attention it does not move: the reference is shifted by half of the
+    // change of ln(#feasible), which keeps both extremes inside the window.
+    {
+        const int nf = __popc(x.s()->maskw[0][row]) + __popc(x.s()->maskw[1][row]) + __popc(x.s()->maskw[2][row]) +
+                       __popc(x.s()->maskw[3][row]);
+        const float lnf = __logf((float)(nf > 0 ? nf : 1));
+        const float shift = have_ref ? 0.5f * (lnf - x.s()->lnf[j][row]) : 0.f;   // first step: no reference yet
+        x.s()->lnf[j][row] = lnf;
+        lse[0] += shift;
+        lse[1] += shift;
+    }
 #pragma unroll
     for (int g = 0; g < 2; ++g) {
         const int h = 4 * g + j;
@@ -535,6 +549,7 @@ __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cach
             tc_fence_before();
             if (team_all(j, ok)) break;
             // rare: the reference missed somewhere in the team -> scores again, then the exact form
+            if (prof != nullptr) prof[15] += 1;        // debug counter: fallbacks of team 0
             spec = false;
             if (g == 1) {                              // the stash sits on the Q tile the MMAs need: rebuild it
 #pragma unroll
@@ -636,6 +651,7 @@ __device__ __forceinline__ float tanh_small(float v) {
 // constant and the row needs no max exchange: greedy / evaluate take ONE 128-thread barrier per step.  Without
 // clipping the row maximum is exchanged first.  Greedy takes the argmax over x itself (log_softmax is monotone;
 // first index on exact ties as torch.argmax).
+template <int MODE>
 __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_args& a, int n, int q, int j,
                                              int row, bool valid, int64_t grow, int t, int T, uint32_t nkey,
                                              int given, int& err_bits) {
@@ -713,8 +729,8 @@ __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_a
 
     float best = -INFINITY, best_x = -INFINITY;
     int best_i = 0x7fffffff;
-    const bool sampling = a.mode == RL4CO_MODE_SAMPLING;
-    if (a.mode == RL4CO_MODE_EVALUATE) {
+    constexpr bool sampling = MODE == RL4CO_MODE_SAMPLING;
+    if (MODE == RL4CO_MODE_EVALUATE) {
 #pragma unroll
         for (int e = 0; e < 28; ++e) {
             if (e < cnt && sh + e == given) {
@@ -747,17 +763,13 @@ __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_a
         for (int e = 0; e < 28; ++e)
             if (e < cnt && sh + e < n) a.logp_all[(grow * T + t) * (int64_t)n + sh + e] = (tv[e] * sc - ref) - lse;
     }
-    if (sampling) {
+    if (sampling && a.gumbel != nullptr) {
         // Gumbel-max over logp + g (decoding.py:403-420 restated with supplied noise)
 #pragma unroll
         for (int e = 0; e < 28; ++e) {
             const float lp = (tv[e] * sc - ref) - lse;              // -inf stays -inf
             float g = 0.f;
-            if (a.gumbel != nullptr) {
-                if ((win >> e) & 1u) g = a.gumbel[(grow * T + t) * (int64_t)n + sh + e];
-            } else {
-                g = noise_gumbel(nkey, sh + e);
-            }
+            if ((win >> e) & 1u) g = a.gumbel[(grow * T + t) * (int64_t)n + sh + e];
             const float cand = lp + g;
             if (cand > best) {
                 best = cand;
@@ -765,6 +777,32 @@ __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_a
                 best_x = tv[e];
             }
         }
+    } else if (sampling) {
+        // Counter noise: argmax_e (logp_e + g_e), g = -ln(-ln u), is argmax_e p_e / (-ln u_e) (the exponential race:
+        // exp is monotone and the row's normaliser is common), so neither logarithm of the Gumbel transform nor the
+        // log-softmax of every element is needed: one lg2, one rcp and the exp(x_e - ref) of the row sum per element.
+        // -lg2 u must be accurate RELATIVE to itself: lg2.approx is (2^-22 absolute near 1), so u > 0.98 takes the
+        // series of -ln(1 - d), d = 1 - u exact.  Keys agree with logp + g to ~1e-5, far inside the near-tie bar.
+        best = 0.f;                                                 // an infeasible node has key 0 and never wins
+#pragma unroll
+        for (int e = 0; e < 28; ++e) {
+            const float u = noise_u(nkey, sh + e);
+            const float d = 1.0f - u;
+            const float ser = d * fmaf(d, fmaf(d, fmaf(d, 0.36067376f, 0.48089835f), 0.72134752f), 1.44269504f);
+            float l2;
+            asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(u));
+            const float big_e = u > 0.98f ? ser : -l2;             // -lg2 u > 0
+            float r;
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(big_e));
+            const float cand = ex2_approx(fmaf(tv[e], c1, c0)) * r;   // exp(-inf) = 0 for infeasible nodes
+            if (cand > best) {
+                best = cand;
+                best_i = sh + e;
+                best_x = tv[e];
+            }
+        }
+    }
+    if (sampling) {
         s->red_c[j][row] = best;
         s->red_i[j][row] = best_i;
         s->red_lp[j][row] = best_x;
@@ -787,7 +825,7 @@ __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_a
     sel.logp = (fx * sc - ref) - lse;
     if (valid && j == 0) {
         const uint32_t ww = (sel.action >> 5) == 0 ? w0 : ((sel.action >> 5) == 1 ? w1 : ((sel.action >> 5) == 2 ? w2 : w3));
-        if (a.mode != RL4CO_MODE_EVALUATE && !((ww >> (sel.action & 31)) & 1u)) err_bits |= RL4CO_ERR_INFEASIBLE;
+        if (MODE != RL4CO_MODE_EVALUATE && !((ww >> (sel.action & 31)) & 1u)) err_bits |= RL4CO_ERR_INFEASIBLE;
     }
     // the log-probability is consumed by thread 1 of the row only (record_action): lse and this check sink there
     if (valid && j == 1 && !(sel.logp > -1000.f)) err_bits |= RL4CO_ERR_NEG_INF_LOGP;   // decoding.py:56-58
@@ -928,7 +966,9 @@ __device__ __forceinline__ void load_tiles(const Ctx& x, unsigned char* smem, co
 }
 
 // ---- persistent fused rollout (constructive/base.py:221-263), tensor path ------------------------------
-template <int ENV>
+// One instantiation per (env, decode mode): the selection code of the other modes (noise, teacher forcing) would
+// otherwise share the 128-register budget of the greedy path.
+template <int ENV, int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
     rollout_tc_kernel(rl4co_cache c, rl4co_rollout_args a, const unsigned char* __restrict__ img, int npad) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -971,7 +1011,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         // forced first action (decoding.py:305-327; select_start_nodes ops.py:147-161)
         int act = 0;
         if (valid) {
-            if (a.mode == RL4CO_MODE_EVALUATE)
+            if (MODE == RL4CO_MODE_EVALUATE)
                 act = (int)a.actions_in[grow * a.actions_in_stride];
             else
                 act = (ENV == RL4CO_ENV_TSP) ? (row % n) : (row % (n - 1)) + 1;
@@ -996,18 +1036,18 @@ __global__ void __launch_bounds__(kThreads, 1)
             }
             decode_step_gemms<ENV>(x, c, b, S, mma_par, team_par, nullptr, nullptr, prof, tprev, lse, t > 1);
             int given = 0;
-            if (a.mode == RL4CO_MODE_EVALUATE && valid) {
+            if (MODE == RL4CO_MODE_EVALUATE && valid) {
                 given = (t < a.actions_in_T) ? (int)a.actions_in[grow * a.actions_in_stride + t] : 0;
                 if (given < 0 || given >= n) {
                     if (j == 0) err_bits |= RL4CO_ERR_INFEASIBLE;
                     given = 0;
                 }
             }
-            const uint32_t nkey = (a.mode == RL4CO_MODE_SAMPLING) ? noise_key(a.seed, a.inst_offset + b, row, t) : 0u;
+            const uint32_t nkey = (MODE == RL4CO_MODE_SAMPLING) ? noise_key(a.seed, a.inst_offset + b, row, t) : 0u;
 #ifdef R4_WARP_PROF   // experiment: per-warp select / env / step-end wait cycles of CTA 0 -> phase_cycles[16 + 4 warp + k]
             const long long wp0 = clock64();
 #endif
-            const RowSel sel = select_row(x, a, n, q, j, row, valid, grow, t, T, nkey, given, err_bits);
+            const RowSel sel = select_row<MODE>(x, a, n, q, j, row, valid, grow, t, T, nkey, given, err_bits);
             R4_STAMP(12);
 #ifdef R4_WARP_PROF
             const long long wp1 = clock64();
@@ -1153,13 +1193,23 @@ int launch_rollout_tc(const rl4co_cache* cache, const rl4co_rollout_args& a, cud
     const size_t smem = tc::smem_bytes(npad);
     const unsigned char* img = reinterpret_cast<const unsigned char*>(cache->tc_img);
     int rc;
-    if (a.env == RL4CO_ENV_TSP) {
-        if ((rc = tc_prepare(tc::rollout_tc_kernel<RL4CO_ENV_TSP>, npad, "rollout_tc"))) return rc;
-        tc::rollout_tc_kernel<RL4CO_ENV_TSP><<<tc_grid(cache->B), tc::kThreads, smem, st>>>(*cache, a, img, npad);
+#define R4_LAUNCH_TC(ENV_, MODE_)                                                                                \
+    do {                                                                                                         \
+        if ((rc = tc_prepare(tc::rollout_tc_kernel<ENV_, MODE_>, npad, "rollout_tc"))) return rc;                \
+        tc::rollout_tc_kernel<ENV_, MODE_><<<tc_grid(cache->B), tc::kThreads, smem, st>>>(*cache, a, img, npad); \
+    } while (0)
+    const bool tsp = a.env == RL4CO_ENV_TSP;
+    if (a.mode == RL4CO_MODE_GREEDY) {
+        if (tsp) R4_LAUNCH_TC(RL4CO_ENV_TSP, RL4CO_MODE_GREEDY);
+        else R4_LAUNCH_TC(RL4CO_ENV_CVRP, RL4CO_MODE_GREEDY);
+    } else if (a.mode == RL4CO_MODE_SAMPLING) {
+        if (tsp) R4_LAUNCH_TC(RL4CO_ENV_TSP, RL4CO_MODE_SAMPLING);
+        else R4_LAUNCH_TC(RL4CO_ENV_CVRP, RL4CO_MODE_SAMPLING);
     } else {
-        if ((rc = tc_prepare(tc::rollout_tc_kernel<RL4CO_ENV_CVRP>, npad, "rollout_tc"))) return rc;
-        tc::rollout_tc_kernel<RL4CO_ENV_CVRP><<<tc_grid(cache->B), tc::kThreads, smem, st>>>(*cache, a, img, npad);
+        if (tsp) R4_LAUNCH_TC(RL4CO_ENV_TSP, RL4CO_MODE_EVALUATE);
+        else R4_LAUNCH_TC(RL4CO_ENV_CVRP, RL4CO_MODE_EVALUATE);
     }
+#undef R4_LAUNCH_TC
     R4_CHECK_LAUNCH("rollout_tc");
     return RL4CO_OK;
 }
