@@ -67,6 +67,8 @@ struct Smem {
     uint32_t tmem_ptr;
     uint32_t pad_;
     float lnf[4][kRows];        // ln(#feasible nodes) of the row at the previous step, one private copy per thread
+    float lnf_depot[4][kRows];  // CVRP: the same at the row's last step AT THE DEPOT (< 0: none yet) ...
+    float lse_depot[2][4][kRows];   // ... and the log-sum-exp of the thread's two heads at that step
 };
 
 // Shared-memory map: [Smem][Q hi][Q lo][K_hi][K_lo][L_hi][L_lo][Vt_hi][Vt_lo].  Everything but the tile size is a
@@ -510,6 +512,7 @@ __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cach
     // of scores(1) and the next step's Q build (8 KB = 128 threads x 16 words, conflict-free)
     float* stash = reinterpret_cast<float*>(x.q_p(j)) + (threadIdx.x & 127);
     float hv[16];
+    const bool at_depot = (ENV == RL4CO_ENV_CVRP) && x.s()->cur[row] == 0;
     build_q<ENV>(x, c, b, S, j, j, q, lane);
     team_sync(j);
     R4_STAMP(0);
@@ -522,7 +525,17 @@ __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cach
         const int nf = __popc(x.s()->maskw[0][row]) + __popc(x.s()->maskw[1][row]) + __popc(x.s()->maskw[2][row]) +
                        __popc(x.s()->maskw[3][row]);
         const float lnf = __logf((float)(nf > 0 ? nf : 1));
-        const float shift = have_ref ? 0.5f * (lnf - x.s()->lnf[j][row]) : 0.f;   // first step: no reference yet
+        // openings are abrupt (1 -> 60 nodes when a full vehicle returns), closings gradual: all of an increase
+        const float dl = lnf - x.s()->lnf[j][row];
+        float shift = have_ref ? (dl > 0.f ? 1.0f : 0.5f) * dl : 0.f;              // first step: no reference yet
+        // CVRP at the depot: the query is the same every time the row is there (cur = depot, full capacity), only
+        // the mask has shrunk, while the step before (a nearly empty vehicle at a customer) says little about it:
+        // the reference comes from the row's previous depot step.
+        if (ENV == RL4CO_ENV_CVRP && have_ref && at_depot && x.s()->lnf_depot[j][row] >= 0.f) {
+            shift = lnf - x.s()->lnf_depot[j][row];
+            lse[0] = x.s()->lse_depot[0][j][row];
+            lse[1] = x.s()->lse_depot[1][j][row];
+        }
         x.s()->lnf[j][row] = lnf;
         lse[0] += shift;
         lse[1] += shift;
@@ -567,6 +580,10 @@ __device__ __forceinline__ void decode_step_gemms(const Ctx& x, const rl4co_cach
         }
         const float inv_l = l > 0.f ? 1.0f / l : 0.f;
         lse[g] = l > 0.f ? m + __logf(l) : 0.f;
+        if (ENV == RL4CO_ENV_CVRP && at_depot) {
+            x.s()->lse_depot[g][j][row] = lse[g];
+            if (g == 1) x.s()->lnf_depot[j][row] = x.s()->lnf[j][row];
+        }
         R4_STAMP(2 + 5 * g);
         if (issuer_warp) { if (elect_one()) issue_pv(x, h, j); }
         if (g == 0) build_q<ENV>(x, c, b, S, 4 + j, j, q, lane);   // next round's Q while PV runs (scores(0) is done)
@@ -1008,6 +1025,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             st.word = 0u;            // cvrp/env.py:102-130: nothing visited
         }
         int err_bits = 0;
+        s->lnf_depot[j][row] = -1.f;
         // forced first action (decoding.py:305-327; select_start_nodes ops.py:147-161)
         int act = 0;
         if (valid) {
@@ -1124,6 +1142,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             }
         }
         s->maskw[j][row] = word;
+        s->lnf_depot[j][row] = -1.f;
         mbar_wait(&s->tma_bar, tma_par);
         tma_par ^= 1u;
         __syncthreads();
