@@ -278,7 +278,7 @@ def run_b200(args):
             "gpu_launches": 2 * len(kernel_ms),      # per step: r4::tc::tc_pack_kernel + r4::tc::rollout_tc_kernel
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": measured_traffic(), "peak_source": peak_src,
-                         "kernel": "r4::tc::rollout_tc_kernel<TSP>", "kernel_ms": k_ms,
+                         "kernel": "r4::tc::rollout_tc_kernel<TSP, GREEDY>", "kernel_ms": k_ms,
                          "algorithmic_bytes_per_launch": ALGO_BYTES_PER_INSTANCE_STEP * isteps,
                          "note": "algorithmic bytes per SURVEY.md §8(d) (K,V,L re-read every step); the "
                                  "kernel keeps the operand tiles in shared memory for the whole rollout, so "

@@ -998,8 +998,13 @@ __global__ void __launch_bounds__(kThreads, 1)
     const bool valid = row < S;
     uint32_t tma_par = 0, mma_par = 0, team_par = 0;
     // optional phase timing (debug): thread 0 of CTA 0 accumulates clock64 deltas per phase
+#ifdef R4_PHASE_PROF   // profile builds only (profiles/phase.sh): the counters cost four registers of a full budget
     long long* prof = (a.phase_cycles != nullptr && blockIdx.x == 0 && threadIdx.x == 0) ? a.phase_cycles : nullptr;
     long long tprev = clock64();
+#else
+    long long* const prof = nullptr;
+    long long tprev = 0;
+#endif
 
     for (int64_t b = blockIdx.x; b < c.B; b += gridDim.x) {
         if (threadIdx.x == 0) load_tiles(x, smem, img, b);

@@ -1,6 +1,6 @@
 """In-kernel phase timing of the tensor-path rollout kernel (debug counter rl4co_rollout_args.phase_cycles):
 clock64 cycles thread 0 of CTA 0 spends in each phase, accumulated over its instances and steps.
-usage (GPU box): python profiles/phase_timing.py [B] [tsp|cvrp] [decode_type]"""
+usage: profiles/phase.sh [B] [tsp|cvrp] [decode_type]   (needs the -DR4_PHASE_PROF build; the product build reports zeros)"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
