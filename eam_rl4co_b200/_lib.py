@@ -32,7 +32,7 @@ EXPORTS = [
     "rl4co_b200_abi_version", "rl4co_last_error", "rl4co_tsp_step", "rl4co_cvrp_step_mask",
     "rl4co_cvrp_action_mask", "rl4co_tour_reward", "rl4co_select", "rl4co_decode_step",
     "rl4co_rollout", "rl4co_noise_gumbel", "rl4co_tc_image_bytes", "rl4co_tc_pack", "rl4co_tc_decode_step",
-    "rl4co_enc_packed_bytes", "rl4co_enc_pack_weight", "rl4co_enc_linear", "rl4co_enc_attention", "rl4co_best_of_starts", "rl4co_generate_instances",
+    "rl4co_enc_packed_bytes", "rl4co_enc_pack_weight", "rl4co_enc_linear", "rl4co_enc_attention", "rl4co_best_of_starts", "rl4co_generate_instances", "rl4co_replay_states",
 ]
 
 

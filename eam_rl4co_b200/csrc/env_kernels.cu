@@ -120,6 +120,71 @@ __global__ void cvrp_mask_kernel(const float* __restrict__ demand, int64_t deman
                   visited + row * n, cur[row], mask_out + row * n, n, lane);
 }
 
+// ---- teacher-forced state replay (the training caller) --------------------------------
+// Replays actions [rows, T] (start-major rows, row = s*B + b) through _step / get_action_mask
+// (tsp/env.py:62-88, cvrp/env.py:68-100,132-144) and writes what the decoder sees BEFORE step t = 1..T-1, directly
+// in instance-major order [B, S, T-1, ...]: current node, feasibility mask, remaining capacity (CVRP).  One warp
+// per row, lanes own nodes (visited flags in a register bit per 32-node block), one launch instead of T env steps.
+__global__ void replay_states_kernel(int env, const int64_t* __restrict__ actions, int64_t rows, int32_t T,
+                                     int64_t B, int32_t n, const float* __restrict__ demand,
+                                     const float* __restrict__ cap, int64_t* __restrict__ cur_out,
+                                     uint8_t* __restrict__ mask_out, float* __restrict__ rem_out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = blockIdx.x * (int64_t)kWarpsPerBlock + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int64_t b = row % B, sidx = row / B, S = rows / B;
+    const int64_t orow = (b * S + sidx) * (int64_t)(T - 1);     // first [b, s, 0] element
+    const int64_t* arow = actions + row * (int64_t)T;
+    const float* drow = (env == RL4CO_ENV_CVRP) ? demand + b * (int64_t)(n - 1) : nullptr;
+    const float capv = (env == RL4CO_ENV_CVRP) ? cap[b] : 1.f;
+    const float lim = capv + 1e-5f;                             // cvrp/env.py:135, fp32 add
+    uint32_t vis = 0u;                                          // bit k: node 32k + lane visited
+    float used = 0.f;
+    float dm[4] = {0.f, 0.f, 0.f, 0.f};                         // demand of this lane's nodes
+    if (env == RL4CO_ENV_CVRP) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int node = 32 * k + lane;
+            if (node >= 1 && node < n) dm[k] = drow[node - 1];
+        }
+    }
+    for (int t = 1; t < T; ++t) {
+        const int64_t a64 = arow[t - 1];
+        const int a = (int)a64;
+        if ((a & 31) == lane && a >= 0 && a < n) vis |= 1u << (a >> 5);     // scatter(-1, action, .)
+        if (env == RL4CO_ENV_CVRP) {
+            int di = a - 1;                                     // clamp(current_node - 1, 0, n_loc - 1)  :73-75
+            di = di < 0 ? 0 : (di > n - 2 ? n - 2 : di);
+            used = (used + drow[di]) * ((a != 0) ? 1.0f : 0.0f);            // :78-80 (same two fp32 ops)
+        }
+        uint8_t* mrow = mask_out + (orow + (t - 1)) * (int64_t)n;
+        int n_free = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int node = 32 * k + lane;
+            bool feas = false;
+            if (node < n) {
+                if (env == RL4CO_ENV_TSP) {
+                    feas = !((vis >> k) & 1u);                  // tsp/env.py:68-70
+                    mrow[node] = feas ? 1 : 0;
+                } else if (node >= 1) {
+                    const bool exceeds = (dm[k] + used) > lim;  // cvrp/env.py:135
+                    feas = !(((vis >> k) & 1u) || exceeds);     // :138
+                    mrow[node] = feas ? 1 : 0;
+                }
+            }
+            if (32 * k < n) n_free += __popc(__ballot_sync(kFull, feas && node >= 1));
+        }
+        if (lane == 0) {
+            if (env == RL4CO_ENV_CVRP) {
+                mrow[0] = ((a == 0) && (n_free > 0)) ? 0 : 1;   // :141-144
+                rem_out[orow + (t - 1)] = capv - used;
+            }
+            cur_out[orow + (t - 1)] = a64;
+        }
+    }
+}
+
 // ---- _get_reward + check_solution_validity --------------------------------------------
 // tsp/env.py:152-168, cvrp/env.py:146-185, ops.py:82-95.  One warp per row; lanes own
 // tour positions; edge lengths summed with a warp tree.
@@ -263,5 +328,21 @@ extern "C" int rl4co_tour_reward(int32_t env, const float* locs, int64_t loc_row
         env, locs, loc_rows, actions, actions_row_stride, T, demand, demand_rows, vehicle_capacity,
         reward, check, err, rows, n_nodes);
     R4_CHECK_LAUNCH("tour_reward");
+    return RL4CO_OK;
+}
+
+extern "C" int rl4co_replay_states(int32_t env, const int64_t* actions, int64_t rows, int32_t T, int64_t B,
+                                   int32_t n_nodes, const float* demand, const float* vehicle_capacity,
+                                   int64_t* cur_out, uint8_t* mask_out, float* rem_out, void* stream) {
+    R4_CHECK_ARG(env == RL4CO_ENV_TSP || env == RL4CO_ENV_CVRP, "replay_states: bad env %d", env);
+    R4_CHECK_ARG(rows >= 0 && B > 0 && rows % B == 0 && T >= 1 && n_nodes > 1 && n_nodes <= 128,
+                 "replay_states: bad sizes (n_nodes <= 128)");
+    if (rows == 0 || T == 1) return RL4CO_OK;
+    R4_CHECK_ARG(actions && cur_out && mask_out, "replay_states: null pointer");
+    if (env == RL4CO_ENV_CVRP) R4_CHECK_ARG(demand && vehicle_capacity && rem_out, "replay_states: CVRP needs demand, capacity, rem_out");
+    unsigned grid = (unsigned)((rows + kWarpsPerBlock - 1) / kWarpsPerBlock);
+    replay_states_kernel<<<grid, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(
+        env, actions, rows, T, B, n_nodes, demand, vehicle_capacity, cur_out, mask_out, rem_out);
+    R4_CHECK_LAUNCH("replay_states");
     return RL4CO_OK;
 }

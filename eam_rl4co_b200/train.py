@@ -15,13 +15,14 @@ sample-while-recording pass.
 Multi-GPU: instances are sharded, the shared baseline is per instance and therefore local,
 and the step ends with ONE flat-buffer all-reduce of gradients + logged sums (`sharding.allreduce_mean_`).
 """
+import ctypes as C
 import math
 from typing import Dict, Optional
 
 import torch
 import torch.nn.functional as F
 
-from . import sharding
+from . import _lib, sharding
 from .tensordict_lite import batchify
 
 
@@ -40,6 +41,8 @@ def teacher_forced_states(env, td, actions: torch.Tensor, num_starts: int) -> Di
         raise NotImplementedError("evaluate_log_likelihood covers the multistart form (num_starts > 1)")
     T = actions.shape[1]
     cvrp = env.name == "cvrp"
+    if actions.is_cuda and td["action_mask"].shape[-1] <= 128:
+        return _replay_states_kernel(td, actions.contiguous(), S, cvrp)
     tdb = batchify(td, S)
     tdb.set("action", actions[:, 0].contiguous())
     tdb = env.step(tdb)["next"]
@@ -55,6 +58,29 @@ def teacher_forced_states(env, td, actions: torch.Tensor, num_starts: int) -> Di
            "mask": _to_bs(torch.stack(mask, 1), S), "taken": _to_bs(actions[:, 1:], S), "td": tdb}
     if cvrp:
         out["rem"] = _to_bs(torch.stack(rem, 1), S)
+    return out
+
+
+def _replay_states_kernel(td, actions: torch.Tensor, S: int, cvrp: bool) -> Dict[str, torch.Tensor]:
+    """The same states from ONE launch of rl4co_replay_states (T-1 env steps per row inside the kernel), written
+    directly in [B, S, T-1, ...] order."""
+    rows, T = actions.shape
+    B = rows // S
+    n = td["action_mask"].shape[-1]
+    dev = actions.device
+    cur = torch.empty(B, S, T - 1, dtype=torch.int64, device=dev)
+    mask = torch.empty(B, S, T - 1, n, dtype=torch.bool, device=dev)
+    rem = torch.empty(B, S, T - 1, dtype=torch.float32, device=dev) if cvrp else None
+    demand = td["demand"].reshape(B, n - 1).contiguous().float() if cvrp else None
+    cap = td["vehicle_capacity"].reshape(B).contiguous().float() if cvrp else None
+    rc = _lib.lib().rl4co_replay_states(
+        C.c_int32(_lib.ENV_CVRP if cvrp else _lib.ENV_TSP), _lib.ptr(actions), C.c_int64(rows), C.c_int32(T),
+        C.c_int64(B), C.c_int32(n), _lib.ptr(demand), _lib.ptr(cap), _lib.ptr(cur), _lib.ptr(mask), _lib.ptr(rem),
+        _lib.stream_ptr())
+    _lib.check(rc, "rl4co_replay_states")
+    out = {"first": _to_bs(actions[:, 0], S), "cur": cur, "mask": mask, "taken": _to_bs(actions[:, 1:], S), "td": None}
+    if cvrp:
+        out["rem"] = rem
     return out
 
 

@@ -81,6 +81,15 @@ int rl4co_cvrp_action_mask(const float* demand, int64_t demand_rows, const float
                            const int64_t* current_node, uint8_t* mask_out, int64_t rows,
                            int32_t n_nodes, void* stream);
 
+/* ---- teacher-forced state replay for the differentiable evaluate (constructive/base.py:221-229 with actions=) ------
+ * actions [rows, T] start-major (row = s*B + b).  Applies _step / get_action_mask (tsp/env.py:62-88,
+ * cvrp/env.py:68-100,132-144) T-1 times in one launch and writes the decoder's inputs before step t = 1..T-1 in
+ * instance-major order: cur_out [B,S,T-1] i64, mask_out [B,S,T-1,n_nodes] bool, rem_out [B,S,T-1] f32
+ * (vehicle_capacity - used_capacity, CVRP only; null for TSP).  demand [B, n_nodes-1], vehicle_capacity [B].     */
+int rl4co_replay_states(int32_t env, const int64_t* actions, int64_t rows, int32_t T, int64_t B,
+                        int32_t n_nodes, const float* demand, const float* vehicle_capacity,
+                        int64_t* cur_out, uint8_t* mask_out, float* rem_out, void* stream);
+
 /* ---- _get_reward (+ check_solution_validity) ------------------------------------------
  * tsp/env.py:152-168, cvrp/env.py:146-185, ops.py:59-95.
  * locs [loc_rows, n_nodes, 2] (CVRP: depot at node 0); row r uses locs row r % loc_rows.
