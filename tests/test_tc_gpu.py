@@ -122,6 +122,29 @@ def test_tc_rollout_matches_fp32_rollout_and_oracle(env_name, N, B, decode_type)
     compare_rollout(env_name, inst, h.cpu(), w, False, a, decode_type, noise_seed=77)
 
 
+# sizes on the edges of the tensor path: S = 8 (smallest multistart the path takes), node counts on both sides of the
+# 16-node MMA granule and of the 32-node mask words, tails of <= 12 real nodes in the last chunk, and the largest
+# tile (112 nodes; CVRP: 111 customers + depot, S = 111)
+@pytest.mark.parametrize("env_name,N", [("tsp", 8), ("tsp", 13), ("tsp", 16), ("tsp", 17), ("tsp", 33), ("tsp", 96),
+                                        ("tsp", 97), ("tsp", 112), ("cvrp", 8), ("cvrp", 15), ("cvrp", 16),
+                                        ("cvrp", 111)])
+def test_tc_rollout_boundary_sizes(env_name, N):
+    B = 2
+    inst, pol, w, env, td, h = _setup(env_name, N, B, seed=3)
+    a = pol(td.clone(), env, decode_type="multistart_greedy", impl=_lib.IMPL_TC)
+    b = pol(td.clone(), env, decode_type="multistart_greedy", impl=_lib.IMPL_FP32)
+    assert a["actions"].shape[0] == B * N
+    T = max(a["actions"].shape[1], b["actions"].shape[1])
+    pad = lambda x: torch.nn.functional.pad(x, (0, T - x.shape[1]))
+    same = (pad(a["actions"]) == pad(b["actions"])).all(1)
+    assert same.float().mean().item() >= 0.95
+    assert rel_close(a["reward"][same], b["reward"][same], LL_RTOL)
+    assert rel_close(a["log_likelihood"][same], b["log_likelihood"][same], LL_RTOL)
+    compare_rollout(env_name, inst, h.cpu(), w, False, a, "multistart_greedy")
+    s = pol(td.clone(), env, decode_type="multistart_sampling", noise_seed=5, impl=_lib.IMPL_TC)
+    compare_rollout(env_name, inst, h.cpu(), w, False, s, "multistart_sampling", noise_seed=5)
+
+
 @pytest.mark.parametrize("env_name", ["tsp", "cvrp"])
 def test_tc_evaluate_and_store_all_logp(env_name):
     N, B = 20, 4
