@@ -183,3 +183,21 @@ def test_tc_full_size_properties():
     assert same >= 0.99, same
     ev = pol(td.clone(), env, actions=a, num_starts=N, impl=_lib.IMPL_FP32)
     assert rel_close(ev["log_likelihood"], out["log_likelihood"], LL_RTOL)
+
+
+@pytest.mark.parametrize("decode_type", ["multistart_greedy", "multistart_sampling"])
+def test_tc_full_size_properties_cvrp(decode_type):
+    """c5 shape (CVRP100, S=100) with several instances per CTA: size-independent properties of the tours (every
+    customer once, capacity never exceeded, reward = recomputed length) and the log-likelihood of the same actions
+    re-evaluated teacher-forced by the fp32 kernels.  Sampling runs the exponential-race selection and, with rows
+    returning to the depot at random, the feasible-set terms of the softmax reference."""
+    N, B = 100, 160
+    inst, pol, w, env, td, h = _setup("cvrp", N, B, seed=5)
+    out = pol(td.clone(), env, decode_type=decode_type, noise_seed=11, impl=_lib.IMPL_TC)
+    a = out["actions"]
+    assert a.shape[0] == B * N
+    # cvrp/env.py:157-185 (every customer exactly once, demand served per route <= capacity) and :146-155
+    assert rel_close(out["reward"], env.get_reward(td, a, check_solution=True), 1e-6)
+    ev = pol(td.clone(), env, actions=a, num_starts=N, impl=_lib.IMPL_FP32)
+    assert rel_close(ev["log_likelihood"], out["log_likelihood"], LL_RTOL)
+    assert rel_close(ev["reward"], out["reward"], 1e-6)
