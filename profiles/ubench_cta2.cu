@@ -29,7 +29,7 @@ __device__ __forceinline__ void put(unsigned char* tile, int r, int k, float v) 
     *reinterpret_cast<__half*>(tile + (r >> 3) * kSBO + (k >> 3) * kLBO + (r & 7) * 16 + (k & 7) * 2) = __float2half(v);
 }
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) probe(float* out, int swap_b) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) probe(float* out, int swap_b, int ts_form) {
     __shared__ __align__(128) unsigned char a_tile[8 * kSBO];          // 64 rows x 16 halves
     __shared__ __align__(128) unsigned char b_tile[(kN / 16) * kSBO];  // N/2 rows x 16 halves
     __shared__ uint64_t bar;
@@ -72,11 +72,34 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) probe(float*
         for (int c = 0; c < 64; c += 8) tmem_st8(tmem + ((uint32_t)(32 * warp) << 16) + c, z);
         tc_wait_st();
     }
+    if (ts_form) {
+        // A operand in TMEM columns [32, 40): every lane offers a row; lanes 0..63 say "row 64 rank + lane", lanes 64..127
+        // say "500 + ..." so that D tells which lanes the pair-MMA reads its A rows from
+        const int l = threadIdx.x;
+        const float v = (l < 64) ? (float)(64 * rank + l) : (float)(500 + 64 * rank + (l - 64));
+        const __half2 w0 = __floats2half2_rn(v, 1.0f);
+        uint32_t a8[8] = {*reinterpret_cast<const uint32_t*>(&w0), 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+        tmem_st8(tmem + ((uint32_t)(32 * warp) << 16) + 32u, a8);
+        tc_wait_st();
+    }
     tc_fence_before();
     __syncthreads();
     cluster_sync_all();
     tc_fence_after();
-    if (rank == 0 && threadIdx.x == 0) {
+    if (rank == 0 && threadIdx.x == 0 && ts_form) {
+        const uint32_t id = idesc_f16(128, kN);
+        const uint64_t bd = smem_desc(smem_u32(b_tile), kLBO, kSBO);
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem),
+            "r"(tmem + 32u), "l"(bd), "r"(id), "r"(0u)
+            : "memory");
+        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                         smem_u32(&bar)),
+                     "h"((uint16_t)3)
+                     : "memory");
+    }
+    if (rank == 0 && threadIdx.x == 0 && !ts_form) {
         const uint32_t id = idesc_f16(128, kN);
         const uint64_t ad = smem_desc(smem_u32(a_tile), kLBO, kSBO);
         const uint64_t bd = smem_desc(smem_u32(b_tile), kLBO, kSBO);
@@ -107,9 +130,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) probe(float*
 int main() {
     float* d;
     cudaMalloc(&d, 2 * 128 * 64 * sizeof(float));
-    for (int swap_b = 0; swap_b < 2; ++swap_b) {
+    for (int mode = 0; mode < 3; ++mode) {
+        const int swap_b = mode == 1, ts_form = mode == 2;
         cudaMemset(d, 0, 2 * 128 * 64 * sizeof(float));
-        probe<<<2, 128>>>(d, swap_b);
+        probe<<<2, 128>>>(d, swap_b, ts_form);
         cudaError_t e = cudaDeviceSynchronize();
         if (e != cudaSuccess) {
             printf("swap_b=%d: %s\n", swap_b, cudaGetErrorString(e));
@@ -117,13 +141,13 @@ int main() {
         }
         std::vector<float> h(2 * 128 * 64);
         cudaMemcpy(h.data(), d, h.size() * sizeof(float), cudaMemcpyDeviceToHost);
-        printf("== B rows [0,N/2) provided by CTA %d ==\n", swap_b);
+        printf("== %s; B rows [0,N/2) provided by CTA %d ==\n", ts_form ? "A from TMEM columns [32,40)" : "A from shared memory", swap_b);
         for (int cta = 0; cta < 2; ++cta) {
             printf("CTA %d: lane -> (row of D, first columns as D column index; '.' = untouched)\n", cta);
             for (int lane = 0; lane < 128; lane += 1) {
                 if (!(lane % 32 < 3 || lane % 32 == 15 || lane % 32 == 16 || lane % 32 == 31)) continue;
                 printf("  lane %3d:", lane);
-                for (int c = 0; c < 40; c += (c < 4 ? 1 : 12)) {
+                for (int c = 0; c < 28; c += (c < 2 ? 1 : 13)) {
                     const float v = h[(cta * 128 + lane) * 64 + c];
                     if (v != v) printf("  c%-2d .      ", c);
                     else printf("  c%-2d r%3d n%3d", c, (int)v, (int)((v - (int)v) * 256.f + 0.5f));
