@@ -6,7 +6,6 @@ import json, os, statistics, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import eam_rl4co_b200 as P
-from oracle import rollout_oracle as O      # instance generators only (test infrastructure, not timed)
 import bench
 
 CONFIGS = [  # name, env, N, B, policy, decode_type, algorithmic bytes per instance-step
@@ -25,7 +24,8 @@ def main():
     out = []
     for name, env_name, N, B, pk, dt, abytes in CONFIGS:
         torch.manual_seed(1234)
-        inst = O.generate_tsp(B, N) if env_name == "tsp" else O.generate_cvrp(B, N)
+        gen = P.TSPGenerator(num_loc=N) if env_name == "tsp" else P.CVRPGenerator(num_loc=N)
+        inst = {k: v for k, v in gen(B).items() if k != "capacity"}
         torch.manual_seed(4321)
         pol = (P.POMOPolicy(env_name) if pk == "pomo" else P.AttentionModelPolicy(env_name=env_name)).eval().to(dev)
         env = P.get_env(env_name, generator_params=dict(num_loc=N), device=dev)

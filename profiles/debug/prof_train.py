@@ -3,7 +3,6 @@ sys.path.insert(0, "/root/repo")
 import torch
 import eam_rl4co_b200 as P
 from eam_rl4co_b200 import train as T
-from oracle import rollout_oracle as O
 from torch.profiler import profile, ProfilerActivity
 dev = torch.device("cuda", 0)
 B = 64
@@ -11,7 +10,7 @@ torch.manual_seed(4321)
 pol = P.POMOPolicy("cvrp").to(dev).train()
 env = P.get_env("cvrp", generator_params=dict(num_loc=100), device=dev)
 torch.manual_seed(1234)
-inst = O.generate_cvrp(B, 100)
+inst = {k: v for k, v in P.CVRPGenerator(num_loc=100)(B).items() if k != "capacity"}
 td = env.reset(P.TensorDict({k: v.to(dev) for k, v in inst.items()}, batch_size=[B]))
 def step(it):
     with torch.no_grad():

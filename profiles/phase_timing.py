@@ -21,12 +21,11 @@ def main():
         env = P.TSPEnv(generator_params=dict(num_loc=bench.N_NODES), device=dev)
         inst = {"locs": bench.make_instances(B)}
     else:
-        from oracle import rollout_oracle as O      # instance generator only
         torch.manual_seed(4321)
         pol = P.POMOPolicy("cvrp").eval().to(dev)
         env = P.get_env("cvrp", generator_params=dict(num_loc=bench.N_NODES), device=dev)
         torch.manual_seed(1234)
-        inst = O.generate_cvrp(B, bench.N_NODES)
+        inst = {k: v for k, v in P.CVRPGenerator(num_loc=bench.N_NODES)(B).items() if k != "capacity"}
     td = env.reset(P.TensorDict({k: v.to(dev) for k, v in inst.items()}, batch_size=[B]))
     with torch.no_grad():
         h, _ = pol.encoder(td)

@@ -6,7 +6,6 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import eam_rl4co_b200 as P
 from eam_rl4co_b200 import train as T
-from oracle import rollout_oracle as O      # instance generator only
 
 
 def main():
@@ -17,7 +16,7 @@ def main():
     opt = torch.optim.Adam(pol.parameters(), lr=1e-4)
     env = P.get_env("cvrp", generator_params=dict(num_loc=100), device=dev)
     torch.manual_seed(1234)
-    inst = O.generate_cvrp(B, 100)
+    inst = {k: v for k, v in P.CVRPGenerator(num_loc=100)(B).items() if k != "capacity"}
     td = env.reset(P.TensorDict({k: v.to(dev) for k, v in inst.items()}, batch_size=[B]))
     ev = lambda: torch.cuda.Event(enable_timing=True)
     rows = []
