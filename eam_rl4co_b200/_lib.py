@@ -25,8 +25,8 @@ ERR_MESSAGES = [  # (bit, reference assertion text); first match is raised
     (32, "Exceeded maximum number of steps during decoding"),
 ]
 IMPL_AUTO, IMPL_FP32, IMPL_TC = 0, 1, 2
-ENC_EPI_PLAIN, ENC_EPI_RELU, ENC_EPI_RES_NORM = 0, 1, 2
-ABI_VERSION = 2
+ENC_EPI_PLAIN, ENC_EPI_RELU, ENC_EPI_RES_NORM, ENC_EPI_RES_AFFINE = 0, 1, 2, 3
+ABI_VERSION = 3
 
 EXPORTS = [
     "rl4co_b200_abi_version", "rl4co_last_error", "rl4co_tsp_step", "rl4co_cvrp_step_mask",
@@ -68,7 +68,7 @@ class RolloutArgs(C.Structure):
                 ("actions_in", C.c_void_p), ("actions_in_stride", C.c_int64),
                 ("actions_in_T", C.c_int32), ("actions", C.c_void_p), ("logp", C.c_void_p),
                 ("logp_all", C.c_void_p), ("reward", C.c_void_p), ("log_likelihood", C.c_void_p),
-                ("lengths", C.c_void_p), ("max_len", C.c_void_p), ("err", C.c_void_p), ("impl", C.c_int32),
+                ("lengths", C.c_void_p), ("max_len", C.c_void_p), ("err", C.c_void_p), ("impl", C.c_int32), ("start_mod", C.c_int32),
                 ("phase_cycles", C.c_void_p)]
 
 

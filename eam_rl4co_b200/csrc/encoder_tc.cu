@@ -32,7 +32,9 @@ constexpr uint32_t kTile = 2 * kHalf;       // 64 KB
 constexpr int kStage = 132;                 // fp32 staging row stride (floats): 16-byte row writes are conflict-free
 constexpr int kRing = 36;                   // store slot row stride: 32 output columns + 16 B pad (same bank argument)
 
-enum { EPI_PLAIN = 0, EPI_RELU = 1, EPI_RES_NORM = 2 };
+// EPI_RES_AFFINE: Y = (R + X W^T + b) * gamma + beta with per-channel gamma / beta = eval-mode BatchNorm1d folded by the
+// host (nn/ops.py:46-47 with running statistics: gamma = w / sqrt(var + eps), beta = b - mean * gamma)
+enum { EPI_PLAIN = 0, EPI_RELU = 1, EPI_RES_NORM = 2, EPI_RES_AFFINE = 3 };
 
 struct Smem {
     uint64_t tma_bar[2];
@@ -263,7 +265,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             // A tile of the next instance while the epilogue warps drain TMEM (all MMAs that read xs are complete);
             // its first W tile too when W buffer 0 is not part of the epilogue's staging area
             const int64_t bn = b + gridDim.x;
-            if (EPI != EPI_RES_NORM && warp == 4) {
+            if (EPI < EPI_RES_NORM && warp == 4) {
                 if (elect_one()) {
                     tile0_in_flight = bn < B;
                     if (tile0_in_flight) {
@@ -276,7 +278,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             if (bn < B) convert_x(X + bn * (int64_t)n * K, n, K, 0, xs);
             fence_proxy_async();
         }
-        if (EPI != EPI_RES_NORM) {
+        if (EPI < EPI_RES_NORM) {
             // TMEM -> registers -> (+bias, relu) -> the warp's staging slot (thread = row) -> coalesced stores (8 lanes
             // per 128-byte row segment).  Lane-per-row stores straight from registers cost one L1 transaction per
             // 16 bytes and made this epilogue 70 % of the kernel; through the slot it is one per 128 bytes.  A warp
@@ -338,7 +340,7 @@ __global__ void __launch_bounds__(kThreads, 1)
                 }
             }
             bar_sync(1, 128);                            // the four epilogue warps
-            {
+            if (EPI == EPI_RES_NORM) {
                 // column statistics, two passes (mean, then biased variance).  A warp takes every fourth node row
                 // and a lane four channels: the residual rows are read as coalesced 512-byte segments, all of a
                 // warp's loads are in flight together, and the four partial sums meet in shared memory.
@@ -380,6 +382,15 @@ __global__ void __launch_bounds__(kThreads, 1)
                 const float4 g = *reinterpret_cast<const float4*>(gamma + c4);
                 const float4 be = *reinterpret_cast<const float4*>(beta + c4);
                 float4 o;
+                if (EPI == EPI_RES_AFFINE) {
+                    const float4 rr = *reinterpret_cast<const float4*>(Rb + (size_t)r * 128 + c4);
+                    o.x = __fadd_rn(__fmul_rn(rr.x + xv.x, g.x), be.x);
+                    o.y = __fadd_rn(__fmul_rn(rr.y + xv.y, g.y), be.y);
+                    o.z = __fadd_rn(__fmul_rn(rr.z + xv.z, g.z), be.z);
+                    o.w = __fadd_rn(__fmul_rn(rr.w + xv.w, g.w), be.w);
+                    *reinterpret_cast<float4*>(Yb + (size_t)r * 128 + c4) = o;
+                    continue;
+                }
                 o.x = __fadd_rn(__fmul_rn(__fmul_rn(xv.x - s->mean[c4], s->rstd[c4]), g.x), be.x);
                 o.y = __fadd_rn(__fmul_rn(__fmul_rn(xv.y - s->mean[c4 + 1], s->rstd[c4 + 1]), g.y), be.y);
                 o.z = __fadd_rn(__fmul_rn(__fmul_rn(xv.z - s->mean[c4 + 2], s->rstd[c4 + 2]), g.z), be.z);
@@ -772,6 +783,10 @@ extern "C" int rl4co_enc_linear(const float* X, const void* Wpacked, const float
             R4_CHECK_ARG(residual && gamma && beta && n_out == 128,
                          "enc_linear: the residual + instance-norm epilogue needs residual, gamma, beta and n_out = 128");
             return launch_linear<enc::EPI_RES_NORM>(X, Wpacked, bias, residual, gamma, beta, eps, Y, B, n, k, n_out, stream);
+        case enc::EPI_RES_AFFINE:
+            R4_CHECK_ARG(residual && gamma && beta && n_out == 128,
+                         "enc_linear: the residual + affine epilogue needs residual, gamma, beta and n_out = 128");
+            return launch_linear<enc::EPI_RES_AFFINE>(X, Wpacked, bias, residual, gamma, beta, 0.f, Y, B, n, k, n_out, stream);
         default:
             R4_CHECK_ARG(false, "enc_linear: unknown epilogue %d", epilogue);
     }

@@ -59,6 +59,8 @@ __device__ __forceinline__ void run_row(const rl4co_cache& c, const rl4co_rollou
     const int64_t row = (int64_t)s * c.B + b;  // start-major (ops.py:13-16)
     const int T = a.max_steps;
     const bool multistart = a.num_starts > 1;
+    const int ncust = (ENV == RL4CO_ENV_TSP) ? n : n - 1;
+    const int smod = (a.start_mod > 0 && a.start_mod <= ncust) ? a.start_mod : ncust;   // ops.py:147-161
     const float2* L = reinterpret_cast<const float2*>(a.locs) + b * (int64_t)n;
 
     // ---- reset (tsp/env.py:90-115, cvrp/env.py:102-130) ----
@@ -102,7 +104,7 @@ __device__ __forceinline__ void run_row(const rl4co_cache& c, const rl4co_rollou
             if (a.mode == RL4CO_MODE_EVALUATE)
                 act = (int)a.actions_in[row * a.actions_in_stride];
             else
-                act = (ENV == RL4CO_ENV_TSP) ? (s % n) : (s % (n - 1)) + 1;
+                act = (ENV == RL4CO_ENV_TSP) ? (s % smod) : (s % smod) + 1;
         } else {
             float4 q4 = row_query(ENV, c, b, first, cur, (ENV == RL4CO_ENV_TSP) && !started, cap - used, lane);
             const float4 hd = warp_glimpse(ip, q4, maskw, lane);

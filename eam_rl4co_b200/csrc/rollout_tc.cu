@@ -722,8 +722,11 @@ __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_a
 #pragma unroll
     for (int e = 0; e < 28; ++e) tv[e] = ((win >> e) & 1u) ? tv[e] : -INFINITY;   // :177
 
+    // The constant reference is only safe while exp(x - ref) >= exp(-2 sc) stays a normal float: sc <= 40
+    // (temperature 0.1 gives sc = 100 and every term would flush to zero -> lse = -inf).  Beyond that the row
+    // maximum is exchanged like in the unclipped case.
     float ref;                                                      // >= every x of the row
-    if (clipped) {
+    if (clipped && sc <= 40.0f) {
         ref = sc;
     } else {
         float lmax = -INFINITY;
@@ -773,7 +776,9 @@ __device__ __forceinline__ RowSel select_row(const Ctx& x, const rl4co_rollout_a
     }
     bar_sync(1 + q, 128);
     const float tot = (s->red_b[0][row] + s->red_b[1][row]) + (s->red_b[2][row] + s->red_b[3][row]);
-    if (tot != tot && valid) err_bits |= RL4CO_ERR_NAN_LOGITS;      // attention.py:303-304 (a feasible logit is NaN)
+    // attention.py:303-304 (a feasible logit is NaN); tot == 0 cannot happen with a feasible node (the maximum
+    // contributes exp(0) or at least exp(-2 sc)) and is flagged as the same numerical failure
+    if ((tot != tot || !(tot > 0.f)) && valid) err_bits |= RL4CO_ERR_NAN_LOGITS;
     const float lse = logf(tot);                                    // log_softmax(x)_e = (x_e - ref) - lse  :190
     if (a.logp_all != nullptr && valid) {
 #pragma unroll
@@ -996,6 +1001,8 @@ __global__ void __launch_bounds__(kThreads, 1)
     const int q = warp & 3, j = warp >> 2, row = 32 * q + lane;
     const int n = c.n_nodes, S = a.num_starts, T = a.max_steps;
     const bool valid = row < S;
+    const int ncust = (ENV == RL4CO_ENV_TSP) ? n : n - 1;
+    const int smod = (a.start_mod > 0 && a.start_mod <= ncust) ? a.start_mod : ncust;   // ops.py:147-161
     uint32_t tma_par = 0, mma_par = 0, team_par = 0;
     // optional phase timing (debug): thread 0 of CTA 0 accumulates clock64 deltas per phase
 #ifdef R4_PHASE_PROF   // profile builds only (profiles/phase.sh): the counters cost four registers of a full budget
@@ -1037,7 +1044,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             if (MODE == RL4CO_MODE_EVALUATE)
                 act = (int)a.actions_in[grow * a.actions_in_stride];
             else
-                act = (ENV == RL4CO_ENV_TSP) ? (row % n) : (row % (n - 1)) + 1;
+                act = (ENV == RL4CO_ENV_TSP) ? (row % smod) : (row % smod) + 1;
             if (act < 0 || act >= n) {
                 err_bits |= RL4CO_ERR_INFEASIBLE;
                 act = 0;

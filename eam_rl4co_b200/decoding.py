@@ -34,6 +34,14 @@ def calculate_entropy(logprobs):
     return entropy
 
 
+def fresh_noise_seed() -> int:
+    """Seed of the counter noise of ONE sampling rollout when the caller gives none: drawn from torch's global
+    CPU generator, so every call samples fresh noise (as `torch.multinomial` does in the reference,
+    decoding.py:403-417) while `torch.manual_seed` still makes a run reproducible.  Ranks that seed alike draw
+    alike; the noise itself is keyed by the global instance index, so sharded and unsharded runs agree."""
+    return int(torch.randint(0, 2 ** 31 - 1, (1,)).item())
+
+
 class DecodingStrategy:
     name = "base"
     mode = None
@@ -41,7 +49,7 @@ class DecodingStrategy:
     def __init__(self, temperature: float = 1.0, top_p: float = 0.0, top_k: int = 0,
                  mask_logits: bool = True, tanh_clipping: float = 0, num_starts: Optional[int] = None,
                  multistart: bool = False, select_start_nodes_fn=None, select_best: bool = False,
-                 store_all_logp: bool = False, noise_seed: int = 0, instance_offset: int = 0,
+                 store_all_logp: bool = False, noise_seed: Optional[int] = None, instance_offset: int = 0,
                  noise: Optional[torch.Tensor] = None, num_samples=None, multisample: bool = False,
                  **unused):
         if top_p or top_k:
@@ -57,7 +65,10 @@ class DecodingStrategy:
         self.num_starts = num_starts if multistart else None
         self.select_start_nodes_fn = select_start_nodes_fn
         self.select_best, self.store_all_logp = select_best, store_all_logp
-        self.noise_seed, self.instance_offset, self.noise = noise_seed, instance_offset, noise
+        if noise_seed is None:       # only sampling consumes the generator
+            noise_seed = fresh_noise_seed() if (self.mode == _lib.MODE_SAMPLING and noise is None) else 0
+        self.noise_seed = int(noise_seed) & 0xFFFFFFFF
+        self.instance_offset, self.noise = instance_offset, noise
         self.actions, self.logprobs = [], []
         self._B = None
 

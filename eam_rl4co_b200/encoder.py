@@ -8,9 +8,10 @@ state_dicts load unchanged.
 
 Two executions of the same arithmetic:
   * the plain-PyTorch modules below (differentiable: training, and any configuration the kernels do not cover);
-  * `GraphAttentionNetwork._forward_kernels`: under `torch.no_grad()` on CUDA with instance normalisation,
+  * `GraphAttentionNetwork._forward_kernels`: under `torch.no_grad()` on CUDA with instance normalisation (POMO)
+    or eval-mode batch normalisation (the AttentionModel default, running statistics = a per-channel affine),
     embed_dim 128, 8 heads and N' <= 128 the layers run on the tcgen05 kernels of csrc/encoder_tc.cu (split-fp16
-    GEMMs with the residual + instance norm fused into their epilogues, fp32 attention) - 5 launches per layer.
+    GEMMs with the residual + norm fused into their epilogues, tcgen05 attention) - 5 launches per layer.
 """
 import ctypes as C
 
@@ -108,18 +109,39 @@ class GraphAttentionNetwork(nn.Module):
         self.num_heads, self.embed_dim, self.normalization = num_heads, embed_dim, normalization
         self.feedforward_hidden = feedforward_hidden
         self.use_kernels = True        # set False to force the PyTorch modules
-        self._packed = {}              # id(weight) -> (version, packed tiles)
+        self._packed = {}              # id(weight) -> (stamp, packed tiles)
 
     def kernels_apply(self, x):
+        norm_ok = self.normalization == "instance" or (self.normalization == "batch" and not self.training)
         return (self.use_kernels and x.is_cuda and not torch.is_grad_enabled() and x.dtype == torch.float32
-                and self.normalization == "instance" and self.embed_dim == 128 and self.num_heads == 8
+                and norm_ok and self.embed_dim == 128 and self.num_heads == 8
                 and self.feedforward_hidden % 128 == 0 and self.feedforward_hidden <= 512 and x.shape[1] <= 128)
 
+    def invalidate_packed(self):
+        """Drop the packed fp16 weight tiles (they are rebuilt on the next kernel forward).  Called by
+        `load_state_dict` / `_apply`; call it yourself after writing weights through `.data` in a way that keeps
+        the storage and the version counter (EMA / SWA helpers)."""
+        self._packed.clear()
+
+    def _apply(self, fn, *a, **kw):
+        self._packed.clear()
+        return super()._apply(fn, *a, **kw)
+
+    def _load_from_state_dict(self, *a, **kw):
+        self._packed.clear()
+        return super()._load_from_state_dict(*a, **kw)
+
+    @staticmethod
+    def _stamp(w):
+        # `_version` moves with in-place updates autograd can see (optimiser steps), data_ptr with re-allocation
+        # (`.to`, `load_state_dict(assign=True)`); writes through `.data` that keep both need invalidate_packed()
+        return (w._version, w.data_ptr(), w.device)
+
     def _pack(self, w):
-        """nn.Linear weight -> MMA tiles; cached per parameter version (in-place optimiser steps bump it)."""
-        key, ver = id(w), w._version
+        """nn.Linear weight -> MMA tiles; cached per (parameter version, storage)."""
+        key, ver = id(w), self._stamp(w)
         hit = self._packed.get(key)
-        if hit is not None and hit[0] == ver and hit[1].device == w.device:
+        if hit is not None and hit[0] == ver:
             return hit[1]
         n_out, k = w.shape
         L = _lib.lib()
@@ -129,15 +151,34 @@ class GraphAttentionNetwork(nn.Module):
         self._packed[key] = (ver, buf)
         return buf
 
+    def _bn_affine(self, bn):
+        """Eval-mode BatchNorm1d (nn/ops.py:46-47) as a per-channel affine; cached per version of its four tensors."""
+        key = ("bn", id(bn))
+        ver = tuple(self._stamp(t) for t in (bn.weight, bn.bias, bn.running_mean, bn.running_var))
+        hit = self._packed.get(key)
+        if hit is not None and hit[0] == ver:
+            return hit[1]
+        g = (bn.weight.detach() * torch.rsqrt(bn.running_var + bn.eps)).contiguous()
+        b = (bn.bias.detach() - bn.running_mean * g).contiguous()
+        self._packed[key] = (ver, (g, b))
+        return g, b
+
     def _linear(self, x, lin, epi, out_ch, residual=None, norm=None):
         L = _lib.lib()
         B, n, k = x.shape
         y = torch.empty(B, n, out_ch, dtype=torch.float32, device=x.device)
-        nrm = norm.normalizer if norm is not None else None
+        g = b = None
+        eps = 0.0
+        if norm is not None:
+            nrm = norm.normalizer
+            if isinstance(nrm, nn.BatchNorm1d):
+                epi = _lib.ENC_EPI_RES_AFFINE
+                g, b = self._bn_affine(nrm)
+            else:
+                g, b, eps = nrm.weight.detach(), nrm.bias.detach(), nrm.eps
         _lib.check(L.rl4co_enc_linear(
             _lib.ptr(x), _lib.ptr(self._pack(lin.weight)), _lib.ptr(lin.bias.detach()),
-            _lib.ptr(residual), _lib.ptr(nrm.weight.detach() if nrm is not None else None),
-            _lib.ptr(nrm.bias.detach() if nrm is not None else None), C.c_float(nrm.eps if nrm is not None else 0.0),
+            _lib.ptr(residual), _lib.ptr(g), _lib.ptr(b), C.c_float(eps),
             _lib.ptr(y), C.c_int64(B), n, k, out_ch, epi, _lib.stream_ptr()), "rl4co_enc_linear")
         return y
 

@@ -9,6 +9,7 @@ step, reward, log-likelihood) is ONE persistent kernel launch (`rl4co_rollout`);
 reference exposes per step.
 """
 import ctypes as C
+import warnings
 from typing import Optional
 
 import torch
@@ -16,7 +17,7 @@ import torch.nn as nn
 
 from . import _lib
 from .decoder import AttentionModelDecoder
-from .decoding import calculate_entropy, get_decoding_strategy, get_log_likelihood
+from .decoding import calculate_entropy, fresh_noise_seed, get_decoding_strategy, get_log_likelihood
 from .encoder import AttentionModelEncoder
 from .envs import RL4COEnvBase, get_env
 from .tensordict_lite import unbatchify
@@ -25,6 +26,8 @@ _MODES = {"greedy": _lib.MODE_GREEDY, "sampling": _lib.MODE_SAMPLING, "evaluate"
 
 
 class AttentionModelPolicy(nn.Module):
+    _warned = False
+
     def __init__(self, encoder: nn.Module = None, decoder: nn.Module = None, embed_dim: int = 128,
                  num_encoder_layers: int = 3, num_heads: int = 8, normalization: str = "batch",
                  feedforward_hidden: int = 512, env_name: str = "tsp", use_graph_context: bool = True,
@@ -48,8 +51,27 @@ class AttentionModelPolicy(nn.Module):
     def forward(self, td, env=None, phase: str = "train", calc_reward: bool = True,
                 return_actions: bool = True, return_entropy: bool = False, return_hidden: bool = False,
                 return_init_embeds: bool = False, return_sum_log_likelihood: bool = True, actions=None,
-                max_steps=1_000_000, fused: bool = True, check: bool = True, **decoding_kwargs) -> dict:
-        hidden, init_embeds = self.encoder(td)                                   # base.py:195
+                max_steps=1_000_000, fused: bool = True, check: bool = True, hidden=None,
+                **decoding_kwargs) -> dict:
+        """`hidden=` (extension): a precomputed encoder output `h [B, N', E]`; the encoder is skipped (the training
+        step encodes once, rolls out on `h.detach()` and differentiates the re-evaluation through the same `h`)."""
+        use_fused = fused and decoding_kwargs.get("select_start_nodes_fn") is None
+        if use_fused:
+            # The fused rollout is a no-grad kernel: its log_likelihood is detached.  Differentiable log-likelihoods
+            # of the sampled actions come from train.evaluate_log_likelihood / train.pomo_train_step (INTEGRATION.md).
+            if torch.is_grad_enabled() and phase == "train" and actions is None and not AttentionModelPolicy._warned:
+                AttentionModelPolicy._warned = True
+                warnings.warn("policy(td, env, phase='train') on the fused kernel returns a DETACHED log_likelihood; "
+                              "use eam_rl4co_b200.train.pomo_train_step / evaluate_log_likelihood for gradients")
+            if hidden is not None:
+                hidden, init_embeds = hidden.detach(), None
+            else:
+                with torch.no_grad():
+                    hidden, init_embeds = self.encoder(td)                       # base.py:195
+        elif hidden is not None:
+            init_embeds = None
+        else:
+            hidden, init_embeds = self.encoder(td)                               # base.py:195
         if isinstance(env, str) or env is None:
             env = get_env(self.env_name if env is None else env)
         decode_type = decoding_kwargs.pop("decode_type", None)                   # base.py:204-208
@@ -63,7 +85,7 @@ class AttentionModelPolicy(nn.Module):
             mask_logits=decoding_kwargs.pop("mask_logits", self.mask_logits),
             store_all_logp=decoding_kwargs.pop("store_all_logp", return_entropy),
             **decoding_kwargs)
-        if fused and cfg.get("select_start_nodes_fn") is None:
+        if use_fused:
             out = self._forward_fused(td, env, hidden, decode_type, actions, max_steps, check, cfg)
         else:
             out = self._forward_steps(td, env, hidden, decode_type, actions, max_steps, cfg)
@@ -155,10 +177,17 @@ class AttentionModelPolicy(nn.Module):
         demand = td["demand"].contiguous() if env_id == _lib.ENV_CVRP else None
         cap = td["vehicle_capacity"].contiguous() if env_id == _lib.ENV_CVRP else None
         cs = cache.cstruct()
+        seed = cfg.get("noise_seed")
+        if seed is None:             # fresh counter noise per sampling call (decoding.fresh_noise_seed)
+            seed = fresh_noise_seed() if (base == "sampling" and noise is None) else 0
+        seed = int(seed) & 0xFFFFFFFF
+        self.last_noise_seed = seed
+        # forced first actions follow env.select_start_nodes: `% env.generator.num_loc` (ops.py:147-161)
+        start_mod = int(getattr(getattr(env, "generator", None), "num_loc", 0) or 0)
         args = _lib.RolloutArgs(
             env=env_id, mode=_MODES[base], num_starts=S, max_steps=T,
             tanh_clipping=float(cfg["tanh_clipping"]), temperature=float(cfg["temperature"]),
-            seed=int(cfg.get("noise_seed", 0)) & 0xFFFFFFFF, inst_offset=int(cfg.get("instance_offset", 0)),
+            seed=seed, inst_offset=int(cfg.get("instance_offset", 0)),
             locs=locs.data_ptr(), demand=demand.data_ptr() if demand is not None else None,
             vehicle_capacity=cap.data_ptr() if cap is not None else None,
             gumbel=noise.data_ptr() if noise is not None else None,
@@ -168,7 +197,7 @@ class AttentionModelPolicy(nn.Module):
             actions=acts.data_ptr(), logp=logp.data_ptr(),
             logp_all=logp_all.data_ptr() if store_all else None, reward=reward.data_ptr(),
             log_likelihood=ll.data_ptr(), lengths=lengths.data_ptr(), max_len=meta.data_ptr(),
-            err=meta.data_ptr() + 4, impl=int(cfg.get("impl", _lib.IMPL_AUTO)),
+            err=meta.data_ptr() + 4, impl=int(cfg.get("impl", _lib.IMPL_AUTO)), start_mod=start_mod,
             phase_cycles=cfg["_phase_cycles"].data_ptr() if cfg.get("_phase_cycles") is not None else None)
         events = cfg.get("_events")           # bench.py: CUDA events around the kernel alone
         if events is not None:

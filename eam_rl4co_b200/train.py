@@ -121,13 +121,15 @@ def batched_log_likelihood(decoder, h: torch.Tensor, states: Dict[str, torch.Ten
 
 
 def evaluate_log_likelihood(policy, td, env, actions: torch.Tensor, num_starts: int,
-                            states: Optional[Dict[str, torch.Tensor]] = None) -> torch.Tensor:
+                            states: Optional[Dict[str, torch.Tensor]] = None,
+                            hidden: Optional[torch.Tensor] = None) -> torch.Tensor:
     """log-likelihood [S*B] (start-major, like `policy(...)["log_likelihood"]`) of given multistart `actions`,
-    with the autograd graph to every policy parameter (encoder included: the PyTorch modules run here)."""
+    with the autograd graph to every policy parameter (encoder included: the PyTorch modules run here, or the
+    caller's `hidden` with its graph)."""
     if states is None:
         states = teacher_forced_states(env, td, actions, num_starts)
     with torch.enable_grad():
-        h, _ = policy.encoder(td)
+        h = hidden if hidden is not None else policy.encoder(td)[0]
         logp = batched_log_likelihood(policy.decoder, h, states, policy.tanh_clipping, policy.temperature)
     return logp.sum(-1).transpose(0, 1).reshape(-1)
 
@@ -140,16 +142,22 @@ def reinforce_loss(reward: torch.Tensor, log_likelihood: torch.Tensor, num_start
     return -(adv * ll).mean(), adv
 
 
-def pomo_train_step(policy, env, td, optimizer=None, num_starts: Optional[int] = None, noise_seed: int = 0,
+def pomo_train_step(policy, env, td, optimizer=None, num_starts: Optional[int] = None, noise_seed: Optional[int] = None,
                     instance_offset: int = 0, max_grad_norm: Optional[float] = 1.0, group=None) -> Dict[str, float]:
     """One POMO training step on this rank's shard `td`: sampled multistart rollout (fused kernel), differentiable
-    re-evaluation, shared-baseline REINFORCE loss, backward, one all-reduce, clip, optimiser step."""
+    re-evaluation, shared-baseline REINFORCE loss, backward, one all-reduce, clip, optimiser step.
+    `noise_seed=None` draws a fresh seed per step from torch's global generator (decoding.fresh_noise_seed); ranks
+    seeded alike draw alike and the noise is keyed by `instance_offset + b`, so shards never share noise."""
     kw = {} if num_starts is None else {"num_starts": num_starts}
+    # ONE encoder pass per step, as in the reference's single differentiable forward (train-mode BatchNorm statistics
+    # are updated once, and the rollout samples from exactly the embeddings the loss differentiates)
+    with torch.enable_grad():
+        h, _ = policy.encoder(td)
     with torch.no_grad():
         out = policy(td, env, decode_type="multistart_sampling", noise_seed=noise_seed,
-                     instance_offset=instance_offset, **kw)
+                     instance_offset=instance_offset, hidden=h, **kw)
     S = out["actions"].shape[0] // td.batch_size[0]
-    ll = evaluate_log_likelihood(policy, td, env, out["actions"], S)
+    ll = evaluate_log_likelihood(policy, td, env, out["actions"], S, hidden=h)
     loss, _ = reinforce_loss(out["reward"], ll, S)
     params = [p for p in policy.parameters() if p.requires_grad]
     for p in params:

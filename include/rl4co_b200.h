@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define RL4CO_B200_ABI_VERSION 2
+#define RL4CO_B200_ABI_VERSION 3
 
 /* return codes */
 #define RL4CO_OK 0
@@ -179,6 +179,9 @@ typedef struct rl4co_rollout_args {
     int32_t* max_len;          /* out device int32: max over rows of lengths (pre-zeroed)   */
     int32_t* err;              /* device int32[2] (pre-zeroed)                              */
     int32_t impl;              /* RL4CO_IMPL_AUTO / _FP32 (CUDA cores) / _TC (tcgen05, needs tc_img) */
+    int32_t start_mod;         /* multistart: forced first action = start % start_mod (+1 for CVRP), the
+                                  reference's `% env.generator.num_loc` (ops.py:147-161); 0 = number of
+                                  customers of the instance (n_nodes for TSP, n_nodes-1 for CVRP)       */
     long long* phase_cycles;   /* nullable debug out, device int64[16]: clock64 cycles CTA 0 spent per phase
                                   of the tensor-path kernel (accumulated; caller zeroes)               */
 } rl4co_rollout_args;
@@ -208,6 +211,9 @@ int rl4co_tc_decode_step(int32_t env, const rl4co_cache* cache, const int64_t* f
 #define RL4CO_ENC_EPI_PLAIN 0    /* Y = X W^T + bias                                                   */
 #define RL4CO_ENC_EPI_RELU 1     /* Y = relu(X W^T + bias)                                             */
 #define RL4CO_ENC_EPI_RES_NORM 2 /* Y = InstanceNorm(residual + X W^T + bias) * gamma + beta, n_out=128 */
+#define RL4CO_ENC_EPI_RES_AFFINE 3 /* Y = (residual + X W^T + bias) * gamma + beta, n_out=128: eval-mode BatchNorm1d
+                                      (nn/ops.py:46-47) with gamma = w / sqrt(running_var + eps),
+                                      beta = b - running_mean * gamma folded by the caller                       */
 int64_t rl4co_enc_packed_bytes(int32_t n_out, int32_t k); /* 0 = unsupported (both must be multiples of 128) */
 /* nn.Linear weight W [n_out, k] -> fp16 hi/lo MMA tiles (once per forward / weight version) */
 int rl4co_enc_pack_weight(const float* W, int32_t n_out, int32_t k, void* packed, void* stream);

@@ -33,7 +33,7 @@ def test_struct_layouts_match_header():
     assert C.sizeof(_lib.Cache) == 8 * 8 + 8 + 16
     assert _lib.RolloutArgs.seed.offset == 24 and _lib.RolloutArgs.inst_offset.offset == 32
     assert C.sizeof(_lib.RolloutArgs) == 176 and _lib.RolloutArgs.err.offset == 152
-    assert _lib.RolloutArgs.impl.offset == 160
+    assert _lib.RolloutArgs.impl.offset == 160 and _lib.RolloutArgs.start_mod.offset == 164
 
 
 def test_argument_errors_return_codes_without_launching():

@@ -182,3 +182,33 @@ def test_large_shape_properties_tsp100_pomo():
     assert rel_close(ev["log_likelihood"], out["log_likelihood"], 1e-6)
     best = P.unbatchify(out["reward"], N).max(-1)[0]
     assert bool((best <= 0).all()) and bool((best > -30).all())
+
+
+@pytest.mark.parametrize("env_name", ["tsp", "cvrp"])
+def test_start_nodes_follow_generator_num_loc(env_name):
+    """forced first actions are `arange(S) % env.generator.num_loc` (+1 for CVRP) as in
+    select_start_nodes (ops.py:147-161), also when the env object was built for another size (policy(td, env=None)
+    builds the default num_loc=20 env): fused and step-granular paths agree."""
+    N, B = 50, 4
+    inst, pol, w, env, td, h = _setup(env_name, True, N, B, seed=8)
+    env20 = P.get_env(env_name, generator_params=dict(num_loc=20), device=DEV)
+    a = pol(td.clone(), env20, decode_type="multistart_greedy", num_starts=N)
+    assert torch.equal(a["actions"][:, 0], env20.select_start_nodes(td, N))
+    b = pol(td.clone(), env20, decode_type="multistart_greedy", num_starts=N, fused=False)
+    assert torch.equal(a["actions"][:, 0], b["actions"][:, 0])
+    same = (a["actions"] == b["actions"][:, :a["actions"].shape[1]]).all(1).float().mean().item()
+    assert same >= 0.99
+
+
+def test_sampling_draws_fresh_noise_by_default():
+    """without noise_seed every sampling call draws a fresh seed from torch's generator (the reference
+    draws fresh multinomial samples per call); torch.manual_seed makes it reproducible."""
+    N, B = 20, 16
+    inst, pol, w, env, td, h = _setup("tsp", False, N, B, seed=9)
+    torch.manual_seed(5)
+    a = pol(td.clone(), env, decode_type="sampling")
+    b = pol(td.clone(), env, decode_type="sampling")
+    torch.manual_seed(5)
+    c = pol(td.clone(), env, decode_type="sampling")
+    assert not torch.equal(a["actions"], b["actions"])
+    assert torch.equal(a["actions"], c["actions"])

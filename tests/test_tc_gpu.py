@@ -201,3 +201,35 @@ def test_tc_full_size_properties_cvrp(decode_type):
     ev = pol(td.clone(), env, actions=a, num_starts=N, impl=_lib.IMPL_FP32)
     assert rel_close(ev["log_likelihood"], out["log_likelihood"], LL_RTOL)
     assert rel_close(ev["reward"], out["reward"], 1e-6)
+
+
+@pytest.mark.parametrize("env_name", ["tsp", "cvrp"])
+@pytest.mark.parametrize("temperature", [0.1, 2.0])
+def test_tc_rollout_temperature(env_name, temperature):
+    """the constant log-sum-exp reference clip/temperature underflows at low temperature (every term of
+    the sum flushes to zero); beyond clip/temperature = 40 the row maximum is exchanged instead.  Both decode modes
+    against the oracle at temperature != 1."""
+    import eam_rl4co_b200 as P
+    from helpers import compare_rollout, decoder_weights, inst_to_env_td
+    N, B = 20, 8
+    torch.manual_seed(77)
+    inst = O.generate_tsp(B, N) if env_name == "tsp" else O.generate_cvrp(B, N)
+    torch.manual_seed(4321)
+    pol = P.POMOPolicy(env_name, temperature=temperature).eval()
+    w = decoder_weights(pol)
+    pol = pol.to("cuda")
+    env, td = inst_to_env_td(P, env_name, inst, "cuda")
+    with torch.no_grad():
+        h, _ = pol.encoder(td)
+    for dt in ("multistart_greedy", "multistart_sampling"):
+        out = pol(td.clone(), env, decode_type=dt, noise_seed=11, impl=P._lib.IMPL_TC)
+        assert torch.isfinite(out["log_likelihood"]).all()
+        with torch.inference_mode():
+            ref = O.rollout(env_name, inst, h.cpu(), w, dt, use_graph_context=False, noise_seed=11,
+                            temperature=temperature)
+            ev = O.rollout(env_name, inst, h.cpu(), w, actions=out["actions"].cpu(), num_starts=N,
+                           use_graph_context=False, temperature=temperature)
+        assert rel_close(out["log_likelihood"], ev["log_likelihood"], 2e-5)
+        T = min(ref["actions"].shape[1], out["actions"].shape[1])
+        same = (ref["actions"][:, :T] == out["actions"].cpu()[:, :T]).all(1).float().mean().item()
+        assert same >= 0.9, (dt, temperature, same)
