@@ -124,3 +124,35 @@ def test_rollout_with_kernel_encoder_matches_torch_encoder():
     best_a = a["reward"].view(N, B).max(0)[0]
     best_b = b["reward"].view(N, B).max(0)[0]
     assert torch.allclose(best_a, best_b, rtol=2e-3)
+
+
+# ---- pinned to the REFERENCE encoder (tests/golden/enc_*.npz, oracle/make_golden.py encoder_fixtures) -----------
+from helpers import encoder_golden_files, load_encoder_golden  # noqa: E402
+
+
+@pytest.mark.parametrize("path", encoder_golden_files(), ids=lambda p: p.split("/")[-1])
+def test_encoder_kernels_match_reference_fixture(path):
+    """enc_* kernels (instance norm for POMO, the eval-BatchNorm affine epilogue for the AttentionModel) against
+    the h the unmodified reference produced; then the full policy on top against the reference's greedy tours."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    g = load_encoder_golden(path, P, DEV)
+    pol, env_name = g["policy"], g["env"]
+    env, td = inst_to_env_td(P, env_name, g["inst"], DEV)
+    with torch.no_grad():
+        assert pol.encoder.net.kernels_apply(pol.encoder.init_embedding(td)), "kernel encoder not taken"
+        h, _ = pol.encoder(td)
+    err = (h.cpu() - g["h"]).abs().max().item()
+    print(f"{g['name']}: max |h_kernels - h_reference| = {err:.2e} (|h| max {g['h'].abs().max().item():.2f})")
+    assert err < 5e-5, err
+    dt = "multistart_greedy" if g["pomo"] else "greedy"
+    out = pol(td.clone(), env, decode_type=dt)
+    ref_a = torch.from_numpy(g["z"][f"{dt}.actions"]).long()
+    T = max(ref_a.shape[1], out["actions"].shape[1])
+    pad = lambda a: F.pad(a, (0, T - a.shape[1]))
+    same = (pad(out["actions"].cpu()) == pad(ref_a)).all(1)
+    print(f"   identical greedy tours end to end: {same.float().mean().item():.4f}")
+    assert same.float().mean().item() >= 0.9
+    r_ref = torch.from_numpy(g["z"][f"{dt}.reward"])
+    ll_ref = torch.from_numpy(g["z"][f"{dt}.log_likelihood"])
+    assert torch.allclose(out["reward"].cpu()[same], r_ref[same], rtol=1e-5, atol=1e-5)
+    assert torch.allclose(out["log_likelihood"].cpu()[same], ll_ref[same], rtol=1e-4, atol=1e-4)

@@ -36,11 +36,13 @@ def _setup(env_name, pomo, N, B, seed=0):
 
 
 @pytest.mark.parametrize("env_name", ["tsp", "cvrp"])
-@pytest.mark.parametrize("pomo,N,B", [(False, 20, 64), (False, 50, 32), (True, 20, 16), (True, 100, 4)])
+@pytest.mark.parametrize("pomo,N,B", [(False, 20, 64), (False, 50, 32), (False, 100, 24), (True, 20, 16),
+                                      (True, 100, 4)])
 @pytest.mark.parametrize("decode_type", DECODE_TYPES)
 def test_fused_rollout_matches_oracle(env_name, pomo, N, B, decode_type):
-    if N >= 100 and not decode_type.startswith("multistart"):
-        pytest.skip("covered by the AM cases")
+    if N >= 100 and pomo != decode_type.startswith("multistart"):
+        pytest.skip("N = 100: the POMO case takes the multistart types, the AttentionModel case (config c3's "
+                    "own shape, N' = 101 on rollout_global_kernel) the single-start ones")
     inst, pol, w, env, td, h = _setup(env_name, pomo, N, B)
     out = pol(td.clone(), env, decode_type=decode_type, noise_seed=2026, instance_offset=3)
     stats = compare_rollout(env_name, inst, h, w, not pomo, out, decode_type, noise_seed=2026,
@@ -155,7 +157,7 @@ def test_fused_rollout_vs_reference_fixtures(path):
         T = max(out["actions"].shape[1], ref_actions.shape[1])
         pad = lambda a: torch.nn.functional.pad(a, (0, T - a.shape[1]))
         same = (pad(out["actions"].cpu()) == pad(ref_actions)).all(1)
-        assert same.float().mean() >= 0.95, (dt, same.float().mean())
+        assert same.float().mean() >= 0.98, (dt, same.float().mean())
         assert rel_close(out["reward"].cpu()[same], torch.from_numpy(z[f"{dt}.reward"])[same], LL_RTOL)
         assert rel_close(out["log_likelihood"].cpu()[same],
                          torch.from_numpy(z[f"{dt}.log_likelihood"])[same], LL_RTOL)
@@ -164,6 +166,40 @@ def test_fused_rollout_vs_reference_fixtures(path):
         ev = pol(td.clone(), env, actions=ref_actions.to(DEV), **kw)
         assert rel_close(ev["log_likelihood"].cpu(), torch.from_numpy(z[f"{dt}.eval_log_likelihood"]), LL_RTOL)
         assert rel_close(ev["reward"].cpu(), torch.from_numpy(z[f"{dt}.reward"]), LL_RTOL)
+
+
+# BASELINE.json batch sizes, compared with the ORACLE (not with another kernel): the full batch runs on the GPU, a
+# contiguous slice of instances is rolled out by the oracle (counter noise is keyed by the global instance index,
+# so `instance_offset = lo` reproduces the slice's noise) and compared tie-aware + teacher-forced.
+@pytest.mark.parametrize("cfg", ["c1", "c2", "c3", "c4", "c5"])
+def test_baseline_batch_sizes_against_oracle_sample(cfg):
+    env_name, pomo, N, B, dt, lo, nsamp = {
+        "c1": ("tsp", False, 20, 512, "greedy", 200, 64),
+        "c2": ("tsp", False, 50, 4096, "sampling", 3000, 64),
+        "c3": ("cvrp", False, 100, 8192, "greedy", 5000, 48),
+        "c4": ("tsp", True, 100, 1024, "multistart_greedy", 700, 6),
+        "c5": ("cvrp", True, 100, 64, "multistart_sampling", 40, 4),
+    }[cfg]
+    inst, pol, w, env, td, h = _setup(env_name, pomo, N, B, seed=11)
+    out = pol(td.clone(), env, decode_type=dt, noise_seed=2026)
+    S = N if dt.startswith("multistart") else 1
+    rows = (torch.arange(S)[:, None] * B + torch.arange(lo, lo + nsamp)[None, :]).reshape(-1)   # start-major
+    sub = {k: out[k][rows.to(DEV)].cpu() for k in ("actions", "reward", "log_likelihood")}
+    inst_s = {k: v[lo:lo + nsamp] for k, v in inst.items()}
+    stats = compare_rollout(env_name, inst_s, h[lo:lo + nsamp], w, not pomo, sub, dt, noise_seed=2026,
+                            instance_offset=lo, min_exact=0.98)
+    print(f"{cfg}: B={B} sample [{lo},{lo + nsamp}) exact rows {stats['exact']:.4f} worst admitted gap "
+          f"{stats['worst_gap']:.2e}")
+    # whole batch: size-independent validity (every customer exactly once; CVRP capacity via the reward kernel)
+    a = out["actions"]
+    if env_name == "tsp":
+        assert bool((a.sort(1)[0] == torch.arange(N, device=DEV)[None]).all())
+    else:
+        cust = a.clamp_min(0)
+        cnt = torch.zeros(a.shape[0], N + 1, device=DEV).scatter_add_(1, cust, torch.ones_like(cust, dtype=torch.float))
+        assert bool((cnt[:, 1:] == 1).all())
+    r2 = env.get_reward(td, a, check_solution=True)       # validity + capacity checks of the reward kernel
+    assert rel_close(out["reward"], r2, 1e-6)
 
 
 def test_large_shape_properties_tsp100_pomo():
