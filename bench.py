@@ -2,18 +2,29 @@
 """bench.py — rollout instance-steps/s on the BASELINE.json headline workload.
 
 Workload (config c4 of BASELINE.json): TSP100, POMO policy (6 encoder layers, instance norm, no graph
-context), multistart greedy with S=100 starts per instance, B=1024 instances PER GPU (weak scaling:
-instances are independent, each rank rolls out its own shard, no data-path collective).
+context), multistart greedy with S=100 starts per instance, ONE batch of B=1024 instances SHARDED over the
+N GPUs (strong scaling: `sharding.shard_bounds`, the split Lightning DDP makes of a dataset batch,
+rl4co/utils/trainer.py:72-89,119; instances are independent, there is no data-path collective).
 One "step" = one full rollout of the batch = B*S rows x T=100 actions = 1.024e7 instance-steps.
 
   value : whole-job instance-steps/s, inputs (encoder output h, locs, weights) resident in HBM;
-          timed region = cache precompute GEMMs + operand pack kernel + the persistent tcgen05 rollout
+          timed region = cache precompute + operand pack kernel + the persistent tcgen05 rollout
           kernel, per step.
   e2e   : the same metric through the public API `policy(td, env, decode_type=...)` with HOST buffers:
           pinned host locs -> H2D -> env.reset -> encoder -> rollout -> D2H of reward / log_likelihood /
-          actions, every step.
+          actions / the sticky error word, every step; the error word of every step is checked inside the
+          timed region.
   roofline : the rollout kernel alone (CUDA events around its launch on the launching stream) against
           SURVEY.md §8(d)'s algorithmic bytes per instance-step and MEASURED_PEAKS.json's HBM figure.
+  weak  : (N > 1) the round-1 weak-scaling number, B=1024 instances PER GPU, device-resident.
+  gpu_eager_baseline : (N = 1) the reference's eager PyTorch path on the same B200 (oracle port of the
+          unmodified reference with CUDA tensors, reduced batch) — what a user of
+          rl4co/tasks/eval.py gets today.
+  configs : (N = 1) rollout kernel time / instance-steps/s / algorithmic-byte fraction of the other
+          BASELINE.json configs (c1, c2, c3, c5), device-resident.
+  train : config c5 — CVRP100 POMO REINFORCE step (sampled rollout, differentiable re-evaluation, shared
+          baseline, backward, ONE flat NCCL all-reduce of gradients + logged means, clip, Adam) at
+          64 instances per GPU, at every N.
   --impl reference : the reference's CPU implementation of the path (oracle port of the unmodified
           reference, bit-identical to it on CPU — see oracle/), all host threads, bounded sample.
 """
@@ -33,11 +44,12 @@ import torch  # noqa: E402
 
 N_NODES = 100
 NUM_STARTS = 100
-B_PER_GPU = 1024
+B_GLOBAL = 1024
 ALGO_BYTES_PER_INSTANCE_STEP = 2302
+ALGO_BYTES = {"c1": 31838, "c2": 77978, "c3": 156494, "c4": 2302, "c5": 2513}
 METRIC = "rollout_instance_steps_per_sec"
 UNIT = "instance-steps/s"
-WORKLOAD = "TSP100 POMO multistart greedy, S=100, B=1024 per GPU, random-init weights"
+WORKLOAD = "TSP100 POMO multistart greedy, S=100, one batch of 1024 instances sharded over the GPUs, random-init weights"
 
 
 def parse():
@@ -46,17 +58,20 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=B_PER_GPU, help="instances per GPU")
+    ap.add_argument("--batch", type=int, default=B_GLOBAL, help="instances in the (global) batch")
     ap.add_argument("--cpu-sample", type=int, default=128, help="instances in the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the weak / gpu_eager_baseline / configs / train sub-records (profiling runs)")
     return ap.parse_args()
 
 
 def measured_traffic():
     """DRAM bytes per launch of the rollout kernel from the committed `ncu --set full` capture."""
-    p = os.path.join(ROOT, "profiles", "r01_rollout_tc_traffic.json")
-    if os.path.exists(p):
-        return json.load(open(p)).get("dram_bytes_per_launch")
+    for name in ("r02_rollout_tc_traffic.json", "r01_rollout_tc_traffic.json"):
+        p = os.path.join(ROOT, "profiles", name)
+        if os.path.exists(p):
+            return json.load(open(p)).get("dram_bytes_per_launch")
     return None
 
 
@@ -100,10 +115,10 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def make_instances(B, seed=1234):
+def make_instances(B, seed=1234, n=N_NODES):
     from eam_rl4co_b200 import TSPGenerator
     torch.manual_seed(seed)
-    return TSPGenerator(num_loc=N_NODES)(B)["locs"]            # host, [B, 100, 2]
+    return TSPGenerator(num_loc=n)(B)["locs"]            # host, [B, n, 2]
 
 
 def make_policy():
@@ -113,31 +128,40 @@ def make_policy():
 
 
 # ---------------------------------------------------------------------------------------------
-# CPU leg: the reference's implementation of the path (oracle port) on the host cores
+# Reference legs: the reference's implementation of the path (oracle port), on the host cores
+# and — as the eager baseline — on the same B200
 # ---------------------------------------------------------------------------------------------
-def cpu_reference_run(sample_B, steps, warmup):
+def reference_run(sample_B, steps, warmup, device="cpu"):
     """Times oracle.rollout (decode loop given h: cache precompute + T decoder/selection/env steps +
-    reward), all host threads, on `sample_B` instances of the same workload.  Returns dict."""
+    reward) on `sample_B` instances of the same workload.  device="cpu": all host threads;
+    device="cuda": the same eager PyTorch ops on the GPU."""
     from oracle import rollout_oracle as O
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     pol = make_policy()
-    w = {k: v.detach().clone() for k, v in pol.decoder.state_dict().items()}
+    w = {k: v.detach().clone().to(device) for k, v in pol.decoder.state_dict().items()}
     locs = make_instances(sample_B)
     with torch.inference_mode():
         h, _ = pol.encoder({"locs": locs})
+        h, locs = h.to(device), locs.to(device)
         times = []
         for it in range(warmup + steps):
+            if device != "cpu":
+                torch.cuda.synchronize()
             t0 = time.perf_counter()
             out = O.rollout("tsp", {"locs": locs}, h, w, "multistart_greedy", use_graph_context=False)
+            if device != "cpu":
+                torch.cuda.synchronize()
             dt = time.perf_counter() - t0
             if it >= warmup:
                 times.append(dt)
     isteps = out["actions"].numel()
     total = sum(times)
-    return {"value": isteps * len(times) / total, "unit": UNIT, "cores": cores, "kind": "port",
+    where = f"torch CPU, {cores} threads" if device == "cpu" else "eager torch CUDA ops on the same B200"
+    return {"value": isteps * len(times) / total, "unit": UNIT, "cores": cores if device == "cpu" else 0,
+            "kind": "port",
             "sample": f"{sample_B} instances x {NUM_STARTS} starts x {N_NODES} steps per rollout, "
-                      f"{len(times)} rollouts, oracle port of the reference (torch CPU, {cores} threads)",
+                      f"{len(times)} rollouts, oracle port of the reference ({where})",
             "ms_per_step": 1e3 * total / len(times), "instance_steps_per_step": isteps}
 
 
@@ -146,14 +170,16 @@ def run_reference(args):
     if rank != 0:
         return
     # bounded sample: 128 instances per rollout is the CPU path's best operating point on these hosts (3.2e6
-    # instance-steps/s; 1.4e6 at 16 instances, 2.0e6 at 512), ~0.4 s per rollout
+    # instance-steps/s; 1.4e6 at 16 instances, 2.0e6 at 512), ~0.4 s per rollout.  The metric is per
+    # instance-step, so the sample size is a normalisation, not a different workload.
     steps = max(1, min(args.steps, 50))
-    warm = max(1, min(args.warmup, 2))
-    r = cpu_reference_run(args.cpu_sample, steps, warm)
+    warm = max(0, min(args.warmup, 10))
+    r = reference_run(args.cpu_sample, steps, warm)
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": steps, "warmup": warm, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sample": r["sample"]},
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "sample": r["sample"],
+                       "same_metric_basis": "per instance-step (value = instance-steps of the sample / its time)"},
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -161,11 +187,111 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------------------------
-# B200 leg
+# B200 legs
 # ---------------------------------------------------------------------------------------------
+def _time_steps(fn, K, W, barrier):
+    for _ in range(W):
+        fn()
+    barrier()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(K):
+        fn()
+    t1.record()
+    barrier()
+    return t0.elapsed_time(t1)
+
+
+def other_configs(dev):
+    """Device-resident rollout of the other BASELINE.json configs on one GPU (kernel time by CUDA events)."""
+    import eam_rl4co_b200 as P
+    res = {}
+    specs = {"c1": ("tsp", False, 20, 512, "greedy"), "c2": ("tsp", False, 50, 4096, "sampling"),
+             "c3": ("cvrp", False, 100, 8192, "greedy"), "c5": ("cvrp", True, 100, 64, "multistart_sampling")}
+    peak, _ = peaks()
+    for name, (env_name, pomo, N, B, dt) in specs.items():
+        torch.manual_seed(1234)
+        gen = (P.TSPGenerator if env_name == "tsp" else P.CVRPGenerator)(num_loc=N)
+        inst = gen(B)
+        torch.manual_seed(4321)
+        pol = (P.POMOPolicy(env_name) if pomo else P.AttentionModelPolicy(env_name=env_name)).eval().to(dev)
+        env = P.get_env(env_name, generator_params=dict(num_loc=N), device=dev)
+        td = env.reset(P.TensorDict({k: v.to(dev) for k, v in inst.items()}, batch_size=[B]))
+        with torch.no_grad():
+            h, _ = pol.encoder(td)
+        events = []
+        cfg = dict(temperature=1.0, tanh_clipping=10.0, mask_logits=True, store_all_logp=False, _events=events)
+        out = None
+        for it in range(3 + 10):
+            cfg["noise_seed"] = it
+            out = pol._forward_fused(td, env, h, dt, None, 10**6, False, cfg)
+        torch.cuda.synchronize()
+        k_ms = statistics.median(a.elapsed_time(b) for a, b in events[3:])
+        isteps = out[1].numel()                    # rows x T (CVRP: T = batch-max length, SURVEY.md §8d)
+        rate = isteps / (k_ms * 1e-3)
+        res[name] = {"workload": f"{env_name.upper()}{N} {'POMO' if pomo else 'AttentionModel'} {dt}, B={B}",
+                     "kernel_ms": k_ms, "instance_steps": isteps, "value": rate, "unit": UNIT,
+                     "algorithmic_bytes_per_instance_step": ALGO_BYTES[name],
+                     "frac_of_hbm_algorithmic": rate * ALGO_BYTES[name] / 1e9 / peak}
+        del pol, td, h, out
+    return res
+
+
+def train_leg(dev, rank, world, steps=8, warmup=3):
+    """Config c5: CVRP100 POMO REINFORCE step, 64 instances x 100 starts per GPU, ONE flat all-reduce."""
+    import torch.distributed as dist
+    import eam_rl4co_b200 as P
+    from eam_rl4co_b200 import sharding, train
+    N, B = 100, 64
+    torch.manual_seed(4321)
+    pol = P.POMOPolicy("cvrp").to(dev).train()
+    opt = torch.optim.Adam(pol.parameters(), lr=1e-4)
+    env = P.get_env("cvrp", generator_params=dict(num_loc=N), device=dev)
+    gen = P.DeviceGenerator("cvrp", num_loc=N, seed=7, device=dev)
+    stats = None
+    # all-reduce alone, same flat buffer size (gradients + 3 logged scalars)
+    n_par = sum(p.numel() for p in pol.parameters() if p.requires_grad)
+    times = []
+    for it in range(warmup + steps):
+        td = env.reset(gen(B, instance_offset=(it * world + rank) * B))
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = torch.cuda.Event(enable_timing=True)
+        t1 = torch.cuda.Event(enable_timing=True)
+        t0.record()
+        stats = train.pomo_train_step(pol, env, td, opt, noise_seed=it, instance_offset=(it * world + rank) * B)
+        t1.record()
+        torch.cuda.synchronize()
+        if it >= warmup:
+            times.append(t0.elapsed_time(t1))
+    ar_ms = None
+    if world > 1:
+        buf = torch.zeros(n_par + 3, dtype=torch.float32, device=dev)
+        for _ in range(3):
+            dist.all_reduce(buf)
+        torch.cuda.synchronize()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(10):
+            dist.all_reduce(buf)
+        a1.record()
+        torch.cuda.synchronize()
+        ar_ms = a0.elapsed_time(a1) / 10
+    step_ms = statistics.median(times)
+    step_ms, = sharding.max_over_ranks([step_ms], device=dev)
+    return {"workload": "CVRP100 POMO REINFORCE step (multistart sampling S=100, shared baseline, backward, "
+                        "flat all-reduce, clip, Adam), 64 instances per GPU",
+            "ms_per_step": step_ms, "instances_per_s": world * B / (step_ms * 1e-3), "n_gpus": world,
+            "allreduce_ms": ar_ms, "allreduce_bytes": 4 * (n_par + 3), "collectives_per_step": 1 if world > 1 else 0,
+            "backend": "nccl" if world > 1 else None, "loss": stats["loss"], "reward": stats["reward"],
+            "ll_gap_rollout_vs_reevaluation": stats["ll_gap"]}
+
+
 def run_b200(args):
     import torch.distributed as dist
     import eam_rl4co_b200 as P
+    from eam_rl4co_b200 import _lib, sharding
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -180,111 +306,152 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
     torch.backends.cuda.matmul.allow_tf32 = False
     torch.backends.cudnn.allow_tf32 = False
-    B, K, W = args.batch, args.steps, max(args.warmup, 3)
+    K, W = args.steps, max(args.warmup, 3)
+    BG = args.batch
+    lo, hi = sharding.shard_bounds(BG, rank, world)          # ONE batch, sharded (trainer.py:72-89,119)
+    B = hi - lo
 
     pol = make_policy().to(dev)
     env = P.TSPEnv(generator_params=dict(num_loc=N_NODES), device=dev)
-    # each rank owns its own shard of instances (global instance index = rank*B + b keys the noise)
-    locs_host = make_instances(B, seed=1234 + rank).pin_memory()
-    locs_dev = locs_host.to(dev)
-    td_dev = env.reset(P.TensorDict({"locs": locs_dev}, batch_size=[B]))
-    with torch.no_grad():
-        h, _ = pol.encoder(td_dev)
-    rows = B * NUM_STARTS
-    isteps = rows * N_NODES
-    events = []
-    cfg = dict(temperature=1.0, tanh_clipping=10.0, mask_logits=True, store_all_logp=False,
-               instance_offset=rank * B, _events=events)
-
-    def device_step():
-        # hot path with inputs resident in HBM: cache precompute + ONE persistent rollout kernel
-        return pol._forward_fused(td_dev, env, h, "multistart_greedy", None, 10**6, False, cfg)
+    locs_all = make_instances(BG, seed=1234)                  # the same global batch on every rank
+    locs_host = locs_all[lo:hi].contiguous().pin_memory()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(W):
-        device_step()
-    barrier()
-    events.clear()
+    def device_leg(locs_h, inst_offset):
+        """device-resident: cache precompute + pack + ONE persistent rollout kernel per step"""
+        Bl = locs_h.shape[0]
+        td_dev = env.reset(P.TensorDict({"locs": locs_h.to(dev)}, batch_size=[Bl]))
+        with torch.no_grad():
+            h, _ = pol.encoder(td_dev)
+        events = []
+        cfg = dict(temperature=1.0, tanh_clipping=10.0, mask_logits=True, store_all_logp=False,
+                   instance_offset=inst_offset, _events=events)
+        step = lambda: pol._forward_fused(td_dev, env, h, "multistart_greedy", None, 10**6, False, cfg)
+        for _ in range(W):
+            step()
+        barrier()
+        events.clear()
+        ms = _time_steps(step, K, 0, barrier)
+        _lib.raise_on_err(pol.last_status[1:])                # the sticky error word of the last rollout
+        return ms, [a.elapsed_time(b) for a, b in events]
+
     # one sampler per job (rank 0's GPU): eight nvidia-smi pollers on one host contend with the CUDA driver for the
     # same locks and show up in the end-to-end leg
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    t0.record()
-    for _ in range(K):
-        device_step()
-    t1.record()
-    barrier()
-    ms_total = t0.elapsed_time(t1)
-    kernel_ms = [a.elapsed_time(b) for a, b in events]
+    ms_total, kernel_ms = device_leg(locs_host, lo)
+    rows = B * NUM_STARTS
+    isteps_local = rows * N_NODES
+    isteps_global = BG * NUM_STARTS * N_NODES
 
     # ---- e2e: public API, host buffers, H2D + D2H inside the timed region --------------------
     out_host = {"reward": torch.empty(rows, dtype=torch.float32).pin_memory(),
                 "log_likelihood": torch.empty(rows, dtype=torch.float32).pin_memory(),
                 "actions": torch.empty(rows, N_NODES, dtype=torch.int64).pin_memory()}
+    status_host = torch.zeros(2, 3, dtype=torch.int32).pin_memory()
     h2d = locs_host.numel() * 4
-    d2h = sum(v.numel() * v.element_size() for v in out_host.values())
+    d2h = sum(v.numel() * v.element_size() for v in out_host.values()) + 12
 
     # result copies run on their own stream so that the D2H of step i overlaps the compute of step i+1; the timed
-    # region ends with a full device synchronize, so every copy is inside it
+    # region ends with a full device synchronize, so every copy is inside it.  The rollout's sticky error word
+    # (NaN logits / infeasible action / -inf log-probability / max steps / fp16 range) travels with the results and
+    # is checked on the host one step later, inside the timed region: the timed path is the checked path.
     copy_stream = torch.cuda.Stream(device=dev)
+    copied = [None, None]
+    n_e2e = [0]
+
+    def check_status(slot):
+        if copied[slot] is not None:
+            copied[slot].synchronize()
+            e = status_host[slot].tolist()
+            if e[1]:
+                _lib.raise_on_err(status_host[slot][1:])
 
     def e2e_step():
+        i = n_e2e[0]
+        n_e2e[0] += 1
         td = P.TensorDict({"locs": locs_host.to(dev, non_blocking=True)}, batch_size=[B])
         td = env.reset(td)
         with torch.no_grad():
-            out = pol(td, env, decode_type="multistart_greedy", check=False, instance_offset=rank * B)
+            out = pol(td, env, decode_type="multistart_greedy", check=False, instance_offset=lo)
+        status = pol.last_status
         copy_stream.wait_stream(torch.cuda.current_stream())
+        check_status(i & 1)                                   # step i-2's word, before its slot is reused
         with torch.cuda.stream(copy_stream):
             for k, v in out_host.items():
                 v.copy_(out[k], non_blocking=True)
                 out[k].record_stream(copy_stream)
+            status_host[i & 1].copy_(status, non_blocking=True)
+            status.record_stream(copy_stream)
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+            copied[i & 1] = ev
         return out
+
+    def e2e_finish():
+        torch.cuda.current_stream().wait_stream(copy_stream)
+        check_status(0)
+        check_status(1)
 
     for _ in range(W):
         e2e_step()
+    e2e_finish()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(K):
         e2e_step()
-    torch.cuda.current_stream().wait_stream(copy_stream)     # the last step's copies are part of the timed region
+    e2e_finish()                                              # the last steps' copies + checks are inside the region
     e1.record()
     barrier()
     e2e_ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None   # sampled over both timed regions (device-resident and end-to-end)
 
-    from eam_rl4co_b200 import sharding
     k_mean = statistics.mean(kernel_ms)
     ms_total, e2e_ms, k_mean = sharding.max_over_ranks([ms_total, e2e_ms, k_mean], device=dev)   # device-timed, MAX
+
+    weak = None
+    if world > 1 and not args.no_extras:
+        # round-1 number: every GPU rolls out its own 1024 instances (no collective either)
+        w_ms, _ = device_leg(make_instances(B_GLOBAL, seed=1234 + rank).pin_memory(), rank * B_GLOBAL)
+        w_ms, = sharding.max_over_ranks([w_ms], device=dev)
+        weak = {"scaling": "weak", "instances_per_gpu": B_GLOBAL, "ms_per_step": w_ms / K,
+                "value": world * B_GLOBAL * NUM_STARTS * N_NODES * K / (w_ms * 1e-3), "unit": UNIT}
+    train_rec = None
+    if not args.no_extras:
+        train_rec = train_leg(dev, rank, world)
+
     if rank == 0:
         peak, peak_src = peaks()
         k_ms = k_mean
-        achieved = ALGO_BYTES_PER_INSTANCE_STEP * isteps / (k_ms * 1e-3) / 1e9
+        achieved = ALGO_BYTES_PER_INSTANCE_STEP * isteps_local / (k_ms * 1e-3) / 1e9
         line = {
-            "metric": METRIC, "value": world * isteps * K / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
+            "metric": METRIC, "value": isteps_global * K / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": K, "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "instances_per_gpu": B, "num_starts": NUM_STARTS,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "global_batch": BG, "instances_per_gpu": B, "num_starts": NUM_STARTS,
                        "nodes": N_NODES, "decode_type": "multistart_greedy", "parallelism": f"dp{world}",
-                       "instance_steps_per_step_per_gpu": isteps,
-                       "l2": "inputs larger than L2 (tables 262 MB + outputs 123 MB per step)",
-                       "timed": "cache precompute GEMMs + operand pack + persistent tcgen05 rollout kernel"},
-            "e2e": {"value": world * isteps * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / K,
-                    "includes": "H2D locs, env.reset, encoder (tcgen05 kernels: 4 GEMMs + attention per layer), "
-                                "cache precompute, rollout kernel, D2H reward+log_likelihood+actions"},
+                       "partition": "one batch split contiguously over the ranks (sharding.shard_bounds), "
+                                    "no data-path collective",
+                       "instance_steps_per_step": isteps_global,
+                       "l2": "inputs larger than L2 at N=1 (tables 262 MB + outputs 123 MB per step); at N=8 the "
+                             "per-GPU shard (48 MB) fits L2 - the kernel reads it once per rollout either way",
+                       "timed": "cache precompute + operand pack + persistent tcgen05 rollout kernel"},
+            "e2e": {"value": isteps_global * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / K, "checked": True,
+                    "includes": "H2D locs, env.reset, encoder (tcgen05 kernels), cache precompute, rollout kernel, "
+                                "D2H reward+log_likelihood+actions+error word, host check of the error word"},
             "gpu_launches": 2 * len(kernel_ms),      # per step: r4::tc::tc_pack_kernel + r4::tc::rollout_tc_kernel
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": measured_traffic(), "peak_source": peak_src,
                          "kernel": "r4::tc::rollout_tc_kernel<TSP, GREEDY>", "kernel_ms": k_ms,
-                         "algorithmic_bytes_per_launch": ALGO_BYTES_PER_INSTANCE_STEP * isteps,
+                         "instances_per_launch": B,
+                         "algorithmic_bytes_per_launch": ALGO_BYTES_PER_INSTANCE_STEP * isteps_local,
                          "note": "algorithmic bytes per SURVEY.md §8(d) (K,V,L re-read every step); the "
                                  "kernel keeps the operand tiles in shared memory for the whole rollout, so "
                                  "DRAM traffic (`traffic`, ncu) is ~60x lower and the binding resources are "
@@ -292,8 +459,22 @@ def run_b200(args):
                                  "tcgen05 MMAs (DESIGN.md, profiles/)"},
             "clocks": clocks,
         }
+        if weak is not None:
+            line["weak"] = weak
+        if train_rec is not None:
+            line["train"] = train_rec
+        if world == 1 and not args.no_extras:
+            try:
+                line["configs"] = other_configs(dev)
+            except Exception as e:  # noqa: BLE001 - a sub-record must not take the headline line down
+                line["configs"] = {"error": repr(e)}
+            try:
+                g = reference_run(32, 3, 1, device=dev)           # ~100 eager steps x ~25 kernels each per rollout
+                line["gpu_eager_baseline"] = {k: g[k] for k in ("value", "unit", "kind", "sample", "ms_per_step")}
+            except Exception as e:  # noqa: BLE001
+                line["gpu_eager_baseline"] = {"error": repr(e)}
         if world == 1 and not args.no_cpu_baseline:
-            r = cpu_reference_run(args.cpu_sample, 30, 1)      # ~12 s of CPU work
+            r = reference_run(args.cpu_sample, 30, 1)      # ~12 s of CPU work
             line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
         print(json.dumps(line), flush=True)
     if world > 1:

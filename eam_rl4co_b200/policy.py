@@ -209,6 +209,7 @@ class AttentionModelPolicy(nn.Module):
             e1.record()
             events.append((e0, e1))
         self.last_lengths = lengths
+        self.last_status = meta              # device int32 [max_len, error bits, first offending row + 1]
         if env_id == _lib.ENV_CVRP or check:
             m = meta.tolist()                 # the ONE host sync of the rollout
             if check:
