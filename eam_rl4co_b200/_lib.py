@@ -9,9 +9,10 @@ import subprocess
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librl4co_b200.so")
+# RL4CO_B200_LIB: experiment builds of the same sources (profiles/variants.sh); the product path is the in-tree library
+LIB_PATH = os.environ.get("RL4CO_B200_LIB") or os.path.join(_HERE, "librl4co_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["capi.cu", "env_kernels.cu", "decode_kernels.cu", "rollout_kernel.cu", "rollout_tc.cu", "encoder_tc.cu", "reduce_kernels.cu", "data_kernels.cu"]
+SOURCES = ["capi.cu", "env_kernels.cu", "decode_kernels.cu", "rollout_kernel.cu", "rollout_coop.cu", "rollout_tc.cu", "encoder_tc.cu", "reduce_kernels.cu", "data_kernels.cu"]
 
 ENV_TSP, ENV_CVRP = 0, 1
 MODE_GREEDY, MODE_SAMPLING, MODE_EVALUATE = 0, 1, 2
@@ -24,7 +25,7 @@ ERR_MESSAGES = [  # (bit, reference assertion text); first match is raised
     (16, "Used more than capacity"),
     (32, "Exceeded maximum number of steps during decoding"),
 ]
-IMPL_AUTO, IMPL_FP32, IMPL_TC = 0, 1, 2
+IMPL_AUTO, IMPL_FP32, IMPL_TC, IMPL_STREAM, IMPL_COOP = 0, 1, 2, 3, 4
 ENC_EPI_PLAIN, ENC_EPI_RELU, ENC_EPI_RES_NORM, ENC_EPI_RES_AFFINE = 0, 1, 2, 3
 ABI_VERSION = 3
 

@@ -23,46 +23,70 @@ __device__ __forceinline__ float dot4(const float4& a, const float4& b) {
     return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
 }
 
-// Masked 8-head glimpse (attention.py:308-322: SDPA with attn_mask, scale 1/sqrt(16)),
-// online softmax over the feasible nodes only.  Returns this lane's 4 channels of `heads`.
+// Masked 8-head glimpse (attention.py:308-322: SDPA with attn_mask, scale 1/sqrt(16)) as an online softmax over the
+// feasible nodes only.  Four nodes per iteration: their eight 512-byte rows are requested before any of them is used
+// (one warp then keeps 4 KB in flight instead of 1 KB - the streaming kernels are bound by latency x bytes in flight,
+// measured 61-65 % of the HBM peak with one node per iteration), the four dot products and their two shuffle levels are
+// independent, and the running maximum is rescaled once per group.
+// glimpse_accum continues the state (m, l, acc) over the nodes of `sub` (bit i <=> node node0 + i); qs = q / sqrt(d).
+__device__ __forceinline__ void glimpse_accum(const float* __restrict__ gk, const float* __restrict__ gv, float4 qs,
+                                              uint32_t sub, int node0, int lane, float& m, float& l, float4& acc) {
+    const int off = 4 * lane;
+    while (sub) {
+        int j[4];
+        bool ok[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            ok[u] = sub != 0u;
+            j[u] = ok[u] ? (__ffs(sub) - 1) : 0;
+            sub &= sub - 1u;                      // 0 stays 0
+        }
+#pragma unroll
+        for (int u = 1; u < 4; ++u) j[u] = ok[u] ? j[u] : j[0];   // unused slots re-read slot 0's rows (cache hits)
+        float4 k4[4], v4[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            k4[u] = ld4(gk + (node0 + j[u]) * kE + off);
+            v4[u] = ld4(gv + (node0 + j[u]) * kE + off);
+        }
+        float s[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) s[u] = dot4(qs, k4[u]);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) s[u] += __shfl_xor_sync(kFull, s[u], 1);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) s[u] += __shfl_xor_sync(kFull, s[u], 2);   // the 4 lanes of a head hold its score
+#pragma unroll
+        for (int u = 1; u < 4; ++u) s[u] = ok[u] ? s[u] : -INFINITY;
+        const float mn = fmaxf(fmaxf(fmaxf(s[0], s[1]), fmaxf(s[2], s[3])), m);
+        const float c = expf(m - mn);             // first group: exp(-inf) = 0
+        float p[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) p[u] = expf(s[u] - mn);   // exp(-inf) = 0 for the unused slots
+        l = fmaf(l, c, (p[0] + p[1]) + (p[2] + p[3]));
+        acc.x = fmaf(acc.x, c, fmaf(p[0], v4[0].x, p[1] * v4[1].x) + fmaf(p[2], v4[2].x, p[3] * v4[3].x));
+        acc.y = fmaf(acc.y, c, fmaf(p[0], v4[0].y, p[1] * v4[1].y) + fmaf(p[2], v4[2].y, p[3] * v4[3].y));
+        acc.z = fmaf(acc.z, c, fmaf(p[0], v4[0].z, p[1] * v4[1].z) + fmaf(p[2], v4[2].z, p[3] * v4[3].z));
+        acc.w = fmaf(acc.w, c, fmaf(p[0], v4[0].w, p[1] * v4[1].w) + fmaf(p[2], v4[2].w, p[3] * v4[3].w));
+        m = mn;
+    }
+}
+
+// Returns this lane's 4 channels of `heads`.
 __device__ __forceinline__ float4 warp_glimpse(const InstPtrs& ip, float4 q4, const uint32_t (&maskw)[kNB],
                                                int lane) {
     const float4 qs = make_float4(q4.x * 0.25f, q4.y * 0.25f, q4.z * 0.25f, q4.w * 0.25f);
     float m = -INFINITY, l = 0.f;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    const int off = 4 * lane;
 #pragma unroll
-    for (int blk = 0; blk < kNB; ++blk) {
-        uint32_t w = maskw[blk];
-        while (w) {
-            const int node = blk * 32 + (__ffs(w) - 1);
-            w &= w - 1;
-            const float4 k4 = ld4(ip.gk + node * kE + off);
-            const float4 v4 = ld4(ip.gv + node * kE + off);
-            float s = dot4(qs, k4);
-            s += __shfl_xor_sync(kFull, s, 1);
-            s += __shfl_xor_sync(kFull, s, 2);  // all 4 lanes of a head hold the head's score
-            if (s > m) {
-                const float c = expf(m - s);    // m = -inf -> 0
-                l *= c;
-                acc.x *= c; acc.y *= c; acc.z *= c; acc.w *= c;
-                m = s;
-            }
-            const float p = expf(s - m);
-            l += p;
-            acc.x = fmaf(p, v4.x, acc.x);
-            acc.y = fmaf(p, v4.y, acc.y);
-            acc.z = fmaf(p, v4.z, acc.z);
-            acc.w = fmaf(p, v4.w, acc.w);
-        }
-    }
+    for (int blk = 0; blk < kNB; ++blk) glimpse_accum(ip.gk, ip.gv, qs, maskw[blk], blk * 32, lane, m, l, acc);
     const float inv = 1.0f / l;  // l == 0 (nothing feasible) -> inf * 0 = NaN, flagged by caller
     return make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
 }
 
 // logits[n] = heads . lk[n] / sqrt(E)   (attention.py:296-301 with project_out folded, :328).
 // Output in "lane owns nodes" form: lg[blk] is the logit of node 32*blk+lane.
-// Nodes outside `which` keep -inf.
+// Nodes outside `which` keep -inf.  Four nodes per iteration (four independent warp reductions).
 __device__ __forceinline__ void warp_logits(const InstPtrs& ip, float4 hd, const uint32_t (&which)[kNB],
                                             int lane, float (&lg)[kNB]) {
     const int off = 4 * lane;
@@ -71,11 +95,27 @@ __device__ __forceinline__ void warp_logits(const InstPtrs& ip, float4 hd, const
         lg[blk] = -INFINITY;
         uint32_t w = which[blk];
         while (w) {
-            const int j = __ffs(w) - 1;
-            w &= w - 1;
-            const float4 l4 = ld4(ip.lk + (blk * 32 + j) * kE + off);
-            float d = warp_sum(dot4(hd, l4));
-            if (lane == j) lg[blk] = d / 11.313708498984761f;  // / math.sqrt(128)
+            int j[4];
+            bool ok[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                ok[u] = w != 0u;
+                j[u] = ok[u] ? (__ffs(w) - 1) : 0;
+                w &= w - 1u;
+            }
+#pragma unroll
+            for (int u = 1; u < 4; ++u) j[u] = ok[u] ? j[u] : j[0];
+            float d[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) d[u] = dot4(hd, ld4(ip.lk + (blk * 32 + j[u]) * kE + off));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) d[u] += __shfl_xor_sync(kFull, d[u], o);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u] && lane == j[u]) lg[blk] = d[u] / 11.313708498984761f;  // / math.sqrt(128)
         }
     }
 }

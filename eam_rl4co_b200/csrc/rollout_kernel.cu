@@ -238,8 +238,11 @@ __global__ void __launch_bounds__(kRolloutWarps * 32, 1)
     }
 }
 
+#ifndef R4_GLOBAL_MINBLOCKS
+#define R4_GLOBAL_MINBLOCKS 4   // 32 warps per SM (64 registers): c2 fits one wave, c3 two equal ones; measured 1.39 / 10.1 ms against 1.50 / 11.6 ms at 3 CTAs per SM
+#endif
 template <int ENV>
-__global__ void __launch_bounds__(kGlobalWarps * 32)
+__global__ void __launch_bounds__(kGlobalWarps * 32, R4_GLOBAL_MINBLOCKS)
     rollout_global_kernel(rl4co_cache c, rl4co_rollout_args a) {
     const int lane = threadIdx.x & 31;
     const int S = a.num_starts > 1 ? a.num_starts : 1;
@@ -263,6 +266,8 @@ namespace r4 {
 int check_cache(const rl4co_cache* c, int env, const char* who);
 bool tc_supported(const rl4co_cache* c, int S);
 int launch_rollout_tc(const rl4co_cache* cache, const rl4co_rollout_args& a, cudaStream_t st);
+bool coop_supported(const rl4co_cache* c);
+int launch_rollout_coop(const rl4co_cache* cache, const rl4co_rollout_args& a, cudaStream_t st);
 }
 
 extern "C" int rl4co_rollout(const rl4co_cache* cache, const rl4co_rollout_args* args, void* stream) {
@@ -289,11 +294,19 @@ extern "C" int rl4co_rollout(const rl4co_cache* cache, const rl4co_rollout_args*
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     rl4co_rollout_args a = *args;
     a.num_starts = S;
-    R4_CHECK_ARG(a.impl >= RL4CO_IMPL_AUTO && a.impl <= RL4CO_IMPL_TC, "rollout: bad impl %d", a.impl);
+    R4_CHECK_ARG(a.impl >= RL4CO_IMPL_AUTO && a.impl <= RL4CO_IMPL_COOP, "rollout: bad impl %d", a.impl);
     if (a.impl == RL4CO_IMPL_TC)
         R4_CHECK_ARG(tc_supported(cache, S), "rollout: tensor path needs tc_img, 8 <= S=%d <= 128, n_nodes=%d <= 112",
                      S, cache->n_nodes);
-    if (a.impl != RL4CO_IMPL_FP32 && tc_supported(cache, S)) return launch_rollout_tc(cache, a, st);
+    if (a.impl != RL4CO_IMPL_FP32 && a.impl != RL4CO_IMPL_STREAM && tc_supported(cache, S))
+        return launch_rollout_tc(cache, a, st);
+    // Single-start rows.  A batch that gives the streaming kernel at least ~8 warps per SM is served best by it (one
+    // warp per row, 64 rows per SM in flight hide every latency; measured c2 1.9 ms / c3 13.5 ms against 3.5 / 29 ms for
+    // the cooperative kernel).  Small batches (c1: 512 rows on 148 SMs) are latency-bound there: the cooperative kernel
+    // (CTA per instance, tables in shared memory, the warps of the CTA share one row's step) halves their time.
+    if (S == 1 && a.impl != RL4CO_IMPL_STREAM && coop_supported(cache) &&
+        (a.impl == RL4CO_IMPL_COOP || cache->B < (int64_t)sms * 8))
+        return launch_rollout_coop(cache, a, st);
     const size_t smem = 3ull * cache->n_nodes * kE * sizeof(float);
     const bool use_smem = S >= 8;
     if (use_smem) {
@@ -309,8 +322,17 @@ extern "C" int rl4co_rollout(const rl4co_cache* cache, const rl4co_rollout_args*
         auto kern = (env == RL4CO_ENV_TSP) ? rollout_global_kernel<RL4CO_ENV_TSP> : rollout_global_kernel<RL4CO_ENV_CVRP>;
         const int64_t rows = cache->B * S;
         int64_t blocks = (rows + kGlobalWarps - 1) / kGlobalWarps;
-        const int64_t cap = (int64_t)sms * 8;  // 8 CTAs x 8 warps = 64 warps per SM
-        if (blocks > cap) blocks = cap;
+        // A row is one long unit of work (its whole rollout) and the kernel is bound by HBM latency x bytes in flight:
+        // a last, nearly empty wave of CTAs runs at a fraction of the bandwidth.  The grid is sized to the resident
+        // capacity and the rows are split into EQUAL waves (each warp walks `waves` rows).
+        int occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kGlobalWarps * 32, 0) != cudaSuccess || occ < 1)
+            occ = 2;
+        const int64_t cap = (int64_t)sms * occ;
+        if (blocks > cap) {
+            const int64_t waves = (blocks + cap - 1) / cap;
+            blocks = (blocks + waves - 1) / waves;
+        }
         kern<<<(unsigned)blocks, kGlobalWarps * 32, 0, st>>>(*cache, a);
     }
     R4_CHECK_LAUNCH("rollout");

@@ -89,6 +89,8 @@ class AttentionModelDecoder(nn.Module):
         self.project_fixed_context = nn.Linear(embed_dim, embed_dim, bias=False)
         self.use_graph_context = use_graph_context
         self.is_dynamic_embedding = False
+        self.use_kernels = True        # cache precompute on the tcgen05 linear kernel (False: torch GEMM)
+        self._packer, self._zero_bias = None, None
 
     def pre_decoder_hook(self, td, env, embeddings, num_starts: int = 0):
         return td, env, self._precompute_cache(embeddings, num_starts=num_starts)
@@ -107,8 +109,13 @@ class AttentionModelDecoder(nn.Module):
             gc = 0
         tsp = self.env_name == "tsp"
         ws = [Wk, Wv, Wl_folded, Wc[:, :E]] + ([Wc[:, E:]] if tsp else [])
-        W = torch.stack([w.contiguous() for w in ws])                       # [k, E, E]
-        tabs = torch.matmul(h.reshape(1, B * n, E), W.transpose(1, 2)).view(len(ws), B, n, E)
+        if self.use_kernels and h.is_cuda and h.dtype == torch.float32 and n <= 128:
+            # the five [n,128] x [128,128] products on the tcgen05 linear kernel of csrc/encoder_tc.cu (split-fp16,
+            # fp32-accurate) instead of an fp32 SIMT GEMM; weight tiles are packed once per parameter version
+            tabs = self._precompute_kernels(h.contiguous(), ws)
+        else:
+            W = torch.stack([w.contiguous() for w in ws])                   # [k, E, E]
+            tabs = torch.matmul(h.reshape(1, B * n, E), W.transpose(1, 2)).view(len(ws), B, n, E)
         gk, gv, lkf = tabs[0], tabs[1], tabs[2]
         gcb = gc[:, None, :] if isinstance(gc, torch.Tensor) else 0
         if tsp:
@@ -124,6 +131,28 @@ class AttentionModelDecoder(nn.Module):
         if h.is_cuda and 8 <= num_starts <= 128:
             self._pack_tensor_tiles(cache)
         return cache
+
+    def _precompute_kernels(self, h, ws):
+        from .encoder import WeightPacker, kernel_linear
+        if self._packer is None:
+            self._packer = WeightPacker()
+        params = (self.project_node_embeddings.weight, self.pointer.project_out.weight,
+                  self.context_embedding.project_context.weight)
+        stamp = tuple(WeightPacker.stamp(p) for p in params)
+        if self._zero_bias is None or self._zero_bias.device != h.device:
+            self._zero_bias = torch.zeros(128, dtype=torch.float32, device=h.device)
+        return [kernel_linear(h, self._packer.pack(w.contiguous(), key=("pre", i), stamp=stamp), self._zero_bias, 128)
+                for i, w in enumerate(ws)]
+
+    def _apply(self, fn, *a, **kw):
+        if getattr(self, "_packer", None) is not None:
+            self._packer.clear()
+        return super()._apply(fn, *a, **kw)
+
+    def _load_from_state_dict(self, *a, **kw):
+        if getattr(self, "_packer", None) is not None:
+            self._packer.clear()
+        return super()._load_from_state_dict(*a, **kw)
 
     @staticmethod
     def _pack_tensor_tiles(cache: PrecomputedCache) -> None:

@@ -95,6 +95,46 @@ class MLP(nn.Module):
         return self.lins[1](F.relu(self.lins[0](x)))
 
 
+class WeightPacker:
+    """fp32 weight [n_out, k] -> fp16 hi/lo MMA tiles of csrc/encoder_tc.cu, cached per (key, version, storage)."""
+
+    def __init__(self):
+        self.cache = {}
+
+    def clear(self):
+        self.cache.clear()
+
+    @staticmethod
+    def stamp(w):
+        # `_version` moves with in-place updates autograd can see (optimiser steps), data_ptr with re-allocation
+        # (`.to`, `load_state_dict(assign=True)`); writes through `.data` that keep both need invalidate_packed()
+        return (w._version, w.data_ptr(), w.device)
+
+    def pack(self, w, key=None, stamp=None):
+        key = id(w) if key is None else key
+        ver = self.stamp(w) if stamp is None else stamp
+        hit = self.cache.get(key)
+        if hit is not None and hit[0] == ver:
+            return hit[1]
+        n_out, k = w.shape
+        L = _lib.lib()
+        buf = torch.empty(L.rl4co_enc_packed_bytes(n_out, k), dtype=torch.uint8, device=w.device)
+        _lib.check(L.rl4co_enc_pack_weight(_lib.ptr(w.detach().contiguous()), n_out, k, _lib.ptr(buf), _lib.stream_ptr()),
+                   "rl4co_enc_pack_weight")
+        self.cache[key] = (ver, buf)
+        return buf
+
+
+def kernel_linear(x, packed, bias, out_ch, epi=0, residual=None, gamma=None, beta=None, eps=0.0):
+    """Y [B, n, out_ch] = epilogue(X [B, n, k] W^T + bias) on the tcgen05 linear kernel (rl4co_enc_linear)."""
+    B, n, k = x.shape
+    y = torch.empty(B, n, out_ch, dtype=torch.float32, device=x.device)
+    _lib.check(_lib.lib().rl4co_enc_linear(
+        _lib.ptr(x), _lib.ptr(packed), _lib.ptr(bias), _lib.ptr(residual), _lib.ptr(gamma), _lib.ptr(beta),
+        C.c_float(eps), _lib.ptr(y), C.c_int64(B), n, k, out_ch, epi, _lib.stream_ptr()), "rl4co_enc_linear")
+    return y
+
+
 class GraphAttentionNetwork(nn.Module):
     def __init__(self, num_heads, embed_dim, num_layers, normalization, feedforward_hidden):
         super().__init__()
@@ -109,7 +149,8 @@ class GraphAttentionNetwork(nn.Module):
         self.num_heads, self.embed_dim, self.normalization = num_heads, embed_dim, normalization
         self.feedforward_hidden = feedforward_hidden
         self.use_kernels = True        # set False to force the PyTorch modules
-        self._packed = {}              # id(weight) -> (stamp, packed tiles)
+        self._packer = WeightPacker()  # id(weight) -> (stamp, packed tiles)
+        self._packed = self._packer.cache
 
     def kernels_apply(self, x):
         norm_ok = self.normalization == "instance" or (self.normalization == "batch" and not self.training)
@@ -131,25 +172,11 @@ class GraphAttentionNetwork(nn.Module):
         self._packed.clear()
         return super()._load_from_state_dict(*a, **kw)
 
-    @staticmethod
-    def _stamp(w):
-        # `_version` moves with in-place updates autograd can see (optimiser steps), data_ptr with re-allocation
-        # (`.to`, `load_state_dict(assign=True)`); writes through `.data` that keep both need invalidate_packed()
-        return (w._version, w.data_ptr(), w.device)
+    _stamp = staticmethod(WeightPacker.stamp)
 
     def _pack(self, w):
         """nn.Linear weight -> MMA tiles; cached per (parameter version, storage)."""
-        key, ver = id(w), self._stamp(w)
-        hit = self._packed.get(key)
-        if hit is not None and hit[0] == ver:
-            return hit[1]
-        n_out, k = w.shape
-        L = _lib.lib()
-        buf = torch.empty(L.rl4co_enc_packed_bytes(n_out, k), dtype=torch.uint8, device=w.device)
-        _lib.check(L.rl4co_enc_pack_weight(_lib.ptr(w.detach().contiguous()), n_out, k, _lib.ptr(buf), _lib.stream_ptr()),
-                   "rl4co_enc_pack_weight")
-        self._packed[key] = (ver, buf)
-        return buf
+        return self._packer.pack(w)
 
     def _bn_affine(self, bn):
         """Eval-mode BatchNorm1d (nn/ops.py:46-47) as a per-channel affine; cached per version of its four tensors."""
@@ -164,9 +191,6 @@ class GraphAttentionNetwork(nn.Module):
         return g, b
 
     def _linear(self, x, lin, epi, out_ch, residual=None, norm=None):
-        L = _lib.lib()
-        B, n, k = x.shape
-        y = torch.empty(B, n, out_ch, dtype=torch.float32, device=x.device)
         g = b = None
         eps = 0.0
         if norm is not None:
@@ -176,11 +200,7 @@ class GraphAttentionNetwork(nn.Module):
                 g, b = self._bn_affine(nrm)
             else:
                 g, b, eps = nrm.weight.detach(), nrm.bias.detach(), nrm.eps
-        _lib.check(L.rl4co_enc_linear(
-            _lib.ptr(x), _lib.ptr(self._pack(lin.weight)), _lib.ptr(lin.bias.detach()),
-            _lib.ptr(residual), _lib.ptr(g), _lib.ptr(b), C.c_float(eps),
-            _lib.ptr(y), C.c_int64(B), n, k, out_ch, epi, _lib.stream_ptr()), "rl4co_enc_linear")
-        return y
+        return kernel_linear(x, self._pack(lin.weight), lin.bias.detach(), out_ch, epi, residual, g, b, eps)
 
     def _forward_kernels(self, x):
         L = _lib.lib()

@@ -52,6 +52,10 @@ extern "C" {
 #define RL4CO_IMPL_AUTO 0           /* tensor path when num_starts >= 8 and cache->tc_img is set */
 #define RL4CO_IMPL_FP32 1           /* fp32 CUDA-core kernels                                     */
 #define RL4CO_IMPL_TC 2             /* tcgen05 kernels; error if the shape is unsupported         */
+#define RL4CO_IMPL_STREAM 3         /* single-start rows: warp per row, K/V/L streamed from global memory / L2 every
+                                       step (AUTO takes it when the batch gives >= 8 rows per SM)  */
+#define RL4CO_IMPL_COOP 4           /* single-start rows: CTA per instance, K/V/L resident in shared memory, the warps
+                                       of the CTA share one row's step (AUTO takes it for small batches)            */
 
 int rl4co_b200_abi_version(void);
 const char* rl4co_last_error(void);
