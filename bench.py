@@ -372,14 +372,8 @@ def run_b200(args):
             if e[1]:
                 _lib.raise_on_err(status_host[slot][1:])
 
-    def e2e_step():
-        i = n_e2e[0]
-        n_e2e[0] += 1
-        td = P.TensorDict({"locs": locs_host.to(dev, non_blocking=True)}, batch_size=[B])
-        td = env.reset(td)
-        with torch.no_grad():
-            out = pol(td, env, decode_type="multistart_greedy", check=False, instance_offset=lo)
-        status = pol.last_status
+    def publish(i, out, status):
+        """D2H of one step's results on the copy stream + deferred check of the error word (two slots)"""
         copy_stream.wait_stream(torch.cuda.current_stream())
         check_status(i & 1)                                   # step i-2's word, before its slot is reused
         with torch.cuda.stream(copy_stream):
@@ -391,29 +385,59 @@ def run_b200(args):
             ev = torch.cuda.Event()
             ev.record(copy_stream)
             copied[i & 1] = ev
-        return out
+
+    def e2e_step_eager():
+        i = n_e2e[0]
+        n_e2e[0] += 1
+        td = P.TensorDict({"locs": locs_host.to(dev, non_blocking=True)}, batch_size=[B])
+        td = env.reset(td)
+        with torch.no_grad():
+            out = pol(td, env, decode_type="multistart_greedy", check=False, instance_offset=lo)
+        publish(i, out, pol.last_status)
+
+    # The same public call captured once as a CUDA graph (eam_rl4co_b200.capture_rollout): ~40 launches per rollout
+    # become one driver call, which is what a 128-instance shard (N = 8) needs.  Two captures with their own output
+    # buffers alternate so that the D2H of step i still overlaps the compute of step i+1.
+    rolls = [P.capture_rollout(pol, env, locs_host, decode_type="multistart_greedy", instance_offset=lo)
+             for _ in range(2)]
+
+    def e2e_step_graph():
+        i = n_e2e[0]
+        n_e2e[0] += 1
+        roll = rolls[i & 1]
+        if copied[i & 1] is not None:                         # its outputs of step i-2 have left the device
+            torch.cuda.current_stream().wait_event(copied[i & 1])
+        out = roll(locs_host)                                 # H2D of the pinned instances + graph replay
+        publish(i, out, roll.status)
 
     def e2e_finish():
         torch.cuda.current_stream().wait_stream(copy_stream)
         check_status(0)
         check_status(1)
 
-    for _ in range(W):
-        e2e_step()
-    e2e_finish()
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(K):
-        e2e_step()
-    e2e_finish()                                              # the last steps' copies + checks are inside the region
-    e1.record()
-    barrier()
-    e2e_ms = e0.elapsed_time(e1)
+    def time_e2e(step):
+        n_e2e[0] = 0
+        copied[0] = copied[1] = None
+        for _ in range(W):
+            step()
+        e2e_finish()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(K):
+            step()
+        e2e_finish()                                          # the last steps' copies + checks are inside the region
+        e1.record()
+        barrier()
+        return e0.elapsed_time(e1)
+
+    e2e_eager_ms = time_e2e(e2e_step_eager)
+    e2e_ms = time_e2e(e2e_step_graph)
     clocks = sampler.stop() if rank == 0 else None   # sampled over both timed regions (device-resident and end-to-end)
 
     k_mean = statistics.mean(kernel_ms)
-    ms_total, e2e_ms, k_mean = sharding.max_over_ranks([ms_total, e2e_ms, k_mean], device=dev)   # device-timed, MAX
+    ms_total, e2e_ms, k_mean, e2e_eager_ms = sharding.max_over_ranks([ms_total, e2e_ms, k_mean, e2e_eager_ms],
+                                                                     device=dev)   # device-timed, MAX
 
     weak = None
     if world > 1 and not args.no_extras:
@@ -444,6 +468,10 @@ def run_b200(args):
                        "timed": "cache precompute + operand pack + persistent tcgen05 rollout kernel"},
             "e2e": {"value": isteps_global * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / K, "checked": True,
+                    "api": "eam_rl4co_b200.capture_rollout(policy, env, locs, decode_type) - the public call "
+                           "policy(td, env, decode_type=...) captured once as a CUDA graph and replayed per step",
+                    "uncaptured_ms_per_step": e2e_eager_ms / K,
+                    "uncaptured_value": isteps_global * K / (e2e_eager_ms * 1e-3),
                     "includes": "H2D locs, env.reset, encoder (tcgen05 kernels), cache precompute, rollout kernel, "
                                 "D2H reward+log_likelihood+actions+error word, host check of the error word"},
             "gpu_launches": 2 * len(kernel_ms),      # per step: r4::tc::tc_pack_kernel + r4::tc::rollout_tc_kernel

@@ -19,6 +19,7 @@ from . import pomo
 from . import data
 from .data import DeviceGenerator, load_data, load_npz_to_tensordict, save_tensordict_to_npz
 from .pomo import StateAugmentation, best_of_starts, pomo_evaluate
+from .graphs import GraphedRollout, capture_rollout
 
 
 def POMOPolicy(env_name: str = "tsp", **kw) -> AttentionModelPolicy:

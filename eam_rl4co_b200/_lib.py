@@ -33,7 +33,7 @@ EXPORTS = [
     "rl4co_b200_abi_version", "rl4co_last_error", "rl4co_tsp_step", "rl4co_cvrp_step_mask",
     "rl4co_cvrp_action_mask", "rl4co_tour_reward", "rl4co_select", "rl4co_decode_step",
     "rl4co_rollout", "rl4co_noise_gumbel", "rl4co_tc_image_bytes", "rl4co_tc_pack", "rl4co_tc_decode_step",
-    "rl4co_enc_packed_bytes", "rl4co_enc_pack_weight", "rl4co_enc_linear", "rl4co_enc_attention", "rl4co_best_of_starts", "rl4co_generate_instances", "rl4co_replay_states",
+    "rl4co_enc_packed_bytes", "rl4co_enc_pack_weight", "rl4co_enc_linear", "rl4co_enc_ffn", "rl4co_enc_attn_block", "rl4co_enc_attention", "rl4co_best_of_starts", "rl4co_generate_instances", "rl4co_replay_states",
 ]
 
 
@@ -127,3 +127,22 @@ def raise_on_err(err):
         for bit, msg in ERR_MESSAGES:
             if e[0] & bit:
                 raise AssertionError(f"{msg} (row {e[1] - 1})")
+
+
+class nvtx_range:
+    """NVTX range around a phase of the path (encoder / cache precompute / rollout): nsys and ncu captures of a
+    `policy(td, env, ...)` call are self-describing.  A no-op when CUDA is not initialised."""
+
+    def __init__(self, name: str):
+        self.name, self.on = name, False
+
+    def __enter__(self):
+        if torch.cuda.is_available() and torch.cuda.is_initialized():
+            torch.cuda.nvtx.range_push(self.name)
+            self.on = True
+        return self
+
+    def __exit__(self, *exc):
+        if self.on:
+            torch.cuda.nvtx.range_pop()
+        return False

@@ -160,6 +160,91 @@ __device__ __forceinline__ void issue_tile(uint32_t tmem, uint32_t dcol, uint32_
     }
 }
 
+
+// ---- residual + norm epilogue of a 128-column accumulator (TMEM columns [0,128) of `lane_base`) -------------------
+// EPI_RES_NORM: residual + InstanceNorm over the node axis (nn/ops.py:48-49; biased variance, eps inside the sqrt);
+// EPI_RES_AFFINE: residual + per-channel affine (eval-mode BatchNorm folded by the host).  Run by the four epilogue
+// warps (threads 0..127, thread = node row); `stage` is a [128][kStage] fp32 area (the idle W buffers).
+template <int EPI>
+__device__ __forceinline__ void epilogue_res_norm(uint32_t lane_base, unsigned char* stage, float* part, float* mean_s,
+                                                  float* rstd_s, const float* __restrict__ bias,
+                                                  const float* __restrict__ Rb, const float* __restrict__ gamma,
+                                                  const float* __restrict__ beta, float eps, float* __restrict__ Yb,
+                                                  int n) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int row = 32 * (warp & 3) + lane;
+    float* st = reinterpret_cast<float*>(stage);
+#pragma unroll 2
+    for (int col = 0; col < 128; col += 16) {
+        uint32_t v[16];
+        tmem_ld16(lane_base + (uint32_t)col, v);
+        tc_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 16; i += 4) {
+            const float4 bb = *reinterpret_cast<const float4*>(bias + col + i);
+            *reinterpret_cast<float4*>(st + row * kStage + col + i) =
+                make_float4(__uint_as_float(v[i]) + bb.x, __uint_as_float(v[i + 1]) + bb.y,
+                            __uint_as_float(v[i + 2]) + bb.z, __uint_as_float(v[i + 3]) + bb.w);
+        }
+    }
+    bar_sync(1, 128);                            // the four epilogue warps
+    if (EPI == EPI_RES_NORM) {
+        // column statistics, two passes (mean, then biased variance).  A warp takes every fourth node row
+        // and a lane four channels: the residual rows are read as coalesced 512-byte segments, all of a
+        // warp's loads are in flight together, and the four partial sums meet in shared memory.
+        const int c4 = 4 * lane;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+        for (int r = warp; r < n; r += 4) {
+            const float4 rr = *reinterpret_cast<const float4*>(Rb + (size_t)r * 128 + c4);
+            float4 v = *reinterpret_cast<const float4*>(st + r * kStage + c4);
+            v = make_float4(rr.x + v.x, rr.y + v.y, rr.z + v.z, rr.w + v.w);
+            *reinterpret_cast<float4*>(st + r * kStage + c4) = v;
+            acc = make_float4(acc.x + v.x, acc.y + v.y, acc.z + v.z, acc.w + v.w);
+        }
+        *reinterpret_cast<float4*>(part + warp * 128 + c4) = acc;
+        bar_sync(1, 128);
+        const int c = threadIdx.x;
+        const float mean = ((part[c] + part[128 + c]) + (part[256 + c] + part[384 + c])) / (float)n;
+        mean_s[c] = mean;
+        bar_sync(1, 128);
+        const float4 m4 = *reinterpret_cast<const float4*>(mean_s + c4);
+        acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+        for (int r = warp; r < n; r += 4) {
+            const float4 v = *reinterpret_cast<const float4*>(st + r * kStage + c4);
+            const float dx = v.x - m4.x, dy = v.y - m4.y, dz = v.z - m4.z, dw = v.w - m4.w;
+            acc = make_float4(fmaf(dx, dx, acc.x), fmaf(dy, dy, acc.y), fmaf(dz, dz, acc.z), fmaf(dw, dw, acc.w));
+        }
+        *reinterpret_cast<float4*>(part + 512 + warp * 128 + c4) = acc;
+        bar_sync(1, 128);
+        const float sq = (part[512 + c] + part[640 + c]) + (part[768 + c] + part[896 + c]);
+        rstd_s[c] = rsqrtf(sq / (float)n + eps);
+    }
+    bar_sync(1, 128);
+    for (int idx = threadIdx.x; idx < n * 32; idx += 128) {
+        const int r = idx >> 5, c4 = (idx & 31) * 4;
+        const float4 xv = *reinterpret_cast<const float4*>(st + r * kStage + c4);
+        const float4 g = *reinterpret_cast<const float4*>(gamma + c4);
+        const float4 be = *reinterpret_cast<const float4*>(beta + c4);
+        float4 o;
+        if (EPI == EPI_RES_AFFINE) {
+            const float4 rr = *reinterpret_cast<const float4*>(Rb + (size_t)r * 128 + c4);
+            o.x = __fadd_rn(__fmul_rn(rr.x + xv.x, g.x), be.x);
+            o.y = __fadd_rn(__fmul_rn(rr.y + xv.y, g.y), be.y);
+            o.z = __fadd_rn(__fmul_rn(rr.z + xv.z, g.z), be.z);
+            o.w = __fadd_rn(__fmul_rn(rr.w + xv.w, g.w), be.w);
+        } else {
+            o.x = __fadd_rn(__fmul_rn(__fmul_rn(xv.x - mean_s[c4], rstd_s[c4]), g.x), be.x);
+            o.y = __fadd_rn(__fmul_rn(__fmul_rn(xv.y - mean_s[c4 + 1], rstd_s[c4 + 1]), g.y), be.y);
+            o.z = __fadd_rn(__fmul_rn(__fmul_rn(xv.z - mean_s[c4 + 2], rstd_s[c4 + 2]), g.z), be.z);
+            o.w = __fadd_rn(__fmul_rn(__fmul_rn(xv.w - mean_s[c4 + 3], rstd_s[c4 + 3]), g.w), be.w);
+        }
+        *reinterpret_cast<float4*>(Yb + (size_t)r * 128 + c4) = o;
+    }
+    fence_proxy_async();   // the staging area is the next instance's TMA destination
+}
+
 #ifdef R4_ENC_PROF
 __device__ long long g_enc_prof[16];
 #define ENC_STAMP(k) do { if (blockIdx.x == 0 && threadIdx.x == PROF_T) { const long long now__ = clock64(); g_enc_prof[k] += now__ - tprev; tprev = now__; } } while (0)
@@ -323,81 +408,8 @@ __global__ void __launch_bounds__(kThreads, 1)
                 __syncwarp();
             }
         } else if (!producer) {
-            // residual + InstanceNorm over the node axis (nn/ops.py:48-49; biased variance, eps inside the sqrt)
-            float* st = reinterpret_cast<float*>(wsm);   // [128][kStage] fp32: the W buffers are idle now
-            const float* Rb = R + b * (int64_t)n * 128;
-#pragma unroll 2
-            for (int col = 0; col < 128; col += 16) {
-                uint32_t v[16];
-                tmem_ld16(lane_base + (uint32_t)col, v);
-                tc_wait_ld();
-#pragma unroll
-                for (int i = 0; i < 16; i += 4) {
-                    const float4 bb = *reinterpret_cast<const float4*>(bias + col + i);
-                    *reinterpret_cast<float4*>(st + row * kStage + col + i) =
-                        make_float4(__uint_as_float(v[i]) + bb.x, __uint_as_float(v[i + 1]) + bb.y,
-                                    __uint_as_float(v[i + 2]) + bb.z, __uint_as_float(v[i + 3]) + bb.w);
-                }
-            }
-            bar_sync(1, 128);                            // the four epilogue warps
-            if (EPI == EPI_RES_NORM) {
-                // column statistics, two passes (mean, then biased variance).  A warp takes every fourth node row
-                // and a lane four channels: the residual rows are read as coalesced 512-byte segments, all of a
-                // warp's loads are in flight together, and the four partial sums meet in shared memory.
-                float* part = s->part[0];
-                const int c4 = 4 * lane;
-                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 8
-                for (int r = warp; r < n; r += 4) {
-                    const float4 rr = *reinterpret_cast<const float4*>(Rb + (size_t)r * 128 + c4);
-                    float4 v = *reinterpret_cast<const float4*>(st + r * kStage + c4);
-                    v = make_float4(rr.x + v.x, rr.y + v.y, rr.z + v.z, rr.w + v.w);
-                    *reinterpret_cast<float4*>(st + r * kStage + c4) = v;
-                    acc = make_float4(acc.x + v.x, acc.y + v.y, acc.z + v.z, acc.w + v.w);
-                }
-                *reinterpret_cast<float4*>(part + warp * 128 + c4) = acc;
-                bar_sync(1, 128);
-                const int c = threadIdx.x;
-                const float mean = ((part[c] + part[128 + c]) + (part[256 + c] + part[384 + c])) / (float)n;
-                s->mean[c] = mean;
-                bar_sync(1, 128);
-                const float4 m4 = *reinterpret_cast<const float4*>(s->mean + c4);
-                acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 8
-                for (int r = warp; r < n; r += 4) {
-                    const float4 v = *reinterpret_cast<const float4*>(st + r * kStage + c4);
-                    const float dx = v.x - m4.x, dy = v.y - m4.y, dz = v.z - m4.z, dw = v.w - m4.w;
-                    acc = make_float4(fmaf(dx, dx, acc.x), fmaf(dy, dy, acc.y), fmaf(dz, dz, acc.z), fmaf(dw, dw, acc.w));
-                }
-                *reinterpret_cast<float4*>(part + 512 + warp * 128 + c4) = acc;
-                bar_sync(1, 128);
-                const float sq = (part[512 + c] + part[640 + c]) + (part[768 + c] + part[896 + c]);
-                s->rstd[c] = rsqrtf(sq / (float)n + eps);
-            }
-            bar_sync(1, 128);
-            float* Yb = Y + b * (int64_t)n * 128;
-            for (int idx = threadIdx.x; idx < n * 32; idx += 128) {
-                const int r = idx >> 5, c4 = (idx & 31) * 4;
-                const float4 xv = *reinterpret_cast<const float4*>(st + r * kStage + c4);
-                const float4 g = *reinterpret_cast<const float4*>(gamma + c4);
-                const float4 be = *reinterpret_cast<const float4*>(beta + c4);
-                float4 o;
-                if (EPI == EPI_RES_AFFINE) {
-                    const float4 rr = *reinterpret_cast<const float4*>(Rb + (size_t)r * 128 + c4);
-                    o.x = __fadd_rn(__fmul_rn(rr.x + xv.x, g.x), be.x);
-                    o.y = __fadd_rn(__fmul_rn(rr.y + xv.y, g.y), be.y);
-                    o.z = __fadd_rn(__fmul_rn(rr.z + xv.z, g.z), be.z);
-                    o.w = __fadd_rn(__fmul_rn(rr.w + xv.w, g.w), be.w);
-                    *reinterpret_cast<float4*>(Yb + (size_t)r * 128 + c4) = o;
-                    continue;
-                }
-                o.x = __fadd_rn(__fmul_rn(__fmul_rn(xv.x - s->mean[c4], s->rstd[c4]), g.x), be.x);
-                o.y = __fadd_rn(__fmul_rn(__fmul_rn(xv.y - s->mean[c4 + 1], s->rstd[c4 + 1]), g.y), be.y);
-                o.z = __fadd_rn(__fmul_rn(__fmul_rn(xv.z - s->mean[c4 + 2], s->rstd[c4 + 2]), g.z), be.z);
-                o.w = __fadd_rn(__fmul_rn(__fmul_rn(xv.w - s->mean[c4 + 3], s->rstd[c4 + 3]), g.w), be.w);
-                *reinterpret_cast<float4*>(Yb + (size_t)r * 128 + c4) = o;
-            }
-            fence_proxy_async();   // the staging area is the next instance's TMA destination
+            epilogue_res_norm<EPI>(lane_base, wsm, s->part[0], s->mean, s->rstd, bias, R + b * (int64_t)n * 128, gamma, beta,
+                                   eps, Y + b * (int64_t)n * 128, n);
         }
         ENC_STAMP(2);
         // the other parity's counters were last used one instance ago: reset them for the next one
@@ -405,6 +417,201 @@ __global__ void __launch_bounds__(kThreads, 1)
         tc_fence_before();
         __syncthreads();
         ENC_STAMP(3);
+    }
+    if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+
+// ---- fused feed-forward block: Y[b] = Norm(X[b] + relu(X[b] W1^T + b1) W2^T + b2) (attnnet.py:50-60, nn/mlp.py) -----
+// The hidden activations (n x 512 fp32 = 205 KB per instance, written and read back by the two-kernel form) never
+// leave the SM.  Per 128-wide hidden block k:  M1(k): acc1[k&1] = X W1[k]^T  (24 MMAs, operands in shared memory);
+// the four epilogue warps drain acc1, add b1, apply relu, split to fp16 hi/lo and store the block as a TS-form A
+// operand in TMEM;  M2(k): out += A W2[:, k]^T (24 MMAs, A from TMEM).  The MMAs are issued in the order
+// M1(0) M1(1) M2(0) M1(2) M2(1) ... so that the tensor pipe works on M1(k+1) while the epilogue warps convert block k.
+// W tiles stream through the two 64 KB buffers in that same order.  TMEM: acc1 x 2 [0,256), A hi [256,320), A lo
+// [320,384), out [384,512).  The final residual + norm epilogue is the one of enc_linear_kernel.
+struct FfnSmem {
+    uint64_t tma_bar[2];     // W tile landed in buffer i
+    uint64_t wfree_bar[2];   // the MMAs reading W buffer i are complete
+    uint64_t acc_full[2];    // M1 into acc1[i] is complete
+    uint64_t acc_free[2];    // the epilogue warps have drained acc1[i]            (128 arrivals)
+    uint64_t a_ready;        // the epilogue warps have written the A operand      (128 arrivals)
+    uint64_t a_free;         // the M2 reading the A operand is complete
+    uint64_t done_bar;       // every MMA of the instance is complete
+    uint32_t tmem_ptr;
+    uint32_t pad_;
+    alignas(16) float mean[kRows];
+    alignas(16) float rstd[kRows];
+    alignas(16) float part[2][4 * kRows];
+};
+constexpr size_t kFfnSmemBytes = kOffS + sizeof(FfnSmem);
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// out (+)= A[tmem] W2tile^T : 8 k-steps x (hi*hi + hi*lo + lo*hi), A = 128 channels as fp16 pairs (64 + 64 columns)
+__device__ __forceinline__ void issue_tile_ts(uint32_t dcol_addr, uint32_t a_hi, uint32_t a_lo, uint32_t ws, bool first) {
+    const uint32_t id = idesc_f16(kRows, 128);
+    uint64_t b_hi = smem_desc(ws, kLBO, kSBO), b_lo = smem_desc(ws + kHalf, kLBO, kSBO);
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) {
+        mma_ts(dcol_addr, a_hi + 8u * ks, b_hi, id, (first && ks == 0) ? 0u : 1u);
+        mma_ts(dcol_addr, a_hi + 8u * ks, b_lo, id, 1u);
+        mma_ts(dcol_addr, a_lo + 8u * ks, b_hi, id, 1u);
+        b_hi += (2u * kLBO) >> 4;
+        b_lo += (2u * kLBO) >> 4;
+    }
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(kThreads, 1)
+    enc_ffn_kernel(const float* __restrict__ X, const unsigned char* __restrict__ W1p, const float* __restrict__ b1,
+                   const unsigned char* __restrict__ W2p, const float* __restrict__ b2, const float* __restrict__ gamma,
+                   const float* __restrict__ beta, float eps, float* __restrict__ Y, int64_t B, int n, int nH) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned char* xs = smem + kOffX;
+    unsigned char* wsm = smem + kOffW;
+    FfnSmem* s = reinterpret_cast<FfnSmem*>(smem + kOffS);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&s->tma_bar[i], 1);
+            mbar_init(&s->wfree_bar[i], 1);
+            mbar_init(&s->acc_full[i], 1);
+            mbar_init(&s->acc_free[i], 128);
+        }
+        mbar_init(&s->a_ready, 128);
+        mbar_init(&s->a_free, 1);
+        mbar_init(&s->done_bar, 1);
+        fence_mbar_init();
+    }
+    __syncwarp();
+    if (warp == 0) tmem_alloc(&s->tmem_ptr, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s->tmem_ptr;
+    const uint32_t xs_a = smem_u32(xs), ws_a = smem_u32(wsm);
+    const bool producer = warp >= 4;
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * (warp & 3)) << 16);
+    constexpr uint32_t kColA = 256, kColOut = 384;
+    const int nSeq = 2 * nH;
+    // completed-phase counters (identical in every thread; each role only uses its own)
+    uint32_t n_tma[2] = {0, 0}, n_wfree[2] = {0, 0}, n_full[2] = {0, 0}, n_free[2] = {0, 0};
+    uint32_t n_aready = 0, n_afree = 0, n_done = 0;
+    bool have_prev_m2 = false;     // epilogue warps: an earlier M2 (this or the previous instance) read the A operand
+
+    if (producer && (int64_t)blockIdx.x < B) convert_x(X + (int64_t)blockIdx.x * n * 128, n, 128, 0, xs);
+    fence_proxy_async();
+    __syncthreads();
+
+    for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
+        if (warp == 4) {
+            if (elect_one()) {
+                // W tile of sequence position sq: even positions after 0 alternate M1(k) / M2(k-1)
+                auto tile_src = [&](int sq) -> const unsigned char* {
+                    if (sq == 0) return W1p;
+                    if (sq == nSeq - 1) return W2p + (size_t)(nH - 1) * kTile;
+                    return (sq & 1) ? W1p + (size_t)((sq + 1) >> 1) * kTile : W2p + (size_t)((sq >> 1) - 1) * kTile;
+                };
+                mbar_expect_tx(&s->tma_bar[0], kTile);
+                bulk_g2s(wsm, tile_src(0), kTile, &s->tma_bar[0]);
+                for (int sq = 0; sq < nSeq; ++sq) {
+                    const int buf = sq & 1;
+                    mbar_wait(&s->tma_bar[buf], n_tma[buf] & 1u);
+                    ++n_tma[buf];
+                    const bool is_m1 = (sq == 0) || ((sq & 1) && sq != nSeq - 1);
+                    if (is_m1) {
+                        const int k = (sq == 0) ? 0 : (sq + 1) >> 1;
+                        if (k >= 2) {             // acc1[k&1] was drained by the epilogue of block k-2
+                            mbar_wait(&s->acc_free[k & 1], n_free[k & 1] & 1u);
+                            ++n_free[k & 1];
+                        }
+                        tc_fence_after();
+                        issue_tile(tmem, (uint32_t)(k & 1) * 128u, xs_a, ws_a + (uint32_t)buf * kTile, true);
+                        tc_commit(&s->acc_full[k & 1]);
+                    } else {
+                        const int k = (sq == nSeq - 1) ? nH - 1 : (sq >> 1) - 1;
+                        mbar_wait(&s->a_ready, n_aready & 1u);
+                        ++n_aready;
+                        tc_fence_after();
+                        issue_tile_ts(tmem + kColOut, tmem + kColA, tmem + kColA + 64u, ws_a + (uint32_t)buf * kTile, k == 0);
+                        tc_commit(&s->a_free);
+                    }
+                    tc_commit(sq + 1 < nSeq ? &s->wfree_bar[buf] : &s->done_bar);
+                    // the next tile goes into the other buffer once ITS previous reader (position sq-1, queued ahead of
+                    // the MMAs just issued) is complete; the copy then runs under the MMAs of position sq
+                    if (sq + 1 < nSeq) {
+                        if (sq >= 1) {
+                            mbar_wait(&s->wfree_bar[buf ^ 1], n_wfree[buf ^ 1] & 1u);
+                            ++n_wfree[buf ^ 1];
+                        }
+                        mbar_expect_tx(&s->tma_bar[buf ^ 1], kTile);
+                        bulk_g2s(wsm + (size_t)(buf ^ 1) * kTile, tile_src(sq + 1), kTile, &s->tma_bar[buf ^ 1]);
+                    }
+                }
+                // the buffer commits nobody waited for, and the last two drains: keep waits == arrivals per barrier
+                // (by now they are all complete or about to be; the instance ends at done_bar)
+                mbar_wait(&s->wfree_bar[(nSeq - 2) & 1], n_wfree[(nSeq - 2) & 1] & 1u);
+                ++n_wfree[(nSeq - 2) & 1];
+                for (int k = (nH >= 2 ? nH - 2 : 0); k < nH; ++k) {
+                    mbar_wait(&s->acc_free[k & 1], n_free[k & 1] & 1u);
+                    ++n_free[k & 1];
+                }
+            }
+            __syncwarp();
+        } else if (!producer) {
+            // the four epilogue warps: hidden block k -> relu -> A operand
+            for (int k = 0; k < nH; ++k) {
+                mbar_wait(&s->acc_full[k & 1], n_full[k & 1] & 1u);
+                ++n_full[k & 1];
+                if (have_prev_m2) {               // the M2 of the previous block has finished reading the A operand
+                    mbar_wait(&s->a_free, n_afree & 1u);
+                    ++n_afree;
+                }
+                have_prev_m2 = true;
+                tc_fence_after();
+                const uint32_t src = lane_base + (uint32_t)(k & 1) * 128u;
+#pragma unroll 2
+                for (int c = 0; c < 128; c += 16) {
+                    uint32_t v[16], hi[8], lo[8];
+                    tmem_ld16(src + (uint32_t)c, v);
+                    tc_wait_ld();
+#pragma unroll
+                    for (int i = 0; i < 16; i += 4) {
+                        const float4 bb = *reinterpret_cast<const float4*>(b1 + 128 * k + c + i);
+                        const float f0 = fmaxf(__uint_as_float(v[i]) + bb.x, 0.f);
+                        const float f1 = fmaxf(__uint_as_float(v[i + 1]) + bb.y, 0.f);
+                        const float f2 = fmaxf(__uint_as_float(v[i + 2]) + bb.z, 0.f);
+                        const float f3 = fmaxf(__uint_as_float(v[i + 3]) + bb.w, 0.f);
+                        split2(f0, f1, hi[i >> 1], lo[i >> 1]);
+                        split2(f2, f3, hi[(i >> 1) + 1], lo[(i >> 1) + 1]);
+                    }
+                    tmem_st8(lane_base + kColA + (uint32_t)(c >> 1), hi);
+                    tmem_st8(lane_base + kColA + 64u + (uint32_t)(c >> 1), lo);
+                }
+                tc_fence_before();
+                mbar_arrive(&s->acc_free[k & 1]);     // every load of acc1[k&1] has completed (tc_wait_ld above)
+                tc_wait_st();
+                tc_fence_before();
+                mbar_arrive(&s->a_ready);
+            }
+        }
+        mbar_wait(&s->done_bar, n_done & 1u);
+        ++n_done;
+        tc_fence_after();
+        if (producer) {
+            // A tile of the next instance while the epilogue warps run the norm (all MMAs reading xs are complete)
+            const int64_t bn = b + gridDim.x;
+            if (bn < B) convert_x(X + bn * (int64_t)n * 128, n, 128, 0, xs);
+            fence_proxy_async();
+        } else {
+            epilogue_res_norm<EPI>(lane_base + kColOut, wsm, s->part[0], s->mean, s->rstd, b2, X + b * (int64_t)n * 128,
+                                   gamma, beta, eps, Y + b * (int64_t)n * 128, n);
+        }
+        tc_fence_before();
+        __syncthreads();
     }
     if (warp == 0) tmem_dealloc(tmem, 512);
 }
@@ -714,6 +921,303 @@ __global__ void __launch_bounds__(kAT, 1) enc_attention_tc_kernel(const float* _
     if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
+
+// ---- fused attention block: Y[b] = Norm(X[b] + MHA(X[b]) Wo^T + bo) (attnnet.py:43-49, attention.py:66-136) ---------
+// One kernel for what was qkv-linear -> attention -> out-proj+norm (three launches, 154 KB of q|k|v and 51 KB of
+// heads per instance through HBM).  Per instance, 512 threads:
+//   1. X -> fp16 hi/lo tile (region R0);  Q = X Wq^T, K = X Wk^T as usual (rows = nodes) and V^T = Wv X^T with the
+//      operand roles swapped (A = the packed Wv tile, B = the X tile), so the accumulator rows are channels and the
+//      V^T operand tile of the PV product is written with contiguous 16-byte stores - no transpose through memory.
+//      W tiles stream through R1 / R2 (TMA bulk copies).  Accumulators: TMEM [0,384).
+//   2. the accumulators are drained, biased (Q also scaled by 1/sqrt(16), exact), split and stored as operand tiles:
+//      Q -> R0 (X is dead), K -> R1, V^T -> R2.
+//   3. attention exactly as enc_attention_tc_kernel (two groups of four heads, scores in TMEM, softmax in registers,
+//      P in place as the TS-form A operand of the PV product); Wo streams into R0 once the last scores are done.
+//   4. the normalised heads go back to TMEM as a TS-form A operand, out = heads Wo^T (24 MMAs), residual + norm.
+struct BlockSmem {
+    // every barrier but mma_bar completes exactly once per instance (shared phase bit `ph`)
+    uint64_t wq_bar, wk_bar, wv_bar, wo_bar;   // W tile landed (TMA)
+    uint64_t r1free_bar;     // the Q product has finished reading Wq (R1 may take Wv)
+    uint64_t qkv_bar;        // the three projection products are complete
+    uint64_t mma_bar;        // attention MMAs of the four teams (4 arrivals), four completions per instance
+    uint64_t out_bar;        // out-proj MMAs complete
+    uint32_t tmem_ptr;
+    uint32_t pad_;
+    alignas(16) float mean[kRows];
+    alignas(16) float rstd[kRows];
+    alignas(16) float part[2][4 * kRows];
+};
+constexpr size_t kBlockSmemBytes = 3 * kTile + sizeof(BlockSmem);
+
+// accumulator block (128 columns at `src`, thread = row) -> + bias, * scale -> fp16 hi/lo K-major tile at `tile`
+// bias_per_row = false: bias indexed by column (Q, K: channel = column); true: by row (V^T: channel = row)
+__device__ __forceinline__ void drain_to_tile(uint32_t src, unsigned char* tile, const float* __restrict__ bias,
+                                              bool bias_per_row, float scale, int row) {
+    const float brow = bias_per_row ? bias[row] : 0.f;
+#pragma unroll 2
+    for (int c = 0; c < 128; c += 16) {
+        uint32_t v[16];
+        tmem_ld16(src + (uint32_t)c, v);
+        tc_wait_ld();
+        float f[16];
+#pragma unroll
+        for (int i = 0; i < 16; i += 4) {
+            float4 bb = make_float4(brow, brow, brow, brow);
+            if (!bias_per_row) bb = *reinterpret_cast<const float4*>(bias + c + i);
+            f[i] = (__uint_as_float(v[i]) + bb.x) * scale;
+            f[i + 1] = (__uint_as_float(v[i + 1]) + bb.y) * scale;
+            f[i + 2] = (__uint_as_float(v[i + 2]) + bb.z) * scale;
+            f[i + 3] = (__uint_as_float(v[i + 3]) + bb.w) * scale;
+        }
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {           // two 8-element K-chunks
+            uint32_t h4[4], l4[4];
+#pragma unroll
+            for (int p = 0; p < 4; ++p) split2(f[8 * hh + 2 * p], f[8 * hh + 2 * p + 1], h4[p], l4[p]);
+            const uint32_t off = (uint32_t)(row >> 3) * kSBO + (uint32_t)((c >> 3) + hh) * kLBO + (uint32_t)(row & 7) * 16u;
+            *reinterpret_cast<uint4*>(tile + off) = make_uint4(h4[0], h4[1], h4[2], h4[3]);
+            *reinterpret_cast<uint4*>(tile + kHalf + off) = make_uint4(l4[0], l4[1], l4[2], l4[3]);
+        }
+    }
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(kAT, 1)
+    enc_attn_block_kernel(const float* __restrict__ X, const unsigned char* __restrict__ Wqkvp,
+                          const float* __restrict__ bqkv, const unsigned char* __restrict__ Wop,
+                          const float* __restrict__ bo, const float* __restrict__ gamma, const float* __restrict__ beta,
+                          float eps, float* __restrict__ Y, int64_t B, int n, int npad) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned char* r0 = smem;                 // X tile -> Q tile -> Wo tile
+    unsigned char* r1 = smem + kTile;         // Wq, Wv -> K tile -> staging
+    unsigned char* r2 = smem + 2 * kTile;     // Wk -> V^T tile -> staging
+    BlockSmem* s = reinterpret_cast<BlockSmem*>(smem + 3 * kTile);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = warp & 3, j = warp >> 2, row = 32 * q + lane;
+    const int nch = npad / 16;
+    if (threadIdx.x == 0) {
+        mbar_init(&s->wq_bar, 1);
+        mbar_init(&s->wk_bar, 1);
+        mbar_init(&s->wv_bar, 1);
+        mbar_init(&s->wo_bar, 1);
+        mbar_init(&s->r1free_bar, 1);
+        mbar_init(&s->qkv_bar, 1);
+        mbar_init(&s->mma_bar, 4);
+        mbar_init(&s->out_bar, 1);
+        fence_mbar_init();
+    }
+    __syncwarp();
+    if (warp == 0) tmem_alloc(&s->tmem_ptr, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s->tmem_ptr;
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * q) << 16);
+    const uint32_t r0_a = smem_u32(r0), r1_a = smem_u32(r1), r2_a = smem_u32(r2);
+    uint32_t ph = 0, par = 0;   // ph: instance parity (once-per-instance barriers); par: mma_bar
+    const float kLog2e = 1.4426950408889634f;
+
+    for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
+        // ---- 1. X tile; Wq -> R1, Wk -> R2 in flight meanwhile ---------------------------------------------------
+        if (warp == 4) {
+            if (elect_one()) {
+                mbar_expect_tx(&s->wq_bar, kTile);
+                bulk_g2s(r1, Wqkvp, kTile, &s->wq_bar);
+                mbar_expect_tx(&s->wk_bar, kTile);
+                bulk_g2s(r2, Wqkvp + kTile, kTile, &s->wk_bar);
+            }
+            __syncwarp();
+        }
+        {
+            const float* Xb = X + b * (int64_t)n * 128;
+            for (int v = warp; v < 64; v += 16) {                // 64 warp passes: 8 rows x 4 chunks each
+                const int rg = v >> 2, c = 4 * (v & 3) + (lane >> 3), r = 8 * rg + (lane & 7);
+                float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bq = a;
+                if (r < n) {
+                    const float* src = Xb + (size_t)r * 128 + 8 * c;
+                    a = *reinterpret_cast<const float4*>(src);
+                    bq = *reinterpret_cast<const float4*>(src + 4);
+                }
+                uint32_t h4[4], l4[4];
+                split2(a.x, a.y, h4[0], l4[0]);
+                split2(a.z, a.w, h4[1], l4[1]);
+                split2(bq.x, bq.y, h4[2], l4[2]);
+                split2(bq.z, bq.w, h4[3], l4[3]);
+                unsigned char* dst = r0 + (uint32_t)rg * kSBO + (uint32_t)c * kLBO + (uint32_t)(lane & 7) * 16u;
+                *reinterpret_cast<uint4*>(dst) = make_uint4(h4[0], h4[1], h4[2], h4[3]);
+                *reinterpret_cast<uint4*>(dst + kHalf) = make_uint4(l4[0], l4[1], l4[2], l4[3]);
+            }
+        }
+        fence_proxy_async();
+        __syncthreads();
+        // ---- projections: Q [0,128), K [128,256), V^T [256,384) -------------------------------------------------
+        if (warp == 4) {
+            if (elect_one()) {
+                mbar_wait(&s->wq_bar, ph);
+                tc_fence_after();
+                issue_tile(tmem, 0u, r0_a, r1_a, true);            // Q = X Wq^T
+                tc_commit(&s->r1free_bar);
+                mbar_wait(&s->wk_bar, ph);
+                tc_fence_after();
+                issue_tile(tmem, 128u, r0_a, r2_a, true);          // K = X Wk^T
+                mbar_wait(&s->r1free_bar, ph);                     // the Q product has finished reading Wq
+                mbar_expect_tx(&s->wv_bar, kTile);
+                bulk_g2s(r1, Wqkvp + 2 * (size_t)kTile, kTile, &s->wv_bar);
+                mbar_wait(&s->wv_bar, ph);
+                tc_fence_after();
+                issue_tile(tmem, 256u, r1_a, r0_a, true);          // V^T = Wv X^T (operand roles swapped)
+                tc_commit(&s->qkv_bar);
+            }
+            __syncwarp();
+        }
+        mbar_wait(&s->qkv_bar, ph);
+        tc_fence_after();
+        // ---- 2. operand tiles: teams 0..2 drain one block each ---------------------------------------------------
+        if (j == 0) drain_to_tile(lane_base + 0u, r0, bqkv, false, 0.25f, row);            // Q / sqrt(16)
+        else if (j == 1) drain_to_tile(lane_base + 128u, r1, bqkv + 128, false, 1.0f, row);
+        else if (j == 2) drain_to_tile(lane_base + 256u, r2, bqkv + 256, true, 1.0f, row);  // rows = channels
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();
+        tc_fence_after();
+
+        // ---- 3. attention (enc_attention_tc_kernel with V^T at the full 128-key stride) --------------------------
+        float o_keep[16], o_last[16];
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+            const int h = 4 * g + j;
+            if (q == j) {
+                if (elect_one()) {
+                    tc_fence_after();
+                    const uint32_t id = idesc_f16(kRows, npad);
+                    const uint64_t a_hi = smem_desc(r0_a + 2u * h * kLBO, kLBO, kSBO);
+                    const uint64_t a_lo = smem_desc(r0_a + kHalf + 2u * h * kLBO, kLBO, kSBO);
+                    const uint64_t b_hi = smem_desc(r1_a + 2u * h * kLBO, kLBO, kSBO);
+                    const uint64_t b_lo = smem_desc(r1_a + kHalf + 2u * h * kLBO, kLBO, kSBO);
+                    const uint32_t d = tmem + (uint32_t)(j * npad);
+                    mma_ss(d, a_hi, b_hi, id, 0u);
+                    mma_ss(d, a_hi, b_lo, id, 1u);
+                    mma_ss(d, a_lo, b_hi, id, 1u);
+                    tc_commit(&s->mma_bar);
+                }
+                __syncwarp();
+            }
+            mbar_wait(&s->mma_bar, par);
+            par ^= 1u;
+            tc_fence_after();
+            if (g == 1 && warp == 4) {            // every score product is done: the Q tile is dead, Wo streams in
+                if (elect_one()) {
+                    fence_proxy_async();
+                    mbar_expect_tx(&s->wo_bar, kTile);
+                    bulk_g2s(r0, Wop, kTile, &s->wo_bar);
+                }
+                __syncwarp();
+            }
+            const uint32_t sp = lane_base + (uint32_t)(j * npad);
+            float m = -INFINITY;
+            for (int c = 0; c < nch; ++c) {
+                uint32_t v[16];
+                tmem_ld16(sp + 16u * c, v);
+                tc_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                    if (16 * c + i < n) m = fmaxf(m, __uint_as_float(v[i]));
+            }
+            const float ml = m * kLog2e;
+            float l0 = 0.f, l1 = 0.f;
+            for (int c = 0; c < nch; ++c) {
+                uint32_t v[16], hi[8], lo[8];
+                tmem_ld16(sp + 16u * c, v);
+                tc_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int k0 = 16 * c + 2 * i;
+                    const float p0 = (k0 < n) ? ex2_approx(fmaf(__uint_as_float(v[2 * i]), kLog2e, -ml)) : 0.f;
+                    const float p1 = (k0 + 1 < n) ? ex2_approx(fmaf(__uint_as_float(v[2 * i + 1]), kLog2e, -ml)) : 0.f;
+                    l0 += p0;
+                    l1 += p1;
+                    split2(p0, p1, hi[i], lo[i]);
+                }
+                tmem_st8(sp + 16u * c, hi);
+                tmem_st8(sp + 16u * c + 8u, lo);
+            }
+            tc_wait_st();
+            const float inv_l = 1.0f / (l0 + l1);
+            tc_fence_before();
+            __syncthreads();
+            if (q == j) {
+                if (elect_one()) {
+                    tc_fence_after();
+                    const uint32_t id = idesc_f16(kRows, 16);
+                    uint64_t bv_hi = smem_desc(r2_a + 2u * h * kSBO, kLBO, kSBO);
+                    uint64_t bv_lo = smem_desc(r2_a + kHalf + 2u * h * kSBO, kLBO, kSBO);
+                    const uint32_t d = tmem + kColO + 16u * j;
+                    uint32_t a = tmem + (uint32_t)(j * npad);
+                    for (int jk = 0; jk < nch; ++jk) {
+                        mma_ts(d, a, bv_hi, id, jk > 0 ? 1u : 0u);
+                        mma_ts(d, a, bv_lo, id, 1u);
+                        mma_ts(d, a + 8u, bv_hi, id, 1u);
+                        a += 16u;
+                        bv_hi += (2u * kLBO) >> 4;
+                        bv_lo += (2u * kLBO) >> 4;
+                    }
+                    tc_commit(&s->mma_bar);
+                }
+                __syncwarp();
+            }
+            mbar_wait(&s->mma_bar, par);
+            par ^= 1u;
+            tc_fence_after();
+            uint32_t o[16];
+            tmem_ld16(lane_base + kColO + 16u * j, o);
+            tc_wait_ld();
+            if (g == 0) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) o_keep[i] = __uint_as_float(o[i]) * inv_l;
+            } else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) o_last[i] = __uint_as_float(o[i]) * inv_l;
+            }
+            tc_fence_before();
+            __syncthreads();          // every warp has drained O and is done with P before the columns are reused
+            tc_fence_after();
+        }
+        // ---- 4. heads -> TS-form A operand (hi [0,64), lo [64,128)), out = heads Wo^T into [128,256) ---------------
+        {
+            uint32_t hi[8], lo[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) split2(o_keep[2 * i], o_keep[2 * i + 1], hi[i], lo[i]);
+            tmem_st8(lane_base + 8u * j, hi);                      // head j: channels [16j, 16j+16)
+            tmem_st8(lane_base + 64u + 8u * j, lo);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) split2(o_last[2 * i], o_last[2 * i + 1], hi[i], lo[i]);
+            tmem_st8(lane_base + 8u * (4 + j), hi);                // head 4 + j
+            tmem_st8(lane_base + 64u + 8u * (4 + j), lo);
+            tc_wait_st();
+        }
+        tc_fence_before();
+        __syncthreads();
+        if (warp == 4) {
+            if (elect_one()) {
+                mbar_wait(&s->wo_bar, ph);                         // Wo has landed in R0
+                tc_fence_after();
+                issue_tile_ts(tmem + 128u, tmem, tmem + 64u, r0_a, true);
+                tc_commit(&s->out_bar);
+            }
+            __syncwarp();
+        }
+        mbar_wait(&s->out_bar, ph);
+        ph ^= 1u;
+        tc_fence_after();
+        if (warp < 4)
+            epilogue_res_norm<EPI>(lane_base + 128u, r1, s->part[0], s->mean, s->rstd, bo, X + b * (int64_t)n * 128, gamma,
+                                   beta, eps, Y + b * (int64_t)n * 128, n);
+        tc_fence_before();
+        __syncthreads();
+    }
+    if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
 }  // namespace enc
 }  // namespace r4
 
@@ -790,6 +1294,85 @@ extern "C" int rl4co_enc_linear(const float* X, const void* Wpacked, const float
         default:
             R4_CHECK_ARG(false, "enc_linear: unknown epilogue %d", epilogue);
     }
+    return RL4CO_OK;
+}
+
+
+template <int EPI>
+static int launch_ffn(const float* X, const void* W1p, const float* b1, const void* W2p, const float* b2,
+                      const float* gamma, const float* beta, float eps, float* Y, int64_t B, int n, int hidden,
+                      cudaStream_t stream) {
+    auto kern = enc::enc_ffn_kernel<EPI>;
+    static bool prepared = false;
+    if (!prepared) {
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)enc::kFfnSmemBytes) != cudaSuccess) {
+            set_error("enc_ffn: cannot reserve %zu bytes of shared memory", enc::kFfnSmemBytes);
+            return RL4CO_E_LAUNCH;
+        }
+        prepared = true;
+    }
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const unsigned grid = (unsigned)(B < sms ? B : sms);
+    kern<<<grid, enc::kThreads, enc::kFfnSmemBytes, stream>>>(X, (const unsigned char*)W1p, b1, (const unsigned char*)W2p,
+                                                              b2, gamma, beta, eps, Y, B, n, hidden / 128);
+    R4_CHECK_LAUNCH("enc_ffn");
+    return RL4CO_OK;
+}
+
+extern "C" int rl4co_enc_ffn(const float* X, const void* W1packed, const float* b1, const void* W2packed,
+                             const float* b2, const float* gamma, const float* beta, float eps, float* Y, int64_t B,
+                             int32_t n, int32_t hidden, int32_t epilogue, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    R4_CHECK_ARG(X && W1packed && b1 && W2packed && b2 && gamma && beta && Y && B >= 0, "enc_ffn: null pointer");
+    R4_CHECK_ARG(n >= 1 && n <= enc::kRows, "enc_ffn: 1 <= nodes <= 128 (got %d)", n);
+    R4_CHECK_ARG(hidden >= 128 && hidden <= 512 && hidden % 128 == 0, "enc_ffn: hidden must be 128..512 in steps of 128 (got %d)", hidden);
+    if (B == 0) return RL4CO_OK;
+    if (epilogue == enc::EPI_RES_NORM)
+        return launch_ffn<enc::EPI_RES_NORM>(X, W1packed, b1, W2packed, b2, gamma, beta, eps, Y, B, n, hidden, stream);
+    if (epilogue == enc::EPI_RES_AFFINE)
+        return launch_ffn<enc::EPI_RES_AFFINE>(X, W1packed, b1, W2packed, b2, gamma, beta, 0.f, Y, B, n, hidden, stream);
+    R4_CHECK_ARG(false, "enc_ffn: epilogue must be RES_NORM or RES_AFFINE (got %d)", epilogue);
+    return RL4CO_OK;
+}
+
+
+template <int EPI>
+static int launch_attn_block(const float* X, const void* Wqkvp, const float* bqkv, const void* Wop, const float* bo,
+                             const float* gamma, const float* beta, float eps, float* Y, int64_t B, int n,
+                             cudaStream_t stream) {
+    auto kern = enc::enc_attn_block_kernel<EPI>;
+    static bool prepared = false;
+    if (!prepared) {
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)enc::kBlockSmemBytes) != cudaSuccess) {
+            set_error("enc_attn_block: cannot reserve %zu bytes of shared memory", enc::kBlockSmemBytes);
+            return RL4CO_E_LAUNCH;
+        }
+        prepared = true;
+    }
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const unsigned grid = (unsigned)(B < sms ? B : sms);
+    kern<<<grid, enc::kAT, enc::kBlockSmemBytes, stream>>>(X, (const unsigned char*)Wqkvp, bqkv, (const unsigned char*)Wop,
+                                                            bo, gamma, beta, eps, Y, B, n, (n + 15) & ~15);
+    R4_CHECK_LAUNCH("enc_attn_block");
+    return RL4CO_OK;
+}
+
+extern "C" int rl4co_enc_attn_block(const float* X, const void* Wqkv_packed, const float* bqkv, const void* Wo_packed,
+                                    const float* bo, const float* gamma, const float* beta, float eps, float* Y,
+                                    int64_t B, int32_t n, int32_t epilogue, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    R4_CHECK_ARG(X && Wqkv_packed && bqkv && Wo_packed && bo && gamma && beta && Y && B >= 0, "enc_attn_block: null pointer");
+    R4_CHECK_ARG(n >= 1 && ((n + 15) & ~15) <= 112, "enc_attn_block: 1 <= nodes <= 112 (got %d)", n);
+    if (B == 0) return RL4CO_OK;
+    if (epilogue == enc::EPI_RES_NORM)
+        return launch_attn_block<enc::EPI_RES_NORM>(X, Wqkv_packed, bqkv, Wo_packed, bo, gamma, beta, eps, Y, B, n, stream);
+    if (epilogue == enc::EPI_RES_AFFINE)
+        return launch_attn_block<enc::EPI_RES_AFFINE>(X, Wqkv_packed, bqkv, Wo_packed, bo, gamma, beta, 0.f, Y, B, n, stream);
+    R4_CHECK_ARG(false, "enc_attn_block: epilogue must be RES_NORM or RES_AFFINE (got %d)", epilogue);
     return RL4CO_OK;
 }
 

@@ -149,6 +149,8 @@ class GraphAttentionNetwork(nn.Module):
         self.num_heads, self.embed_dim, self.normalization = num_heads, embed_dim, normalization
         self.feedforward_hidden = feedforward_hidden
         self.use_kernels = True        # set False to force the PyTorch modules
+        self.fuse_ffn = True           # FFN1 + FFN2 + norm in one kernel (False: two enc_linear launches)
+        self.fuse_attention = True     # QKV + attention + out-proj + norm in one kernel (n <= 112)
         self._packer = WeightPacker()  # id(weight) -> (stamp, packed tiles)
         self._packed = self._packer.cache
 
@@ -208,14 +210,50 @@ class GraphAttentionNetwork(nn.Module):
         B, n, E = x.shape
         for layer in self.layers:
             mha, norm1, mlp, norm2 = layer[0].module, layer[1], layer[2].module, layer[3]
-            qkv = self._linear(x, mha.Wqkv, _lib.ENC_EPI_PLAIN, 3 * E)
-            heads = torch.empty(B, n, E, dtype=torch.float32, device=x.device)
-            _lib.check(L.rl4co_enc_attention(_lib.ptr(qkv), _lib.ptr(heads), C.c_int64(B), n, _lib.stream_ptr()),
-                       "rl4co_enc_attention")
-            x = self._linear(heads, mha.out_proj, _lib.ENC_EPI_RES_NORM, E, residual=x, norm=norm1)
-            f = self._linear(x, mlp.lins[0], _lib.ENC_EPI_RELU, self.feedforward_hidden)
-            x = self._linear(f, mlp.lins[1], _lib.ENC_EPI_RES_NORM, E, residual=x, norm=norm2)
+            if self.fuse_attention and n <= 112:
+                x = self._attn_block(x, mha, norm1)
+            else:
+                qkv = self._linear(x, mha.Wqkv, _lib.ENC_EPI_PLAIN, 3 * E)
+                heads = torch.empty(B, n, E, dtype=torch.float32, device=x.device)
+                _lib.check(L.rl4co_enc_attention(_lib.ptr(qkv), _lib.ptr(heads), C.c_int64(B), n, _lib.stream_ptr()),
+                           "rl4co_enc_attention")
+                x = self._linear(heads, mha.out_proj, _lib.ENC_EPI_RES_NORM, E, residual=x, norm=norm1)
+            if self.fuse_ffn:
+                x = self._ffn(x, mlp, norm2)
+            else:
+                f = self._linear(x, mlp.lins[0], _lib.ENC_EPI_RELU, self.feedforward_hidden)
+                x = self._linear(f, mlp.lins[1], _lib.ENC_EPI_RES_NORM, E, residual=x, norm=norm2)
         return x
+
+    def _norm_args(self, norm):
+        nrm = norm.normalizer
+        if isinstance(nrm, nn.BatchNorm1d):
+            g, b = self._bn_affine(nrm)
+            return _lib.ENC_EPI_RES_AFFINE, g, b, 0.0
+        return _lib.ENC_EPI_RES_NORM, nrm.weight.detach(), nrm.bias.detach(), nrm.eps
+
+    def _attn_block(self, x, mha, norm):
+        """Norm(x + MHA(x) Wo^T + bo) in ONE kernel (rl4co_enc_attn_block): q, k, v and the heads stay on chip."""
+        B, n, E = x.shape
+        y = torch.empty_like(x)
+        epi, g, b, eps = self._norm_args(norm)
+        _lib.check(_lib.lib().rl4co_enc_attn_block(
+            _lib.ptr(x), _lib.ptr(self._pack(mha.Wqkv.weight)), _lib.ptr(mha.Wqkv.bias.detach()),
+            _lib.ptr(self._pack(mha.out_proj.weight)), _lib.ptr(mha.out_proj.bias.detach()), _lib.ptr(g), _lib.ptr(b),
+            C.c_float(eps), _lib.ptr(y), C.c_int64(B), n, epi, _lib.stream_ptr()), "rl4co_enc_attn_block")
+        return y
+
+    def _ffn(self, x, mlp, norm):
+        """Norm(x + W2 relu(W1 x + b1) + b2) in ONE kernel (rl4co_enc_ffn): the hidden activations stay in TMEM."""
+        B, n, E = x.shape
+        y = torch.empty_like(x)
+        epi, g, b, eps = self._norm_args(norm)
+        l1, l2 = mlp.lins
+        _lib.check(_lib.lib().rl4co_enc_ffn(
+            _lib.ptr(x), _lib.ptr(self._pack(l1.weight)), _lib.ptr(l1.bias.detach()), _lib.ptr(self._pack(l2.weight)),
+            _lib.ptr(l2.bias.detach()), _lib.ptr(g), _lib.ptr(b), C.c_float(eps), _lib.ptr(y), C.c_int64(B), n,
+            self.feedforward_hidden, epi, _lib.stream_ptr()), "rl4co_enc_ffn")
+        return y
 
     def forward(self, x):
         if self.kernels_apply(x):

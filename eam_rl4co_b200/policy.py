@@ -66,7 +66,7 @@ class AttentionModelPolicy(nn.Module):
             if hidden is not None:
                 hidden, init_embeds = hidden.detach(), None
             else:
-                with torch.no_grad():
+                with torch.no_grad(), _lib.nvtx_range("rl4co_b200.encoder"):
                     hidden, init_embeds = self.encoder(td)                       # base.py:195
         elif hidden is not None:
             init_embeds = None
@@ -151,7 +151,8 @@ class AttentionModelPolicy(nn.Module):
             S = env.get_num_starts(td) if num_starts is None else num_starts
         rows = B * max(S, 1)
         dev = hidden.device
-        td, env, cache = self.decoder.pre_decoder_hook(td, env, hidden, S)
+        with _lib.nvtx_range("rl4co_b200.cache_precompute"):
+            td, env, cache = self.decoder.pre_decoder_hook(td, env, hidden, S)
         if actions is not None:
             actions = actions.contiguous()
             T = actions.shape[1]
@@ -203,7 +204,8 @@ class AttentionModelPolicy(nn.Module):
         if events is not None:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-        rc = _lib.lib().rl4co_rollout(C.byref(cs), C.byref(args), _lib.stream_ptr())
+        with _lib.nvtx_range("rl4co_b200.rollout"):
+            rc = _lib.lib().rl4co_rollout(C.byref(cs), C.byref(args), _lib.stream_ptr())
         _lib.check(rc, "rl4co_rollout")
         if events is not None:
             e1.record()

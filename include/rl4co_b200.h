@@ -224,6 +224,17 @@ int rl4co_enc_pack_weight(const float* W, int32_t n_out, int32_t k, void* packed
 int rl4co_enc_linear(const float* X, const void* Wpacked, const float* bias, const float* residual,
                      const float* gamma, const float* beta, float eps, float* Y, int64_t B, int32_t n,
                      int32_t k, int32_t n_out, int32_t epilogue, void* stream);
+/* Fused feed-forward block (attnnet.py:50-60, nn/mlp.py): Y = Norm(X + relu(X W1^T + b1) W2^T + b2) with the hidden
+ * activations kept on chip (TMEM); W1 [hidden,128], W2 [128,hidden] packed by rl4co_enc_pack_weight, hidden in
+ * {128,256,384,512}; epilogue = RL4CO_ENC_EPI_RES_NORM (gamma/beta/eps of the InstanceNorm) or _RES_AFFINE.        */
+int rl4co_enc_ffn(const float* X, const void* W1packed, const float* b1, const void* W2packed, const float* b2,
+                  const float* gamma, const float* beta, float eps, float* Y, int64_t B, int32_t n, int32_t hidden,
+                  int32_t epilogue, void* stream);
+/* Fused attention block (attnnet.py:43-49, attention.py:66-136): Y = Norm(X + MHA(X) Wo^T + bo), 8 heads x 16, no
+ * mask, n <= 112; Wqkv [384,128] and Wo [128,128] packed by rl4co_enc_pack_weight; q, k, v and the heads stay on chip. */
+int rl4co_enc_attn_block(const float* X, const void* Wqkv_packed, const float* bqkv, const void* Wo_packed,
+                         const float* bo, const float* gamma, const float* beta, float eps, float* Y, int64_t B,
+                         int32_t n, int32_t epilogue, void* stream);
 /* qkv [B, n, 384] = (q | k | v) x (8 heads x 16) -> heads [B, n, 128] (input of out_proj), no mask */
 int rl4co_enc_attention(const float* qkv, float* out, int64_t B, int32_t n, void* stream);
 

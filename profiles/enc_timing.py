@@ -33,8 +33,14 @@ def main():
         print(f"out   linear 128->128 + norm {timed(lambda: net._linear(x, mha.out_proj, 2, 128, residual=x, norm=norm1)):8.3f} ms")
         print(f"ffn1  linear 128->512 relu   {timed(lambda: net._linear(x, mlp.lins[0], 1, 512)):8.3f} ms")
         print(f"ffn2  linear 512->128 + norm {timed(lambda: net._linear(f, mlp.lins[1], 2, 128, residual=x, norm=norm2)):8.3f} ms")
+        print(f"fused ffn (ffn1+ffn2+norm)   {timed(lambda: net._ffn(x, mlp, norm2)):8.3f} ms")
+        print(f"fused attention block        {timed(lambda: net._attn_block(x, mha, norm1)):8.3f} ms")
         td = P.TSPEnv(generator_params=dict(num_loc=n), device=dev).reset(P.TensorDict({"locs": bench.make_instances(B).to(dev)}, batch_size=[B]))
         print(f"encoder, kernels             {timed(lambda: pol.encoder(td)):8.3f} ms")
+        net.fuse_attention = False
+        print(f"encoder, kernels, unfused attention {timed(lambda: pol.encoder(td)):8.3f} ms")
+        net.fuse_ffn = False
+        print(f"encoder, kernels, 5 launches/layer  {timed(lambda: pol.encoder(td)):8.3f} ms")
         net.use_kernels = False
         print(f"encoder, torch               {timed(lambda: pol.encoder(td)):8.3f} ms")
 

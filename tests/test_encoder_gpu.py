@@ -156,3 +156,73 @@ def test_encoder_kernels_match_reference_fixture(path):
     ll_ref = torch.from_numpy(g["z"][f"{dt}.log_likelihood"])
     assert torch.allclose(out["reward"].cpu()[same], r_ref[same], rtol=1e-5, atol=1e-5)
     assert torch.allclose(out["log_likelihood"].cpu()[same], ll_ref[same], rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("n,B", [(100, 3), (20, 5), (128, 2), (51, 300)])
+@pytest.mark.parametrize("norm", ["instance", "batch"])
+def test_fused_ffn_matches_fp64(n, B, norm):
+    """rl4co_enc_ffn: Norm(x + W2 relu(W1 x + b1) + b2) with the hidden activations kept in TMEM, against float64."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(5)
+    pol = (P.POMOPolicy("tsp") if norm == "instance" else P.AttentionModelPolicy(env_name="tsp")).eval().to(DEV)
+    net = pol.encoder.net
+    layer = net.layers[1]
+    mlp, norm2 = layer[2].module, layer[3]
+    with torch.no_grad():
+        norm2.normalizer.weight.uniform_(0.5, 1.5)
+        norm2.normalizer.bias.uniform_(-0.5, 0.5)
+        if norm == "batch":
+            norm2.normalizer.running_mean.normal_(0, 0.3)
+            norm2.normalizer.running_var.uniform_(0.5, 1.5)
+    g = torch.Generator(device=DEV).manual_seed(n * 7 + B)
+    x = torch.randn(B, n, 128, device=DEV, generator=g)
+    with torch.no_grad():
+        got = net._ffn(x, mlp, norm2)
+        f = F.relu(_lin64(mlp.lins[0], x))
+        pre = x.double() + F.linear(f, mlp.lins[1].weight.double(), mlp.lins[1].bias.double())
+        if norm == "instance":
+            ref = _norm64(norm2, pre)
+        else:
+            bn = norm2.normalizer
+            ref = (pre - bn.running_mean.double()) * torch.rsqrt(bn.running_var.double() + bn.eps) * bn.weight.double() \
+                + bn.bias.double()
+    err = _rel(got, ref.float())
+    print(f"fused ffn {norm} n={n} B={B}: rel err {err:.2e}")
+    assert err < 2e-6, err
+
+
+@pytest.mark.parametrize("n,B", [(100, 3), (20, 5), (112, 2), (51, 300), (101, 4)])
+@pytest.mark.parametrize("norm", ["instance", "batch"])
+def test_fused_attention_block_matches_fp64(n, B, norm):
+    """rl4co_enc_attn_block: Norm(x + MHA(x) Wo^T + bo) with q, k, v^T and the heads kept on chip, against float64."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(6)
+    pol = (P.POMOPolicy("tsp") if norm == "instance" else P.AttentionModelPolicy(env_name="tsp")).eval().to(DEV)
+    net = pol.encoder.net
+    layer = net.layers[0]
+    mha, norm1 = layer[0].module, layer[1]
+    with torch.no_grad():
+        norm1.normalizer.weight.uniform_(0.5, 1.5)
+        norm1.normalizer.bias.uniform_(-0.5, 0.5)
+        mha.Wqkv.bias.uniform_(-0.3, 0.3)
+        mha.out_proj.bias.uniform_(-0.3, 0.3)
+        if norm == "batch":
+            norm1.normalizer.running_mean.normal_(0, 0.3)
+            norm1.normalizer.running_var.uniform_(0.5, 1.5)
+    g = torch.Generator(device=DEV).manual_seed(n * 3 + B)
+    x = torch.randn(B, n, 128, device=DEV, generator=g)
+    with torch.no_grad():
+        got = net._attn_block(x, mha, norm1)
+        qkv = _lin64(mha.Wqkv, x)
+        q, k, v = qkv.view(B, n, 3, 8, 16).permute(2, 0, 3, 1, 4).unbind(0)
+        a = F.scaled_dot_product_attention(q, k, v).transpose(1, 2).reshape(B, n, 128)
+        pre = x.double() + F.linear(a, mha.out_proj.weight.double(), mha.out_proj.bias.double())
+        if norm == "instance":
+            ref = _norm64(norm1, pre)
+        else:
+            bn = norm1.normalizer
+            ref = (pre - bn.running_mean.double()) * torch.rsqrt(bn.running_var.double() + bn.eps) * bn.weight.double() \
+                + bn.bias.double()
+    err = _rel(got, ref.float())
+    print(f"fused attention block {norm} n={n} B={B}: rel err {err:.2e}")
+    assert err < 2e-6, err

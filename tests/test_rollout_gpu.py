@@ -264,3 +264,23 @@ def test_single_start_kernels_against_oracle(env_name, N, B, decode_type):
         assert stats["T_got"] >= stats["T_ref"] or stats["exact"] < 1.0
     ev = pol(td.clone(), env, actions=out["actions"])
     assert rel_close(ev["log_likelihood"], out["log_likelihood"], 1e-6)
+
+
+def test_captured_graph_replays_the_eager_rollout():
+    """capture_rollout: the CUDA graph holds the same launches as the eager call - identical outputs, new inputs are
+    picked up on replay, the error word is readable."""
+    N, B = 50, 16
+    inst, pol, w, env, td, h = _setup("tsp", True, N, B, seed=13)
+    eager = pol(td.clone(), env, decode_type="multistart_greedy")
+    roll = P.capture_rollout(pol, env, inst["locs"], decode_type="multistart_greedy")
+    out = roll(inst["locs"].to(DEV))
+    for k in ("actions", "reward", "log_likelihood"):
+        assert torch.equal(out[k], eager[k]), k
+    roll.raise_on_error()
+    inst2, _, _, env2, td2, _ = _setup("tsp", True, N, B, seed=14)
+    eager2 = pol(td2.clone(), env2, decode_type="multistart_greedy")
+    out2 = roll(inst2["locs"].pin_memory())
+    torch.cuda.synchronize()
+    assert torch.equal(out2["actions"], eager2["actions"]) and torch.equal(out2["reward"], eager2["reward"])
+    with pytest.raises(NotImplementedError):
+        P.capture_rollout(pol, P.get_env("cvrp", device=DEV), inst["locs"])
