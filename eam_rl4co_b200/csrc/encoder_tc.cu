@@ -46,10 +46,22 @@ struct Smem {
     int next_chunk[2][4];  // [instance parity][TMEM lane quadrant]: next 32-column chunk of the epilogue to drain
     alignas(16) float mean[kRows];
     alignas(16) float rstd[kRows];
-    alignas(16) float part[2][4 * kRows];   // per-warp partial column sums (mean pass, variance pass)
+    alignas(16) float part[2][16 * kRows];  // per-warp partial column sums (mean pass, variance pass), <= 16 warps
 };
 constexpr uint32_t kOffX = 0, kOffW = kTile, kOffS = 3 * kTile;
 constexpr size_t kSmemBytes = kOffS + sizeof(Smem);
+
+// one 64 KB W tile as R4_TMA_SPLIT bulk copies counted on the same mbarrier (expect_tx covers the whole tile)
+#ifndef R4_TMA_SPLIT
+#define R4_TMA_SPLIT 1
+#endif
+__device__ __forceinline__ void bulk_tile(void* dst, const void* src, uint64_t* bar) {
+    constexpr uint32_t piece = kTile / R4_TMA_SPLIT;
+#pragma unroll
+    for (int i = 0; i < R4_TMA_SPLIT; ++i)
+        bulk_g2s(reinterpret_cast<unsigned char*>(dst) + i * piece, reinterpret_cast<const unsigned char*>(src) + i * piece,
+                 piece, bar);
+}
 
 // ---- weights: W [n_out, K] fp32 (nn.Linear layout) -> tiles (kb, nb) of 128 x 128, hi then lo, in consumption order
 __global__ void __launch_bounds__(256) enc_pack_weight_kernel(const float* __restrict__ W, int n_out, int K,
@@ -163,19 +175,22 @@ __device__ __forceinline__ void issue_tile(uint32_t tmem, uint32_t dcol, uint32_
 
 // ---- residual + norm epilogue of a 128-column accumulator (TMEM columns [0,128) of `lane_base`) -------------------
 // EPI_RES_NORM: residual + InstanceNorm over the node axis (nn/ops.py:48-49; biased variance, eps inside the sqrt);
-// EPI_RES_AFFINE: residual + per-channel affine (eval-mode BatchNorm folded by the host).  Run by the four epilogue
-// warps (threads 0..127, thread = node row); `stage` is a [128][kStage] fp32 area (the idle W buffers).
-template <int EPI>
+// EPI_RES_AFFINE: residual + per-channel affine (eval-mode BatchNorm folded by the host).  Run by the first NT threads
+// of the CTA (NT = 128, 256 or 512: warp w drains the columns [CW (w / 4), +CW) of TMEM lane quadrant w % 4,
+// CW = 128 / (NT / 128)); `stage` is a [128][kStage] fp32 area (idle operand buffers); `part` holds 2 x (NT / 32) x 128
+// floats.  `lane_base` = accumulator base with the caller's quadrant lane offset.
+template <int EPI, int NT>
 __device__ __forceinline__ void epilogue_res_norm(uint32_t lane_base, unsigned char* stage, float* part, float* mean_s,
                                                   float* rstd_s, const float* __restrict__ bias,
                                                   const float* __restrict__ Rb, const float* __restrict__ gamma,
                                                   const float* __restrict__ beta, float eps, float* __restrict__ Yb,
                                                   int n) {
+    constexpr int NW = NT / 32, CW = 128 / (NT / 128);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int row = 32 * (warp & 3) + lane;
+    const int row = 32 * (warp & 3) + lane, c0 = CW * (warp >> 2);
     float* st = reinterpret_cast<float*>(stage);
 #pragma unroll 2
-    for (int col = 0; col < 128; col += 16) {
+    for (int col = c0; col < c0 + CW; col += 16) {
         uint32_t v[16];
         tmem_ld16(lane_base + (uint32_t)col, v);
         tc_wait_ld();
@@ -187,15 +202,15 @@ __device__ __forceinline__ void epilogue_res_norm(uint32_t lane_base, unsigned c
                             __uint_as_float(v[i + 2]) + bb.z, __uint_as_float(v[i + 3]) + bb.w);
         }
     }
-    bar_sync(1, 128);                            // the four epilogue warps
+    bar_sync(1, NT);
     if (EPI == EPI_RES_NORM) {
-        // column statistics, two passes (mean, then biased variance).  A warp takes every fourth node row
-        // and a lane four channels: the residual rows are read as coalesced 512-byte segments, all of a
-        // warp's loads are in flight together, and the four partial sums meet in shared memory.
+        // column statistics, two passes (mean, then biased variance).  A warp takes every NW-th node row and a lane
+        // four channels: the residual rows are read as coalesced 512-byte segments, all of a warp's loads are in
+        // flight together, and the NW partial sums meet in shared memory.
         const int c4 = 4 * lane;
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 8
-        for (int r = warp; r < n; r += 4) {
+#pragma unroll 4
+        for (int r = warp; r < n; r += NW) {
             const float4 rr = *reinterpret_cast<const float4*>(Rb + (size_t)r * 128 + c4);
             float4 v = *reinterpret_cast<const float4*>(st + r * kStage + c4);
             v = make_float4(rr.x + v.x, rr.y + v.y, rr.z + v.z, rr.w + v.w);
@@ -203,26 +218,34 @@ __device__ __forceinline__ void epilogue_res_norm(uint32_t lane_base, unsigned c
             acc = make_float4(acc.x + v.x, acc.y + v.y, acc.z + v.z, acc.w + v.w);
         }
         *reinterpret_cast<float4*>(part + warp * 128 + c4) = acc;
-        bar_sync(1, 128);
+        bar_sync(1, NT);
         const int c = threadIdx.x;
-        const float mean = ((part[c] + part[128 + c]) + (part[256 + c] + part[384 + c])) / (float)n;
-        mean_s[c] = mean;
-        bar_sync(1, 128);
+        if (c < 128) {
+            float sum = 0.f;
+#pragma unroll
+            for (int w = 0; w < NW; ++w) sum += part[w * 128 + c];
+            mean_s[c] = sum / (float)n;
+        }
+        bar_sync(1, NT);
         const float4 m4 = *reinterpret_cast<const float4*>(mean_s + c4);
         acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 8
-        for (int r = warp; r < n; r += 4) {
+#pragma unroll 4
+        for (int r = warp; r < n; r += NW) {
             const float4 v = *reinterpret_cast<const float4*>(st + r * kStage + c4);
             const float dx = v.x - m4.x, dy = v.y - m4.y, dz = v.z - m4.z, dw = v.w - m4.w;
             acc = make_float4(fmaf(dx, dx, acc.x), fmaf(dy, dy, acc.y), fmaf(dz, dz, acc.z), fmaf(dw, dw, acc.w));
         }
-        *reinterpret_cast<float4*>(part + 512 + warp * 128 + c4) = acc;
-        bar_sync(1, 128);
-        const float sq = (part[512 + c] + part[640 + c]) + (part[768 + c] + part[896 + c]);
-        rstd_s[c] = rsqrtf(sq / (float)n + eps);
+        *reinterpret_cast<float4*>(part + (NW + warp) * 128 + c4) = acc;
+        bar_sync(1, NT);
+        if (c < 128) {
+            float sq = 0.f;
+#pragma unroll
+            for (int w = 0; w < NW; ++w) sq += part[(NW + w) * 128 + c];
+            rstd_s[c] = rsqrtf(sq / (float)n + eps);
+        }
     }
-    bar_sync(1, 128);
-    for (int idx = threadIdx.x; idx < n * 32; idx += 128) {
+    bar_sync(1, NT);
+    for (int idx = threadIdx.x; idx < n * 32; idx += NT) {
         const int r = idx >> 5, c4 = (idx & 31) * 4;
         const float4 xv = *reinterpret_cast<const float4*>(st + r * kStage + c4);
         const float4 g = *reinterpret_cast<const float4*>(gamma + c4);
@@ -319,15 +342,14 @@ __global__ void __launch_bounds__(kThreads, 1)
                         const int t = kb * nN + nb, buf = t & 1;
                         if (t == 0 && !tile0_in_flight) {
                             mbar_expect_tx(&s->tma_bar[0], kTile);
-                            bulk_g2s(wsm, Wp, kTile, &s->tma_bar[0]);
+                            bulk_tile(wsm, Wp, &s->tma_bar[0]);
                         }
                         if (t + 1 < T) {   // next W tile into the other buffer once its previous reader (tile t-1) is done
                             if (t >= 1) {
                                 mbar_wait(&s->mma_bar[buf ^ 1], ((buf ? n_mma0 : n_mma1) - 1u) & 1u);
                             }
                             mbar_expect_tx(&s->tma_bar[buf ^ 1], kTile);
-                            bulk_g2s(wsm + (size_t)(buf ^ 1) * kTile, Wp + (size_t)(t + 1) * kTile, kTile,
-                                     &s->tma_bar[buf ^ 1]);
+                            bulk_tile(wsm + (size_t)(buf ^ 1) * kTile, Wp + (size_t)(t + 1) * kTile, &s->tma_bar[buf ^ 1]);
                         }
                         mbar_wait(&s->tma_bar[buf], (buf ? n_tma1 : n_tma0) & 1u);
                         tc_fence_after();
@@ -355,7 +377,7 @@ __global__ void __launch_bounds__(kThreads, 1)
                     tile0_in_flight = bn < B;
                     if (tile0_in_flight) {
                         mbar_expect_tx(&s->tma_bar[0], kTile);
-                        bulk_g2s(wsm, Wp, kTile, &s->tma_bar[0]);
+                        bulk_tile(wsm, Wp, &s->tma_bar[0]);
                     }
                 }
                 __syncwarp();
@@ -408,7 +430,7 @@ __global__ void __launch_bounds__(kThreads, 1)
                 __syncwarp();
             }
         } else if (!producer) {
-            epilogue_res_norm<EPI>(lane_base, wsm, s->part[0], s->mean, s->rstd, bias, R + b * (int64_t)n * 128, gamma, beta,
+            epilogue_res_norm<EPI, 128>(lane_base, wsm, s->part[0], s->mean, s->rstd, bias, R + b * (int64_t)n * 128, gamma, beta,
                                    eps, Y + b * (int64_t)n * 128, n);
         }
         ENC_STAMP(2);
@@ -442,7 +464,7 @@ struct FfnSmem {
     uint32_t pad_;
     alignas(16) float mean[kRows];
     alignas(16) float rstd[kRows];
-    alignas(16) float part[2][4 * kRows];
+    alignas(16) float part[2][16 * kRows];
 };
 constexpr size_t kFfnSmemBytes = kOffS + sizeof(FfnSmem);
 
@@ -501,6 +523,15 @@ __global__ void __launch_bounds__(kThreads, 1)
     uint32_t n_tma[2] = {0, 0}, n_wfree[2] = {0, 0}, n_full[2] = {0, 0}, n_free[2] = {0, 0};
     uint32_t n_aready = 0, n_afree = 0, n_done = 0;
     bool have_prev_m2 = false;     // epilogue warps: an earlier M2 (this or the previous instance) read the A operand
+#ifdef R4_ENC_PROF
+    // g_enc_prof: [0] issuer: wait W tile, [1] wait acc_free, [2] wait a_ready, [3] wait wfree, [4] issue, [5] tail waits,
+    // [6] wait done (all threads, thread 0), [7] final epilogue + conversion, [8] epilogue warps: wait acc_full,
+    // [9] wait a_free, [10] drain/convert/store
+    long long tp = clock64();
+#define FFN_STAMP(k) do { if (blockIdx.x == 0) { const long long now__ = clock64(); g_enc_prof[k] += now__ - tp; tp = now__; } } while (0)
+#else
+#define FFN_STAMP(k) do { } while (0)
+#endif
 
     if (producer && (int64_t)blockIdx.x < B) convert_x(X + (int64_t)blockIdx.x * n * 128, n, 128, 0, xs);
     fence_proxy_async();
@@ -515,12 +546,16 @@ __global__ void __launch_bounds__(kThreads, 1)
                     if (sq == nSeq - 1) return W2p + (size_t)(nH - 1) * kTile;
                     return (sq & 1) ? W1p + (size_t)((sq + 1) >> 1) * kTile : W2p + (size_t)((sq >> 1) - 1) * kTile;
                 };
-                mbar_expect_tx(&s->tma_bar[0], kTile);
-                bulk_g2s(wsm, tile_src(0), kTile, &s->tma_bar[0]);
+                if (b == (int64_t)blockIdx.x) {               // later instances: requested at the end of the previous one
+                    mbar_expect_tx(&s->tma_bar[0], kTile);
+                    bulk_tile(wsm, tile_src(0), &s->tma_bar[0]);
+                }
+                FFN_STAMP(4);
                 for (int sq = 0; sq < nSeq; ++sq) {
                     const int buf = sq & 1;
                     mbar_wait(&s->tma_bar[buf], n_tma[buf] & 1u);
                     ++n_tma[buf];
+                    FFN_STAMP(0);
                     const bool is_m1 = (sq == 0) || ((sq & 1) && sq != nSeq - 1);
                     if (is_m1) {
                         const int k = (sq == 0) ? 0 : (sq + 1) >> 1;
@@ -528,6 +563,7 @@ __global__ void __launch_bounds__(kThreads, 1)
                             mbar_wait(&s->acc_free[k & 1], n_free[k & 1] & 1u);
                             ++n_free[k & 1];
                         }
+                        FFN_STAMP(1);
                         tc_fence_after();
                         issue_tile(tmem, (uint32_t)(k & 1) * 128u, xs_a, ws_a + (uint32_t)buf * kTile, true);
                         tc_commit(&s->acc_full[k & 1]);
@@ -535,11 +571,13 @@ __global__ void __launch_bounds__(kThreads, 1)
                         const int k = (sq == nSeq - 1) ? nH - 1 : (sq >> 1) - 1;
                         mbar_wait(&s->a_ready, n_aready & 1u);
                         ++n_aready;
+                        FFN_STAMP(2);
                         tc_fence_after();
                         issue_tile_ts(tmem + kColOut, tmem + kColA, tmem + kColA + 64u, ws_a + (uint32_t)buf * kTile, k == 0);
                         tc_commit(&s->a_free);
                     }
                     tc_commit(sq + 1 < nSeq ? &s->wfree_bar[buf] : &s->done_bar);
+                    FFN_STAMP(4);
                     // the next tile goes into the other buffer once ITS previous reader (position sq-1, queued ahead of
                     // the MMAs just issued) is complete; the copy then runs under the MMAs of position sq
                     if (sq + 1 < nSeq) {
@@ -547,8 +585,9 @@ __global__ void __launch_bounds__(kThreads, 1)
                             mbar_wait(&s->wfree_bar[buf ^ 1], n_wfree[buf ^ 1] & 1u);
                             ++n_wfree[buf ^ 1];
                         }
+                        FFN_STAMP(3);
                         mbar_expect_tx(&s->tma_bar[buf ^ 1], kTile);
-                        bulk_g2s(wsm + (size_t)(buf ^ 1) * kTile, tile_src(sq + 1), kTile, &s->tma_bar[buf ^ 1]);
+                        bulk_tile(wsm + (size_t)(buf ^ 1) * kTile, tile_src(sq + 1), &s->tma_bar[buf ^ 1]);
                     }
                 }
                 // the buffer commits nobody waited for, and the last two drains: keep waits == arrivals per barrier
@@ -559,6 +598,7 @@ __global__ void __launch_bounds__(kThreads, 1)
                     mbar_wait(&s->acc_free[k & 1], n_free[k & 1] & 1u);
                     ++n_free[k & 1];
                 }
+                FFN_STAMP(5);
             }
             __syncwarp();
         } else if (!producer) {
@@ -566,11 +606,13 @@ __global__ void __launch_bounds__(kThreads, 1)
             for (int k = 0; k < nH; ++k) {
                 mbar_wait(&s->acc_full[k & 1], n_full[k & 1] & 1u);
                 ++n_full[k & 1];
+                if (threadIdx.x == 0) { FFN_STAMP(8); }
                 if (have_prev_m2) {               // the M2 of the previous block has finished reading the A operand
                     mbar_wait(&s->a_free, n_afree & 1u);
                     ++n_afree;
                 }
                 have_prev_m2 = true;
+                if (threadIdx.x == 0) { FFN_STAMP(9); }
                 tc_fence_after();
                 const uint32_t src = lane_base + (uint32_t)(k & 1) * 128u;
 #pragma unroll 2
@@ -596,22 +638,40 @@ __global__ void __launch_bounds__(kThreads, 1)
                 tc_wait_st();
                 tc_fence_before();
                 mbar_arrive(&s->a_ready);
+                if (threadIdx.x == 0) { FFN_STAMP(10); }
             }
         }
         mbar_wait(&s->done_bar, n_done & 1u);
         ++n_done;
         tc_fence_after();
-        if (producer) {
-            // A tile of the next instance while the epilogue warps run the norm (all MMAs reading xs are complete)
-            const int64_t bn = b + gridDim.x;
-            if (bn < B) convert_x(X + bn * (int64_t)n * 128, n, 128, 0, xs);
-            fence_proxy_async();
-        } else {
-            epilogue_res_norm<EPI>(lane_base + kColOut, wsm, s->part[0], s->mean, s->rstd, b2, X + b * (int64_t)n * 128,
-                                   gamma, beta, eps, Y + b * (int64_t)n * 128, n);
-        }
+#ifdef R4_ENC_PROF
+        if (threadIdx.x == 0 || threadIdx.x == 128) tp = clock64();
+#endif
+        // residual + norm by all eight warps, then the next instance's A tile by all eight (every MMA reading xs is done);
+        // the first W tile of the next instance is requested first so that its flight covers the conversion
+        epilogue_res_norm<EPI, kThreads>(lane_base + kColOut, wsm, s->part[0], s->mean, s->rstd, b2,
+                                         X + b * (int64_t)n * 128, gamma, beta, eps, Y + b * (int64_t)n * 128, n);
         tc_fence_before();
         __syncthreads();
+        const int64_t bn = b + gridDim.x;
+        if (bn < B) {
+            if (warp == 4) {
+                if (elect_one()) {
+                    mbar_expect_tx(&s->tma_bar[0], kTile);
+                    bulk_tile(wsm, W1p, &s->tma_bar[0]);
+                }
+                __syncwarp();
+            }
+            float4 xa[8], xb[8];
+            load_x8(X + bn * (int64_t)n * 128, n, 128, 0, xa, xb);
+            store_x8(xa, xb, xs);
+            fence_proxy_async();
+        }
+        __syncthreads();
+#ifdef R4_ENC_PROF
+        if (threadIdx.x == 0) { FFN_STAMP(7); }
+        if (threadIdx.x == 128 && blockIdx.x == 0) tp = clock64();
+#endif
     }
     if (warp == 0) tmem_dealloc(tmem, 512);
 }
@@ -945,7 +1005,7 @@ struct BlockSmem {
     uint32_t pad_;
     alignas(16) float mean[kRows];
     alignas(16) float rstd[kRows];
-    alignas(16) float part[2][4 * kRows];
+    alignas(16) float part[2][16 * kRows];
 };
 constexpr size_t kBlockSmemBytes = 3 * kTile + sizeof(BlockSmem);
 
@@ -1022,9 +1082,9 @@ __global__ void __launch_bounds__(kAT, 1)
         if (warp == 4) {
             if (elect_one()) {
                 mbar_expect_tx(&s->wq_bar, kTile);
-                bulk_g2s(r1, Wqkvp, kTile, &s->wq_bar);
+                bulk_tile(r1, Wqkvp, &s->wq_bar);
                 mbar_expect_tx(&s->wk_bar, kTile);
-                bulk_g2s(r2, Wqkvp + kTile, kTile, &s->wk_bar);
+                bulk_tile(r2, Wqkvp + kTile, &s->wk_bar);
             }
             __syncwarp();
         }
@@ -1062,7 +1122,7 @@ __global__ void __launch_bounds__(kAT, 1)
                 issue_tile(tmem, 128u, r0_a, r2_a, true);          // K = X Wk^T
                 mbar_wait(&s->r1free_bar, ph);                     // the Q product has finished reading Wq
                 mbar_expect_tx(&s->wv_bar, kTile);
-                bulk_g2s(r1, Wqkvp + 2 * (size_t)kTile, kTile, &s->wv_bar);
+                bulk_tile(r1, Wqkvp + 2 * (size_t)kTile, &s->wv_bar);
                 mbar_wait(&s->wv_bar, ph);
                 tc_fence_after();
                 issue_tile(tmem, 256u, r1_a, r0_a, true);          // V^T = Wv X^T (operand roles swapped)
@@ -1109,7 +1169,7 @@ __global__ void __launch_bounds__(kAT, 1)
                 if (elect_one()) {
                     fence_proxy_async();
                     mbar_expect_tx(&s->wo_bar, kTile);
-                    bulk_g2s(r0, Wop, kTile, &s->wo_bar);
+                    bulk_tile(r0, Wop, &s->wo_bar);
                 }
                 __syncwarp();
             }
@@ -1209,9 +1269,8 @@ __global__ void __launch_bounds__(kAT, 1)
         mbar_wait(&s->out_bar, ph);
         ph ^= 1u;
         tc_fence_after();
-        if (warp < 4)
-            epilogue_res_norm<EPI>(lane_base + 128u, r1, s->part[0], s->mean, s->rstd, bo, X + b * (int64_t)n * 128, gamma,
-                                   beta, eps, Y + b * (int64_t)n * 128, n);
+        epilogue_res_norm<EPI, kAT>(lane_base + 128u, r1, s->part[0], s->mean, s->rstd, bo, X + b * (int64_t)n * 128, gamma,
+                                    beta, eps, Y + b * (int64_t)n * 128, n);
         tc_fence_before();
         __syncthreads();
     }
