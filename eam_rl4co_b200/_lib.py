@@ -32,7 +32,7 @@ ABI_VERSION = 3
 EXPORTS = [
     "rl4co_b200_abi_version", "rl4co_last_error", "rl4co_tsp_step", "rl4co_cvrp_step_mask",
     "rl4co_cvrp_action_mask", "rl4co_tour_reward", "rl4co_select", "rl4co_decode_step",
-    "rl4co_rollout", "rl4co_noise_gumbel", "rl4co_tc_image_bytes", "rl4co_tc_pack", "rl4co_tc_decode_step",
+    "rl4co_rollout", "rl4co_rollout_noalloc", "rl4co_noalloc_max_instances", "rl4co_noise_gumbel", "rl4co_tc_image_bytes", "rl4co_tc_pack", "rl4co_tc_decode_step",
     "rl4co_enc_packed_bytes", "rl4co_enc_pack_weight", "rl4co_enc_linear", "rl4co_enc_ffn", "rl4co_enc_attn_block", "rl4co_enc_attention", "rl4co_best_of_starts", "rl4co_generate_instances", "rl4co_replay_states",
 ]
 
@@ -88,6 +88,7 @@ def lib():
         for name in EXPORTS:
             getattr(L, name)  # fail loudly on a missing symbol
         L.rl4co_tc_image_bytes.restype = C.c_int64
+        L.rl4co_noalloc_max_instances.restype = C.c_int64
         L.rl4co_enc_packed_bytes.restype = C.c_int64
         if L.rl4co_b200_abi_version() != ABI_VERSION:
             raise RuntimeError("librl4co_b200.so ABI version mismatch")

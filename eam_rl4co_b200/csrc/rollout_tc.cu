@@ -18,6 +18,8 @@
 // Shared memory: the six static operand tiles of the instance (K, L, V^T; hi and lo), brought in
 // once per instance by TMA bulk copies from an image built by tc_pack_kernel, stay resident for
 // all T steps; the per-step Q tile (64 channels = 4 heads at a time) is rebuilt by the CUDA cores.
+#include <mutex>
+
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
@@ -1299,4 +1301,87 @@ extern "C" int rl4co_tc_decode_step(int32_t env, const rl4co_cache* cache, const
     }
     R4_CHECK_LAUNCH("tc_decode_step");
     return RL4CO_OK;
+}
+
+// ---- allocation-free variant of the tensor-path rollout ---------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  The only scratch the
+// tensor-path rollout needs beyond the caller's inputs / outputs is the fp16 hi/lo operand image of the instances
+// (rl4co_tc_pack's output, 6 * npad * 256 B per instance).  Here it lives in a file-scope device array of
+// RL4CO_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit.  In HOST code `g_noalloc_scratch` is
+// only a stand-in for the symbol, not a device address: its address is resolved once per device, with that device
+// current, by cudaGetSymbolAddress, and that pointer is what the kernels receive.
+// The pack kernel rewrites every byte of the image it uses (real rows and zero padding alike), so nothing has to be
+// cleared between calls; all calls share the array, so calls that overlap on the GPU (different streams) race.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[RL4CO_NOALLOC_SCRATCH_BYTES];
+
+namespace r4 {
+static int noalloc_scratch_ptr(unsigned char** out) {
+    constexpr int kMaxDev = 64;
+    static unsigned char* ptrs[kMaxDev] = {nullptr};
+    static std::mutex mu;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDev) {
+        set_error("rollout_noalloc: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+        return RL4CO_E_LAUNCH;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (ptrs[dev] == nullptr) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_noalloc_scratch);     // device `dev` is current
+        if (e != cudaSuccess || p == nullptr) {
+            set_error("rollout_noalloc: cudaGetSymbolAddress(scratch) on device %d: %s", dev, cudaGetErrorString(e));
+            return RL4CO_E_LAUNCH;
+        }
+        ptrs[dev] = static_cast<unsigned char*>(p);
+    }
+    *out = ptrs[dev];
+    return RL4CO_OK;
+}
+}  // namespace r4
+
+extern "C" int64_t rl4co_noalloc_max_instances(int32_t n_nodes) {
+    const int64_t per = rl4co_tc_image_bytes(n_nodes);
+    return per > 0 ? (int64_t)RL4CO_NOALLOC_SCRATCH_BYTES / per : 0;
+}
+
+extern "C" int rl4co_rollout_noalloc(const rl4co_cache* cache, const rl4co_rollout_args* args, void* stream) {
+    R4_CHECK_ARG(args != nullptr, "rollout_noalloc: null args");
+    const int env = args->env;
+    R4_CHECK_ARG(env == RL4CO_ENV_TSP || env == RL4CO_ENV_CVRP, "rollout_noalloc: bad env %d", env);
+    int rc = check_cache(cache, env, "rollout_noalloc");
+    if (rc) return rc;
+    R4_CHECK_ARG(args->mode >= 0 && args->mode <= 2, "rollout_noalloc: bad mode %d", args->mode);
+    R4_CHECK_ARG(args->max_steps > 0 && args->temperature > 0.f, "rollout_noalloc: bad max_steps / temperature");
+    R4_CHECK_ARG(args->locs && args->actions && args->logp && args->reward && args->log_likelihood && args->lengths &&
+                     args->max_len && args->err, "rollout_noalloc: null output/input pointer");
+    if (env == RL4CO_ENV_CVRP)
+        R4_CHECK_ARG(args->demand && args->vehicle_capacity, "rollout_noalloc: CVRP needs demand/capacity");
+    if (args->mode == RL4CO_MODE_EVALUATE)
+        R4_CHECK_ARG(args->actions_in && args->actions_in_T > 0 && args->actions_in_stride >= args->actions_in_T,
+                     "rollout_noalloc: evaluate needs actions_in");
+    const int S = args->num_starts;
+    const int64_t per = rl4co_tc_image_bytes(cache->n_nodes);
+    R4_CHECK_ARG(per > 0 && S >= 8 && S <= tc::kRows,
+                 "rollout_noalloc: tensor-path shapes only (8 <= num_starts=%d <= 128, n_nodes=%d <= %d)", S,
+                 cache->n_nodes, tc::kMaxNPad);
+    const int max_starts = (env == RL4CO_ENV_TSP) ? cache->n_nodes : cache->n_nodes - 1;
+    R4_CHECK_ARG(args->mode == RL4CO_MODE_EVALUATE || S <= max_starts, "rollout_noalloc: num_starts=%d > %d start nodes",
+                 S, max_starts);
+    R4_CHECK_ARG(cache->B * per <= (int64_t)RL4CO_NOALLOC_SCRATCH_BYTES,
+                 "rollout_noalloc: %lld instances x %lld B of operand image exceed the static scratch of %lld B "
+                 "(at most %lld instances at n_nodes=%d); use rl4co_tc_pack + rl4co_rollout with a caller-owned image",
+                 (long long)cache->B, (long long)per, (long long)RL4CO_NOALLOC_SCRATCH_BYTES,
+                 (long long)((int64_t)RL4CO_NOALLOC_SCRATCH_BYTES / per), cache->n_nodes);
+    unsigned char* scratch = nullptr;
+    if ((rc = noalloc_scratch_ptr(&scratch))) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    rl4co_cache c = *cache;
+    c.tc_img = scratch;                                      // any caller-supplied image is ignored
+    tc::tc_pack_kernel<<<(unsigned)c.B, 256, 0, st>>>(c, scratch, tc::npad_of(c.n_nodes), args->err);
+    R4_CHECK_LAUNCH("rollout_noalloc (operand pack)");
+    rl4co_rollout_args a = *args;
+    a.impl = RL4CO_IMPL_TC;
+    return launch_rollout_tc(&c, a, st);
 }

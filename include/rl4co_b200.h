@@ -192,6 +192,19 @@ typedef struct rl4co_rollout_args {
 
 int rl4co_rollout(const rl4co_cache* cache, const rl4co_rollout_args* args, void* stream);
 
+/* ---- Allocation-free rollout.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * Same contract and results as rl4co_rollout on the tensor path (8 <= num_starts <= 128, n_nodes <= 112), but the
+ * fp16 operand image that rl4co_tc_pack would write into caller memory (cache->tc_img, ignored here) is packed into a
+ * static device array of RL4CO_NOALLOC_SCRATCH_BYTES inside the library: the call allocates and frees nothing.
+ * Limit: B * rl4co_tc_image_bytes(n_nodes) <= RL4CO_NOALLOC_SCRATCH_BYTES (rl4co_noalloc_max_instances: 48 instances
+ * at n_nodes = 100, 170 at 20); larger batches return RL4CO_E_ARG.  The pack's fp16-range flag is raised in args->err.
+ * Every call on a device shares the one array (fully rewritten by each call): calls that overlap on the GPU race -
+ * serialise them on one stream.                                                                                      */
+#define RL4CO_NOALLOC_SCRATCH_BYTES (8u << 20)
+int64_t rl4co_noalloc_max_instances(int32_t n_nodes);
+int rl4co_rollout_noalloc(const rl4co_cache* cache, const rl4co_rollout_args* args, void* stream);
+
 /* ---- Tensor-core (tcgen05/TMEM) path for multistart rows: S = rows/B starts of an instance form the
  * M dimension of the MMAs (8 <= S <= 128, n_nodes <= 112).  Same arithmetic as above with every fp32
  * operand split into fp16 hi + lo and three MMAs per product (fp32 accumulate).                      */
