@@ -26,13 +26,14 @@ ERR_MESSAGES = [  # (bit, reference assertion text); first match is raised
     (32, "Exceeded maximum number of steps during decoding"),
 ]
 IMPL_AUTO, IMPL_FP32, IMPL_TC, IMPL_STREAM, IMPL_COOP = 0, 1, 2, 3, 4
+TC_LAYOUT_RESIDENT, TC_LAYOUT_STREAM = 0, 1
 ENC_EPI_PLAIN, ENC_EPI_RELU, ENC_EPI_RES_NORM, ENC_EPI_RES_AFFINE = 0, 1, 2, 3
 ABI_VERSION = 3
 
 EXPORTS = [
     "rl4co_b200_abi_version", "rl4co_last_error", "rl4co_tsp_step", "rl4co_cvrp_step_mask",
     "rl4co_cvrp_action_mask", "rl4co_tour_reward", "rl4co_select", "rl4co_decode_step",
-    "rl4co_rollout", "rl4co_rollout_noalloc", "rl4co_noalloc_max_instances", "rl4co_noise_gumbel", "rl4co_tc_image_bytes", "rl4co_tc_pack", "rl4co_tc_decode_step",
+    "rl4co_rollout", "rl4co_rollout_noalloc", "rl4co_noalloc_max_instances", "rl4co_noise_gumbel", "rl4co_tc_image_bytes", "rl4co_tc_preferred_layout", "rl4co_tc_pack", "rl4co_tc_decode_step",
     "rl4co_enc_packed_bytes", "rl4co_enc_pack_weight", "rl4co_enc_linear", "rl4co_enc_ffn", "rl4co_enc_attn_block", "rl4co_enc_attention", "rl4co_best_of_starts", "rl4co_generate_instances", "rl4co_replay_states",
 ]
 
@@ -58,7 +59,7 @@ class Cache(C.Structure):
     _fields_ = [("gk", C.c_void_p), ("gv", C.c_void_p), ("lk", C.c_void_p), ("pa", C.c_void_p),
                 ("pb", C.c_void_p), ("q0", C.c_void_p), ("wcap", C.c_void_p), ("tc_img", C.c_void_p),
                 ("B", C.c_int64),
-                ("n_nodes", C.c_int32), ("embed_dim", C.c_int32), ("num_heads", C.c_int32)]
+                ("n_nodes", C.c_int32), ("embed_dim", C.c_int32), ("num_heads", C.c_int32), ("tc_layout", C.c_int32)]
 
 
 class RolloutArgs(C.Structure):

@@ -182,8 +182,8 @@ __global__ void __launch_bounds__(256) tc_pack_kernel(rl4co_cache c, unsigned ch
 // pb[cur]) / :70-74,155-157 (CVRP, pb[cur] + (cap - used) * wcap), split to fp16 hi/lo.  Warp q covers rows
 // [32q, 32q+32) in four passes of 8 rows; four lanes read the 64 contiguous bytes of a row (whole sectors).
 // Rows >= S are written as zeros.
-template <int ENV>
-__device__ __forceinline__ void build_q(const Ctx& x, const rl4co_cache& c, int64_t b, int S, int h, int team,
+template <int ENV, class CX>
+__device__ __forceinline__ void build_q(const CX& x, const rl4co_cache& c, int64_t b, int S, int h, int team,
                                         int q, int lane) {
     const int64_t base = b * (int64_t)c.n_nodes;
     const int pc = lane & 3;                           // 4-channel piece of the head's 16 channels
@@ -409,7 +409,8 @@ __device__ __forceinline__ void softmax_chunk(uint32_t sp, int ch, const uint32_
 // spec = false: exact online form, returns rowsum(P) and the reference m_out it is relative to.
 // spec = true : P = exp(S - ref) against the caller's reference (ref * log2e in refl2); the caller checks the
 //               returned row sum and falls back to the exact form when it left the safe window.
-__device__ __forceinline__ float softmax_inplace(const Ctx& x, uint32_t sp, int row, float* dbg_scores, int n,
+template <class CX>
+__device__ __forceinline__ float softmax_inplace(const CX& x, uint32_t sp, int row, float* dbg_scores, int n,
                                                  bool spec, float refl2, float& m_out) {
     const uint32_t w0 = x.s()->maskw[0][row], w1 = x.s()->maskw[1][row], w2 = x.s()->maskw[2][row],
                    w3 = x.s()->maskw[3][row];
@@ -1194,6 +1195,8 @@ __global__ void __launch_bounds__(kThreads, 1)
     if (warp == 0) tmem_dealloc(x.tmem, kTmemCols);
 }
 
+#include "rollout_tc2.cuh"
+
 }  // namespace tc
 
 // ---- host-side launchers ---------------------------------------------------------------------------------
@@ -1221,7 +1224,43 @@ static unsigned tc_grid(int64_t B) {
     return (unsigned)(B < sms ? B : sms);
 }
 
+// streaming kernel (operand image v2): two CTAs per SM
+static int launch_rollout_tc2(const rl4co_cache* cache, const rl4co_rollout_args& a, cudaStream_t st) {
+    const int npad = tc::npad_of(cache->n_nodes);
+    const size_t smem = tc::t2::smem_bytes2(npad);
+    const unsigned char* img = reinterpret_cast<const unsigned char*>(cache->tc_img);
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const unsigned grid = (unsigned)(cache->B < 2 * sms ? cache->B : 2 * sms);
+#define R4_LAUNCH_TC2(ENV_, MODE_)                                                                                  \
+    do {                                                                                                            \
+        auto kern = tc::t2::rollout_tc2_kernel<ENV_, MODE_>;                                                        \
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);         \
+        if (e != cudaSuccess) {                                                                                     \
+            set_error("rollout_tc2: cudaFuncSetAttribute(%zu B smem): %s", smem, cudaGetErrorString(e));            \
+            return RL4CO_E_LAUNCH;                                                                                  \
+        }                                                                                                           \
+        kern<<<grid, tc::t2::kThreads2, smem, st>>>(*cache, a, img, npad);                                          \
+    } while (0)
+    const bool tsp = a.env == RL4CO_ENV_TSP;
+    if (a.mode == RL4CO_MODE_GREEDY) {
+        if (tsp) R4_LAUNCH_TC2(RL4CO_ENV_TSP, RL4CO_MODE_GREEDY);
+        else R4_LAUNCH_TC2(RL4CO_ENV_CVRP, RL4CO_MODE_GREEDY);
+    } else if (a.mode == RL4CO_MODE_SAMPLING) {
+        if (tsp) R4_LAUNCH_TC2(RL4CO_ENV_TSP, RL4CO_MODE_SAMPLING);
+        else R4_LAUNCH_TC2(RL4CO_ENV_CVRP, RL4CO_MODE_SAMPLING);
+    } else {
+        if (tsp) R4_LAUNCH_TC2(RL4CO_ENV_TSP, RL4CO_MODE_EVALUATE);
+        else R4_LAUNCH_TC2(RL4CO_ENV_CVRP, RL4CO_MODE_EVALUATE);
+    }
+#undef R4_LAUNCH_TC2
+    R4_CHECK_LAUNCH("rollout_tc2");
+    return RL4CO_OK;
+}
+
 int launch_rollout_tc(const rl4co_cache* cache, const rl4co_rollout_args& a, cudaStream_t st) {
+    if (cache->tc_layout == RL4CO_TC_LAYOUT_STREAM) return launch_rollout_tc2(cache, a, st);
     const int npad = tc::npad_of(cache->n_nodes);
     const size_t smem = tc::smem_bytes(npad);
     const unsigned char* img = reinterpret_cast<const unsigned char*>(cache->tc_img);
@@ -1256,11 +1295,25 @@ extern "C" int64_t rl4co_tc_image_bytes(int32_t n_nodes) {
     return 6ll * tc::tile_bytes(tc::npad_of(n_nodes));
 }
 
+extern "C" int32_t rl4co_tc_preferred_layout(int64_t B) {
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // two instances per SM only pay when there is more than one instance per SM to run
+    return B > sms ? RL4CO_TC_LAYOUT_STREAM : RL4CO_TC_LAYOUT_RESIDENT;
+}
+
 extern "C" int rl4co_tc_pack(const rl4co_cache* cache, void* image, int32_t* err, void* stream) {
     R4_CHECK_ARG(cache && cache->gk && cache->gv && cache->lk && cache->B > 0 && image && err, "tc_pack: null pointer");
     R4_CHECK_ARG(cache->embed_dim == kE && cache->num_heads == kH, "tc_pack: only embed_dim=128, num_heads=8");
     R4_CHECK_ARG(rl4co_tc_image_bytes(cache->n_nodes) > 0, "tc_pack: n_nodes=%d outside the tensor path (<= %d)",
                  cache->n_nodes, tc::kMaxNPad);
+    R4_CHECK_ARG(cache->tc_layout == RL4CO_TC_LAYOUT_RESIDENT || cache->tc_layout == RL4CO_TC_LAYOUT_STREAM,
+                 "tc_pack: unknown tc_layout %d", cache->tc_layout);
+    if (cache->tc_layout == RL4CO_TC_LAYOUT_STREAM)
+        tc::t2::tc2_pack_kernel<<<(unsigned)cache->B, 256, 0, (cudaStream_t)stream>>>(
+            *cache, reinterpret_cast<unsigned char*>(image), tc::npad_of(cache->n_nodes), err);
+    else
     tc::tc_pack_kernel<<<(unsigned)cache->B, 256, 0, (cudaStream_t)stream>>>(
         *cache, reinterpret_cast<unsigned char*>(image), tc::npad_of(cache->n_nodes), err);
     R4_CHECK_LAUNCH("tc_pack");
@@ -1282,6 +1335,7 @@ extern "C" int rl4co_tc_decode_step(int32_t env, const rl4co_cache* cache, const
     R4_CHECK_ARG(tc_supported(cache, S), "tc_decode_step: needs tc_img, 8 <= S=%d <= 128, n_nodes=%d <= %d", S,
                  cache->n_nodes, tc::kMaxNPad);
     R4_CHECK_ARG(current_node && mask && logits_out && err, "tc_decode_step: null pointer");
+    R4_CHECK_ARG(cache->tc_layout == RL4CO_TC_LAYOUT_RESIDENT, "tc_decode_step: needs the resident operand image (tc_layout 0)");
     if (env == RL4CO_ENV_TSP) R4_CHECK_ARG(first_node, "tc_decode_step: TSP needs first_node");
     if (env == RL4CO_ENV_CVRP) R4_CHECK_ARG(used_capacity && vehicle_capacity, "tc_decode_step: CVRP needs capacities");
     const int npad = tc::npad_of(cache->n_nodes);
@@ -1379,6 +1433,7 @@ extern "C" int rl4co_rollout_noalloc(const rl4co_cache* cache, const rl4co_rollo
     cudaStream_t st = (cudaStream_t)stream;
     rl4co_cache c = *cache;
     c.tc_img = scratch;                                      // any caller-supplied image is ignored
+    c.tc_layout = RL4CO_TC_LAYOUT_RESIDENT;
     tc::tc_pack_kernel<<<(unsigned)c.B, 256, 0, st>>>(c, scratch, tc::npad_of(c.n_nodes), args->err);
     R4_CHECK_LAUNCH("rollout_noalloc (operand pack)");
     rl4co_rollout_args a = *args;

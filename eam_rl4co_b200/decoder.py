@@ -59,6 +59,7 @@ class PrecomputedCache:
     _logit_key_w: Optional[torch.Tensor] = None
     tc_img: Optional[torch.Tensor] = None   # [B, rl4co_tc_image_bytes(n)] uint8: tcgen05 operand tiles
     tc_err: Optional[torch.Tensor] = None
+    tc_layout: int = 0                      # _lib.TC_LAYOUT_*: resident tiles / head-sliced for the streaming kernel
 
     @property
     def logit_key(self):
@@ -68,7 +69,7 @@ class PrecomputedCache:
         B, n, E = self.node_embeddings.shape
         p = lambda t: (t.data_ptr() if t is not None else None)
         return _lib.Cache(p(self.glimpse_key), p(self.glimpse_val), p(self.logit_key_folded), p(self.pa),
-                          p(self.pb), p(self.q0), p(self.wcap), p(self.tc_img), B, n, E, 8)
+                          p(self.pb), p(self.q0), p(self.wcap), p(self.tc_img), B, n, E, 8, self.tc_layout)
 
 
 class AttentionModelDecoder(nn.Module):
@@ -90,6 +91,7 @@ class AttentionModelDecoder(nn.Module):
         self.use_graph_context = use_graph_context
         self.is_dynamic_embedding = False
         self.use_kernels = True        # cache precompute on the tcgen05 linear kernel (False: torch GEMM)
+        self.tc_layout = None          # None: by batch size; _lib.TC_LAYOUT_RESIDENT / _STREAM force a rollout kernel
         self._packer, self._zero_bias = None, None
 
     def pre_decoder_hook(self, td, env, embeddings, num_starts: int = 0):
@@ -129,7 +131,7 @@ class AttentionModelDecoder(nn.Module):
         cache = PrecomputedCache(h, gc, gk, gv, lkf, pa, pb, q0, wcap,
                                  _lib.ENV_TSP if tsp else _lib.ENV_CVRP, Wl)
         if h.is_cuda and 8 <= num_starts <= 128:
-            self._pack_tensor_tiles(cache)
+            self._pack_tensor_tiles(cache, self.tc_layout)
         return cache
 
     def _precompute_kernels(self, h, ws):
@@ -155,9 +157,11 @@ class AttentionModelDecoder(nn.Module):
         return super()._load_from_state_dict(*a, **kw)
 
     @staticmethod
-    def _pack_tensor_tiles(cache: PrecomputedCache) -> None:
-        """Operand image of the tcgen05 kernels (multistart rows): fp16 hi/lo tiles of K, L, V^T."""
+    def _pack_tensor_tiles(cache: PrecomputedCache, layout: Optional[int] = None) -> None:
+        """Operand image of the tcgen05 kernels (multistart rows): fp16 hi/lo tiles of K, L, V^T.  `layout` None: the
+        library's choice for this batch size (streaming kernel, two instances per SM, when B exceeds the SM count)."""
         B, n, _ = cache.node_embeddings.shape
+        cache.tc_layout = int(_lib.lib().rl4co_tc_preferred_layout(C.c_int64(B))) if layout is None else int(layout)
         nbytes = _lib.lib().rl4co_tc_image_bytes(C.c_int32(n))
         if nbytes <= 0:
             return                      # n_nodes beyond the tensor path: the fp32 kernels take the rows
@@ -181,7 +185,8 @@ class AttentionModelDecoder(nn.Module):
         err = _lib.new_err(dev)
         cs = cached.cstruct()
         cur = td["current_node"].contiguous()
-        use_tc = impl != _lib.IMPL_FP32 and cached.tc_img is not None and 8 <= rows // cs.B <= 128
+        use_tc = (impl != _lib.IMPL_FP32 and cached.tc_img is not None and 8 <= rows // cs.B <= 128
+                  and cached.tc_layout == _lib.TC_LAYOUT_RESIDENT)
         if impl == _lib.IMPL_TC and not use_tc:
             raise RuntimeError("tensor-core decode step needs multistart rows (8 <= S <= 128) and a packed cache")
         if use_tc:

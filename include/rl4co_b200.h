@@ -142,6 +142,7 @@ typedef struct rl4co_cache {
     int32_t n_nodes;
     int32_t embed_dim; /* must be 128 */
     int32_t num_heads; /* must be 8   */
+    int32_t tc_layout; /* layout of tc_img: RL4CO_TC_LAYOUT_* (occupies the struct's former tail padding) */
 } rl4co_cache;
 
 /* ---- AttentionModelDecoder.forward — am/decoder.py:161-198 (+ context.py, attention.py) --
@@ -209,6 +210,13 @@ int rl4co_rollout_noalloc(const rl4co_cache* cache, const rl4co_rollout_args* ar
  * M dimension of the MMAs (8 <= S <= 128, n_nodes <= 112).  Same arithmetic as above with every fp32
  * operand split into fp16 hi + lo and three MMAs per product (fp32 accumulate).                      */
 int64_t rl4co_tc_image_bytes(int32_t n_nodes); /* bytes per instance of cache->tc_img; 0 = unsupported */
+/* Two operand-image layouts (same size), selected by cache->tc_layout at pack time and read back by rl4co_rollout:
+ *   RESIDENT: six whole tiles; rollout_tc_kernel keeps them in shared memory (1 instance per SM, 512 threads);
+ *   STREAM  : head-sliced; rollout_tc2_kernel streams the slices from L2 with TMA (2 instances per SM, 256 threads each).
+ * rl4co_tc_preferred_layout(B): STREAM when the batch has more instances than the GPU has SMs.                      */
+#define RL4CO_TC_LAYOUT_RESIDENT 0
+#define RL4CO_TC_LAYOUT_STREAM 1
+int32_t rl4co_tc_preferred_layout(int64_t B);
 int rl4co_tc_pack(const rl4co_cache* cache, void* image, int32_t* err, void* stream);
 /* AttentionModelDecoder.forward (am/decoder.py:161-198) for multistart rows on the tensor path: RAW
  * logits [rows, n_nodes].  TSP callers must be past the first step (i >= 1, always true after the

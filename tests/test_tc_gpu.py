@@ -233,3 +233,35 @@ def test_tc_rollout_temperature(env_name, temperature):
         T = min(ref["actions"].shape[1], out["actions"].shape[1])
         same = (ref["actions"][:, :T] == out["actions"].cpu()[:, :T]).all(1).float().mean().item()
         assert same >= 0.9, (dt, temperature, same)
+
+
+@pytest.mark.parametrize("env_name", ["tsp", "cvrp"])
+@pytest.mark.parametrize("N,B", [(20, 9), (50, 5), (100, 3)])
+@pytest.mark.parametrize("decode_type", ["multistart_greedy", "multistart_sampling"])
+def test_streaming_kernel_matches_oracle_and_resident_kernel(env_name, N, B, decode_type):
+    """rollout_tc2_kernel (operand image v2 streamed from L2, two CTAs per SM; the default when B exceeds the SM count) forced
+    at a small batch: against the oracle (tie-aware) and against the resident kernel; then evaluate mode on its actions."""
+    import eam_rl4co_b200 as P
+    from helpers import compare_rollout, decoder_weights, inst_to_env_td
+    torch.manual_seed(31 + N)
+    inst = O.generate_tsp(B, N) if env_name == "tsp" else O.generate_cvrp(B, N)
+    torch.manual_seed(4321)
+    pol = P.POMOPolicy(env_name).eval()
+    w = decoder_weights(pol)
+    pol = pol.to("cuda")
+    env, td = inst_to_env_td(P, env_name, inst, "cuda")
+    with torch.no_grad():
+        h, _ = pol.encoder(td)
+    pol.decoder.tc_layout = _lib.TC_LAYOUT_STREAM
+    out = pol(td.clone(), env, decode_type=decode_type, noise_seed=5, impl=_lib.IMPL_TC)
+    st = compare_rollout(env_name, inst, h.cpu(), w, False, out, decode_type, noise_seed=5, min_exact=0.97)
+    ev = pol(td.clone(), env, actions=out["actions"], num_starts=N, impl=_lib.IMPL_TC)
+    assert rel_close(ev["log_likelihood"], out["log_likelihood"], 2e-6)
+    pol.decoder.tc_layout = _lib.TC_LAYOUT_RESIDENT
+    ref = pol(td.clone(), env, decode_type=decode_type, noise_seed=5, impl=_lib.IMPL_TC)
+    T = min(ref["actions"].shape[1], out["actions"].shape[1])
+    same = (ref["actions"][:, :T] == out["actions"][:, :T]).all(1)
+    assert same.float().mean().item() >= 0.97
+    assert rel_close(out["log_likelihood"][same], ref["log_likelihood"][same], 2e-6)
+    assert rel_close(out["reward"][same], ref["reward"][same], 1e-6)
+    print(f"{env_name}{N} {decode_type}: exact vs oracle {st['exact']:.4f}, identical to resident kernel {same.float().mean().item():.4f}")
