@@ -303,6 +303,7 @@ def run_b200(args):
         # keep stdout to the one JSON line: NCCL's version banner goes there at NCCL_DEBUG=VERSION
         if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
             os.environ["NCCL_DEBUG"] = "WARN"
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")    # the version banner is not part of the JSON line
         dist.init_process_group("nccl", device_id=dev)
     torch.backends.cuda.matmul.allow_tf32 = False
     torch.backends.cudnn.allow_tf32 = False
@@ -474,10 +475,12 @@ def run_b200(args):
                     "uncaptured_value": isteps_global * K / (e2e_eager_ms * 1e-3),
                     "includes": "H2D locs, env.reset, encoder (tcgen05 kernels), cache precompute, rollout kernel, "
                                 "D2H reward+log_likelihood+actions+error word, host check of the error word"},
-            "gpu_launches": 2 * len(kernel_ms),      # per step: r4::tc::tc_pack_kernel + r4::tc::rollout_tc_kernel
+            # per step: 5 x r4::enc::enc_linear_kernel (cache precompute) + operand pack kernel + the rollout kernel
+            "gpu_launches": 7 * len(kernel_ms),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": measured_traffic(), "peak_source": peak_src,
-                         "kernel": "r4::tc::rollout_tc_kernel<TSP, GREEDY>", "kernel_ms": k_ms,
+                         "kernel": ("r4::tc::t2::rollout_tc2_kernel<TSP, GREEDY> (streaming, 2 CTAs per SM)" if B > 148 else
+                                    "r4::tc::rollout_tc_kernel<TSP, GREEDY> (resident, 1 CTA per SM)"), "kernel_ms": k_ms,
                          "instances_per_launch": B,
                          "algorithmic_bytes_per_launch": ALGO_BYTES_PER_INSTANCE_STEP * isteps_local,
                          "note": "algorithmic bytes per SURVEY.md §8(d) (K,V,L re-read every step); the "

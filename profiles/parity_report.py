@@ -42,8 +42,11 @@ def main():
         with torch.no_grad():
             h, _ = pol.encoder(td)
         for dt in dts:
-            impls = [("tc", _lib.IMPL_TC), ("fp32", _lib.IMPL_FP32)] if pomo else [("fp32", _lib.IMPL_AUTO)]
-            for iname, impl in impls:
+            impls = ([("tc resident", _lib.IMPL_TC, _lib.TC_LAYOUT_RESIDENT), ("tc streaming", _lib.IMPL_TC, _lib.TC_LAYOUT_STREAM),
+                      ("fp32", _lib.IMPL_FP32, None)] if pomo else
+                     [("coop" if B < 148 * 8 else "stream", _lib.IMPL_AUTO, None)])
+            for iname, impl, lay in impls:
+                pol.decoder.tc_layout = lay
                 out = pol(td.clone(), env, decode_type=dt, noise_seed=2026, impl=impl)
                 st = compare_rollout(env_name, inst, h.cpu(), w, not pomo, out, dt, noise_seed=2026, min_exact=0.0,
                                      tie_gap=float("inf"), ll_rtol=1.0)
