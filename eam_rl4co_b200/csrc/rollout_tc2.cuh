@@ -693,8 +693,11 @@ __device__ __forceinline__ void cta_setup2(Ctx2& x) {
 }
 
 // ---- persistent fused rollout, streaming tensor path: two CTAs (instances) per SM ---------------------------------------
+#ifndef R4_TC2_MINBLOCKS
+#define R4_TC2_MINBLOCKS 2
+#endif
 template <int ENV, int MODE>
-__global__ void __launch_bounds__(kThreads2, 2)
+__global__ void __launch_bounds__(kThreads2, R4_TC2_MINBLOCKS)
     rollout_tc2_kernel(rl4co_cache c, rl4co_rollout_args a, const unsigned char* __restrict__ img, int npad) {
     extern __shared__ __align__(128) unsigned char smem[];
     Ctx2 x;
