@@ -873,8 +873,8 @@ struct RowState {
 
 // Outputs of the step that nothing in the next step waits for; called after the step-end barrier, where the
 // three short chains (logf, sqrt, scattered stores) of a row run in different warps under the next Q gathers.
-template <int ENV>
-__device__ __forceinline__ void record_action(const Ctx& x, const rl4co_rollout_args& a, RowState& st, int j,
+template <int ENV, class CX>
+__device__ __forceinline__ void record_action(const CX& x, const rl4co_rollout_args& a, RowState& st, int j,
                                               bool valid, int64_t grow, int t, int T, int act, float lpa) {
     if (!valid) return;
     if (j == 1) {
@@ -893,10 +893,10 @@ __device__ __forceinline__ void record_action(const Ctx& x, const rl4co_rollout_
     }
 }
 
-template <int ENV>
-__device__ __forceinline__ void apply_action(const Ctx& x, const rl4co_rollout_args& a, RowState& st, int n, int q,
+template <int ENV, class CX>
+__device__ __forceinline__ void apply_action(const CX& x, const rl4co_rollout_args& a, RowState& st, int n, int q,
                                              int j, int row, bool valid, int t, int act) {
-    Smem* s = x.s();
+    auto* s = x.s();
     if (j == 0 && valid) s->cur[row] = act;
     if (ENV == RL4CO_ENV_TSP) {
         if (valid && (act >> 5) == j) st.word &= ~(1u << (act & 31));

@@ -156,7 +156,8 @@ __global__ void __launch_bounds__(256) tc2_pack_kernel(rl4co_cache c, unsigned c
 
 // ---- MMA issue (one elected lane of the team's issuer warp) ---------------------------------------------------
 // scores of the head whose K pair sits in the team's K slot: S = Q . K_h^T, hi*hi + hi*lo + lo*hi
-__device__ __forceinline__ void issue_scores2(const Ctx2& x, int team) {
+template <class CX>
+__device__ __forceinline__ void issue_scores2(const CX& x, int team) {
     tc_fence_after();
     const uint32_t id = idesc_f16(kRows, x.npad);
     const uint64_t aq_hi = smem_desc(x.q_hi(team), kLBO_Q, kSBO_Q);
@@ -172,7 +173,8 @@ __device__ __forceinline__ void issue_scores2(const Ctx2& x, int team) {
 }
 
 // O = P . V_h : A = P from TMEM, B = the V^T pair in the team's V slot
-__device__ __forceinline__ void issue_pv2(const Ctx2& x, int team) {
+template <class CX>
+__device__ __forceinline__ void issue_pv2(const CX& x, int team) {
     tc_fence_after();
     const uint32_t id = idesc_f16(kRows, 16);
     const uint32_t vs = x.slot(team, 1);
@@ -192,25 +194,29 @@ __device__ __forceinline__ void issue_pv2(const Ctx2& x, int team) {
 }
 
 // one (hi, lo) pair of slices of instance image `img_b` -> ring slot; `which`: 0 = K, 1 = Vt, 2 = L of head h
-__device__ __forceinline__ void load_pair(const Ctx2& x, const unsigned char* img_b, int h, int which, void* dst,
+template <class CX>
+__device__ __forceinline__ void load_pair(const CX& x, const unsigned char* img_b, int h, int which, void* dst,
                                           uint64_t* bar) {
     const uint32_t sl = slice_bytes(x.npad);
     mbar_expect_tx(bar, 2u * sl);
     bulk_g2s(dst, img_b + (size_t)(6 * h + 2 * which) * sl, 2u * sl, bar);
 }
 // the team's K / V slot <- pair; the issuing lane counts the loads of a slot, a waiter takes the parity from the count
-__device__ __forceinline__ void load_slot(const Ctx2& x, const unsigned char* img_b, int h, int which, int team, int kv) {
+template <class CX>
+__device__ __forceinline__ void load_slot(const CX& x, const unsigned char* img_b, int h, int which, int team, int kv) {
     x.s()->n_load[team][kv] += 1u;
     load_pair(x, img_b, h, which, x.slot_p(team, kv), &x.s()->kv_bar[team][kv]);
 }
-__device__ __forceinline__ void wait_slot(const Ctx2& x, int team, int kv) {
+template <class CX>
+__device__ __forceinline__ void wait_slot(const CX& x, int team, int kv) {
     mbar_wait(&x.s()->kv_bar[team][kv], (x.s()->n_load[team][kv] - 1u) & 1u);
 }
 
 // logits = heads . (L W_out / sqrt(E))^T : k-step jk = head jk, its L pair sits in slot (jk & 1, jk >> 1) for jk < 4 and in
 // the stash area for jk >= 4 (requested here: the stash was consumed before the barrier that precedes this call)
-__device__ __forceinline__ void issue_logits2(const Ctx2& x, const unsigned char* img_b) {
-    Smem2* s = x.s();
+template <class CX>
+__device__ __forceinline__ void issue_logits2(const CX& x, const unsigned char* img_b) {
+    auto* s = x.s();
     fence_proxy_async();   // generic-proxy reads of the stash before the async-proxy overwrite
     s->n_lload += 1u;
 #pragma unroll
