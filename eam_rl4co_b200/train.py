@@ -84,13 +84,65 @@ def _replay_states_kernel(td, actions: torch.Tensor, S: int, cvrp: bool) -> Dict
     return out
 
 
+class _FusedEvaluate(torch.autograd.Function):
+    """log p(taken | row) [B,R] from the fused kernels rl4co_eval_ll_fwd / rl4co_eval_ll_bwd (csrc/evaluate_kernels.cu):
+    masked 8-head glimpse + pointer + log_softmax + gather per row, tables of an instance in shared memory; the backward
+    recomputes the probabilities from the saved log-sum-exps.  Differentiable in q, gk, gv, lkf."""
+
+    @staticmethod
+    def forward(ctx, q, gk, gv, lkf, mask, taken, tanh_clipping, temperature):
+        B, R, E = q.shape
+        n = gk.shape[1]
+        q, gk, gv, lkf = (t.contiguous().float() for t in (q, gk, gv, lkf))
+        mask = mask.reshape(B, R, n).contiguous()
+        taken = taken.reshape(B, R).contiguous()
+        dev = q.device
+        logp = torch.empty(B, R, device=dev)
+        heads = torch.empty(B, R, E, device=dev)
+        lse_h = torch.empty(B, R, 8, device=dev)
+        lse_z = torch.empty(B, R, device=dev)
+        maskw = torch.empty(B, R, 4, dtype=torch.int32, device=dev)
+        rc = _lib.lib().rl4co_eval_ll_fwd(_lib.ptr(q), _lib.ptr(gk), _lib.ptr(gv), _lib.ptr(lkf), _lib.ptr(mask),
+                                          _lib.ptr(taken), _lib.ptr(logp), _lib.ptr(heads), _lib.ptr(lse_h), _lib.ptr(lse_z),
+                                          _lib.ptr(maskw), C.c_int64(B), C.c_int64(R), C.c_int32(n), C.c_float(tanh_clipping),
+                                          C.c_float(temperature), _lib.stream_ptr())
+        _lib.check(rc, "rl4co_eval_ll_fwd")
+        ctx.save_for_backward(q, gk, gv, lkf, maskw, taken, heads, lse_h, lse_z)
+        ctx.scalars = (float(tanh_clipping), float(temperature))
+        return logp
+
+    @staticmethod
+    def backward(ctx, dlogp):
+        q, gk, gv, lkf, maskw, taken, heads, lse_h, lse_z = ctx.saved_tensors
+        B, R, E = q.shape
+        n = gk.shape[1]
+        dlogp = dlogp.contiguous().float()
+        dheads, du_t = torch.empty_like(heads), torch.empty_like(heads)
+        dq = torch.empty_like(q)
+        dgk, dgv, dlkf = torch.zeros_like(gk), torch.zeros_like(gv), torch.zeros_like(lkf)
+        rc = _lib.lib().rl4co_eval_ll_bwd(_lib.ptr(q), _lib.ptr(gk), _lib.ptr(gv), _lib.ptr(lkf), _lib.ptr(maskw),
+                                          _lib.ptr(taken), _lib.ptr(heads), _lib.ptr(lse_h), _lib.ptr(lse_z), _lib.ptr(dlogp),
+                                          _lib.ptr(dheads), _lib.ptr(du_t), _lib.ptr(torch.empty_like(lse_h)), _lib.ptr(dq), _lib.ptr(dgk), _lib.ptr(dgv), _lib.ptr(dlkf),
+                                          C.c_int64(B), C.c_int64(R), C.c_int32(n), C.c_float(ctx.scalars[0]),
+                                          C.c_float(ctx.scalars[1]), _lib.stream_ptr())
+        _lib.check(rc, "rl4co_eval_ll_bwd")
+        return dq, dgk, dgv, dlkf, None, None, None, None
+
+
+def fused_evaluate_supported(h: torch.Tensor, n: int) -> bool:
+    """The fused kernels cover CUDA fp32 embeddings of width 128 (8 heads) and n <= rl4co_eval_ll_max_nodes()."""
+    return h.is_cuda and h.shape[-1] == 128 and n <= int(_lib.lib().rl4co_eval_ll_max_nodes())
+
+
 def batched_log_likelihood(decoder, h: torch.Tensor, states: Dict[str, torch.Tensor], tanh_clipping: float = 10.0,
-                           temperature: float = 1.0) -> torch.Tensor:
+                           temperature: float = 1.0, fused: Optional[bool] = None) -> torch.Tensor:
     """Differentiable log p(action_t | prefix) for all (instance, start, step) at once -> [B, S, T-1].
 
     am/decoder.py:133-198 (context -> glimpse query), attention.py:282-328 (masked MHA glimpse, project_out,
-    logits / sqrt(E)), decoding.py:140-190 (tanh clip, mask, temperature, log_softmax).  Pure PyTorch: runs on any
-    device and is what autograd differentiates; `h` is the encoder output with its graph attached."""
+    logits / sqrt(E)), decoding.py:140-190 (tanh clip, mask, temperature, log_softmax).  `h` is the encoder output with its
+    graph attached.  The table products and the query gathers are PyTorch (autograd); the masked attention, pointer and
+    log-softmax of the B*S*(T-1) rows run on the fused forward / backward kernels (`_FusedEvaluate`) on CUDA, and as plain
+    PyTorch ops (`fused=False`, CPU tensors, n > 112) otherwise - the form the host tests pin against the oracle."""
     B, n, E = h.shape
     H = decoder.num_heads
     cur, mask, taken = states["cur"], states["mask"], states["taken"]
@@ -108,6 +160,13 @@ def batched_log_likelihood(decoder, h: torch.Tensor, states: Dict[str, torch.Ten
         q = idx(pb, cur).view(B, S, Tm, E) + states["rem"].unsqueeze(-1) * Wc[:, E]
     if decoder.use_graph_context:                                                  # decoder.py:223-224
         q = q + F.linear(h.mean(1), decoder.project_fixed_context.weight).view(B, 1, 1, E)
+    if fused is None:
+        fused = fused_evaluate_supported(h, n) and H == 8
+    if fused:
+        # logits = (glimpse W_out^T) lk^T = glimpse (lk W_out)^T: the fold the rollout kernels use (decoder.py cache)
+        lkf = torch.matmul(lk, decoder.pointer.project_out.weight)
+        logp = _FusedEvaluate.apply(q.reshape(B, R, E), gk, gv, lkf, mask, taken, float(tanh_clipping), float(temperature))
+        return logp.view(B, S, Tm)
     heads = lambda x, L: x.reshape(B, L, H, E // H).transpose(1, 2)
     am = mask.reshape(B, 1, R, n)
     glimpse = F.scaled_dot_product_attention(heads(q, R), heads(gk, n), heads(gv, n), attn_mask=am)

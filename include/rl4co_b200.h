@@ -268,6 +268,27 @@ int rl4co_best_of_starts(const float* reward, const int64_t* actions, int64_t B,
                          int32_t T, float* max_reward, int64_t* best_start, int64_t* best_multistart_actions,
                          float* max_aug_reward, int64_t* best_aug, int64_t* best_aug_actions, void* stream);
 
+/* ---- teacher-forced evaluate of ALL decoding steps at once, forward and backward ---------------------------------------
+ * decoding.py:452-465 (Evaluate), constructive/base.py:204-229, am/decoder.py:161-198, attention.py:282-328,
+ * decoding.py:140-190; the differentiable log-likelihood that reinforce.py:73-115 / pomo/model.py:103-112 backpropagate.
+ * Row (b, r), r = start * (T-1) + step, is independent of every other row once the actions are known:
+ *   q     [B,R,128]  glimpse query of the row (step context + fixed context, context.py:70-74,118-157; caller-built),
+ *   gk, gv, lkf [B,n,128]  glimpse key / value and logit key folded with project_out (lkf = lk @ W_out),
+ *   mask  [B,R,n] bool (feasible = 1; rl4co_replay_states writes it), taken [B,R] i64 (the action of the row).
+ * fwd: logp [B,R] = log_softmax(clip * tanh(heads . lkf / sqrt(128)) masked / temperature)[taken], and the values the
+ *      backward reuses: heads [B,R,128], lse_h [B,R,8] (log-sum-exp of each head's scores), lse_z [B,R], maskw [B,R,4]
+ *      (the mask as bit words).
+ * bwd: given dlogp [B,R]: dq [B,R,128] (written), dgk / dgv / dlkf [B,n,128] (ACCUMULATED: zero them first);
+ *      dheads, du_t [B,R,128] and dd [B,R,8] are scratch.  n_nodes <= rl4co_eval_ll_max_nodes() (112).                                  */
+int32_t rl4co_eval_ll_max_nodes(void);
+int rl4co_eval_ll_fwd(const float* q, const float* gk, const float* gv, const float* lkf, const uint8_t* mask,
+                      const int64_t* taken, float* logp, float* heads, float* lse_h, float* lse_z, uint32_t* maskw,
+                      int64_t B, int64_t R, int32_t n_nodes, float tanh_clipping, float temperature, void* stream);
+int rl4co_eval_ll_bwd(const float* q, const float* gk, const float* gv, const float* lkf, const uint32_t* maskw,
+                      const int64_t* taken, const float* heads, const float* lse_h, const float* lse_z, const float* dlogp,
+                      float* dheads, float* du_t, float* dd, float* dq, float* dgk, float* dgv, float* dlkf, int64_t B,
+                      int64_t R, int32_t n_nodes, float tanh_clipping, float temperature, void* stream);
+
 /* ---- on-device instance generation: the input spec of tsp/generator.py:53-62 and cvrp/generator.py:120-147 -----------
  * locs [B, n_loc, 2] uniform in [0,1); CVRP also depot [B,2] and demand [B, n_loc] = integer 1..9 / capacity.  Values come
  * from the counter hash keyed (seed, inst_offset + b, element), so shards of a global batch agree with the whole.   */

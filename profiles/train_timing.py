@@ -47,7 +47,7 @@ def main():
     print(f"CVRP100 POMO train step, B={B} x S={S}, T={out['actions'].shape[1]}: total {tot:.1f} ms "
           f"({isteps / tot * 1e3:.3e} instance-steps/s)")
     names = ["policy(): encoder + sampled rollout (fused kernel)", "state replay (rl4co_replay_states, one launch)",
-             "teacher-forced re-evaluation, forward (PyTorch)", "backward (PyTorch autograd)", "clip + Adam step"]
+             "teacher-forced re-evaluation, forward (rl4co_eval_ll_fwd + torch glue)", "backward (rl4co_eval_ll_bwd + torch autograd glue)", "clip + Adam step"]
     for name, v in zip(names, med):
         print(f"  {name:52s} {v:8.2f} ms  {100 * v / tot:5.1f}%")
     print(f"  peak memory {torch.cuda.max_memory_allocated() / 2**30:.2f} GiB")

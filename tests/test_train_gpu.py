@@ -101,3 +101,53 @@ def test_train_step_with_optimizer_improves_the_sampled_objective():
         net.use_kernels = True
     assert (hk - ht).abs().max().item() < 1e-4
     assert sum(h["reward"] for h in hist[-4:]) / 4 > sum(h["reward"] for h in hist[:4]) / 4 - 0.05
+
+
+@pytest.mark.parametrize("env_name,B,N,clip,temp", [("tsp", 3, 20, 10.0, 1.0), ("cvrp", 3, 20, 10.0, 1.0),
+                                                    ("tsp", 2, 100, 10.0, 1.0), ("cvrp", 2, 100, 10.0, 1.0),
+                                                    ("tsp", 2, 33, 0.0, 1.0), ("cvrp", 2, 20, 10.0, 0.7)])
+def test_fused_evaluate_kernels_match_eager_autograd(env_name, B, N, clip, temp):
+    """rl4co_eval_ll_fwd / rl4co_eval_ll_bwd against the plain-PyTorch form of the same rows (decoding.py:452-465,
+    attention.py:282-328, decoding.py:140-190): log-probabilities and the gradients w.r.t. the embeddings and every
+    decoder weight, under a random cotangent."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    inst, pol, env, td = _setup(env_name, B, N, seed=5)
+    with torch.no_grad():
+        out = pol(td.clone(), env, decode_type="multistart_sampling", noise_seed=9)
+        h0, _ = pol.encoder(td)
+    S = out["actions"].shape[0] // B
+    states = train.teacher_forced_states(env, td.clone(), out["actions"], S)
+    torch.manual_seed(7)
+    cot = torch.randn(B, S, states["cur"].shape[2], device=DEV)
+    res = {}
+    for fused in (True, False):
+        h = h0.clone().requires_grad_(True)
+        for p in pol.decoder.parameters():
+            p.grad = None
+        logp = train.batched_log_likelihood(pol.decoder, h, states, clip, temp, fused=fused)
+        (logp * cot).sum().backward()
+        grads = {k: p.grad.clone() for k, p in pol.decoder.named_parameters() if p.grad is not None}
+        res[fused] = (logp.detach(), h.grad.clone(), grads)
+    lf, hf, gf = res[True]
+    le, he, ge = res[False]
+    assert torch.isfinite(lf).all()
+    assert (lf - le).abs().max().item() < 2e-5 * max(1.0, le.abs().max().item())
+    tol = lambda a, b: (a - b).abs().max().item() / max(b.abs().max().item(), 1e-6)
+    assert tol(hf, he) < 2e-4
+    assert set(gf) == set(ge) and len(gf) >= 3
+    for k in ge:
+        assert tol(gf[k], ge[k]) < 2e-4, k
+
+
+def test_fused_evaluate_rejects_unsupported_sizes():
+    from eam_rl4co_b200 import _lib
+    import ctypes as C
+    L = _lib.lib()
+    assert L.rl4co_eval_ll_max_nodes() == 112
+    z = torch.zeros(8, device=DEV)
+    p = C.c_void_p(z.data_ptr())
+    rc = L.rl4co_eval_ll_fwd(p, p, p, p, p, p, p, p, p, p, p, C.c_int64(1), C.c_int64(1), C.c_int32(113), C.c_float(10.0),
+                             C.c_float(1.0), None)
+    assert rc != 0 and b"n_nodes" in L.rl4co_last_error()
+    h = torch.zeros(1, 120, 128, device=DEV)
+    assert not train.fused_evaluate_supported(h, 120) and train.fused_evaluate_supported(h, 101)
