@@ -37,6 +37,15 @@ __device__ __forceinline__ void copy_table(float* dst, const float* __restrict__
     for (int i = threadIdx.x; i < n * (kE / 4); i += blockDim.x)
         reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(src)[i];
 }
+// The row kernels read a table row as "head h, 4-channel chunk i" = 8 lanes x 16 B per LDS.128; with the natural layout the
+// lanes are 64 B apart and heads h, h + 2, h + 4, h + 6 share banks (4-way conflict, measured 2.2x on the forward kernel).
+// Swizzled layout: chunk i of head h of node nd at nd * 128 + 32 i + 4 h, i.e. the 8 lanes read 128 contiguous bytes.
+__device__ __forceinline__ void copy_table_swz(float* dst, const float* __restrict__ src, int n) {
+    for (int i = threadIdx.x; i < n * (kE / 4); i += blockDim.x) {
+        const int nd = i >> 5, c4 = i & 31;            // c4 = 4 h + chunk
+        reinterpret_cast<float4*>(dst)[nd * 32 + (c4 & 3) * 8 + (c4 >> 2)] = reinterpret_cast<const float4*>(src)[i];
+    }
+}
 __device__ __forceinline__ float sel4(const float (&v)[kNB], int k) {
     return k == 0 ? v[0] : (k == 1 ? v[1] : (k == 2 ? v[2] : v[3]));
 }
@@ -55,89 +64,130 @@ __device__ __forceinline__ void row_range(int64_t R, int64_t& r0, int64_t& r1) {
 // exp on the MUFU ex2 approximation (relative error ~2^-22, the arithmetic of the tensor-path rollout kernels)
 __device__ __forceinline__ float fexp(float x) { return __expf(x); }
 
-// glimpse_accum (decode_core.cuh) with fexp: online masked softmax over the feasible nodes of `sub`, four per iteration
-__device__ __forceinline__ void glimpse_accum_f(const float* gk, const float* gv, float4 qs, uint32_t sub, int node0,
-                                                int lane, float& m, float& l, float4& acc) {
-    const int off = 4 * lane;
-    while (sub) {
-        int j[4];
-        bool ok[4];
+// ---- lane mapping of the row kernels ------------------------------------------------------------------------------------------
+// A warp owns FOUR consecutive rows (consecutive steps of one start: nearly the same feasible set); lane = 8 ri + h holds
+// head h of row ri, i.e. 16 query / head channels in registers.  A 16-channel dot product is 16 FMAs without a shuffle
+// (a lane-owns-4-channels mapping needs two shuffle levels per score and repeats the softmax arithmetic in four lanes:
+// 2.4x the instructions, measured), table rows are read as 4 x LDS.128 (the four rows of the warp broadcast).
+// The node loops run over the UNION of the four rows' feasible sets; a row's own mask gates its probabilities.
+__device__ __forceinline__ void ld16(const float* __restrict__ p, float (&v)[16]) {
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            ok[u] = sub != 0u;
-            j[u] = ok[u] ? (__ffs(sub) - 1) : 0;
-            sub &= sub - 1u;
-        }
-#pragma unroll
-        for (int u = 1; u < 4; ++u) j[u] = ok[u] ? j[u] : j[0];
-        float4 k4[4], v4[4];
-        float s[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            k4[u] = ld4(gk + (node0 + j[u]) * kE + off);
-            v4[u] = ld4(gv + (node0 + j[u]) * kE + off);
-            s[u] = dot4(qs, k4[u]);
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) s[u] += __shfl_xor_sync(kFull, s[u], 1);
-#pragma unroll
-        for (int u = 0; u < 4; ++u) s[u] += __shfl_xor_sync(kFull, s[u], 2);
-#pragma unroll
-        for (int u = 1; u < 4; ++u) s[u] = ok[u] ? s[u] : -INFINITY;
-        const float mn = fmaxf(fmaxf(fmaxf(s[0], s[1]), fmaxf(s[2], s[3])), m);
-        const float c = fexp(m - mn);
-        float p[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) p[u] = fexp(s[u] - mn);
-        l = fmaf(l, c, (p[0] + p[1]) + (p[2] + p[3]));
-        acc.x = fmaf(acc.x, c, fmaf(p[0], v4[0].x, p[1] * v4[1].x) + fmaf(p[2], v4[2].x, p[3] * v4[3].x));
-        acc.y = fmaf(acc.y, c, fmaf(p[0], v4[0].y, p[1] * v4[1].y) + fmaf(p[2], v4[2].y, p[3] * v4[3].y));
-        acc.z = fmaf(acc.z, c, fmaf(p[0], v4[0].z, p[1] * v4[1].z) + fmaf(p[2], v4[2].z, p[3] * v4[3].z));
-        acc.w = fmaf(acc.w, c, fmaf(p[0], v4[0].w, p[1] * v4[1].w) + fmaf(p[2], v4[2].w, p[3] * v4[3].w));
-        m = mn;
+    for (int i = 0; i < 4; ++i) {
+        const float4 t = ld4(p + 4 * i);
+        v[4 * i] = t.x;
+        v[4 * i + 1] = t.y;
+        v[4 * i + 2] = t.z;
+        v[4 * i + 3] = t.w;
     }
 }
-
-// warp_logits (decode_core.cuh) with half the shuffles: the four partial dot products of a group are reduce-scattered
-// (xor 16 keeps two of them per half warp, xor 8 one per quarter) before the last three butterfly levels, and the logit
-// is scaled by a multiplication.  lg[blk] = heads . lkf[32 blk + lane] / sqrt(E) on the nodes of `which`, -inf elsewhere.
-__device__ __forceinline__ void warp_logits_f(const float* lk, float4 hd, const uint32_t (&which)[kNB], int lane,
-                                              float (&lg)[kNB]) {
-    const int off = 4 * lane;
-    const bool h16 = lane & 16, h8 = lane & 8;
+__device__ __forceinline__ void st16(float* __restrict__ p, const float (&v)[16]) {
 #pragma unroll
+    for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<float4*>(p + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+}
+// t = swizzled table row of a node + 4 h (copy_table_swz): chunk i at t + 32 i
+__device__ __forceinline__ float dot16(const float (&a)[16], const float* t) {
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float4 k = ld4(t + 32 * i);
+        s0 = fmaf(a[4 * i], k.x, s0);
+        s1 = fmaf(a[4 * i + 1], k.y, s1);
+        s0 = fmaf(a[4 * i + 2], k.z, s0);
+        s1 = fmaf(a[4 * i + 3], k.w, s1);
+    }
+    return s0 + s1;
+}
+__device__ __forceinline__ void axpy16(float (&acc)[16], float a, const float* t) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float4 k = ld4(t + 32 * i);
+        acc[4 * i] = fmaf(a, k.x, acc[4 * i]);
+        acc[4 * i + 1] = fmaf(a, k.y, acc[4 * i + 1]);
+        acc[4 * i + 2] = fmaf(a, k.z, acc[4 * i + 2]);
+        acc[4 * i + 3] = fmaf(a, k.w, acc[4 * i + 3]);
+    }
+}
+// union of a per-row word over the four rows of the warp
+__device__ __forceinline__ uint32_t or_rows(uint32_t w) {
+    w |= __shfl_xor_sync(kFull, w, 8);
+    w |= __shfl_xor_sync(kFull, w, 16);
+    return w;
+}
+// up to G node indices of `wb` (ascending), the rest repeat the first one with ok = false
+template <int G>
+__device__ __forceinline__ void next_nodes(uint32_t& wb, int (&j)[G], bool (&ok)[G]) {
+#pragma unroll
+    for (int u = 0; u < G; ++u) {
+        ok[u] = wb != 0u;
+        j[u] = ok[u] ? (__ffs(wb) - 1) : 0;
+        wb &= wb - 1u;
+    }
+#pragma unroll
+    for (int u = 1; u < G; ++u) j[u] = ok[u] ? j[u] : j[0];
+}
+// Transposed reduction over the 8 head lanes of a row: d[u] is this lane's partial of value u; afterwards lane h of the row
+// holds the total of value h (7 shuffles instead of 8 x 3).
+__device__ __forceinline__ float reduce_scatter8(const float (&d)[8], int h) {
+    const bool b2 = h & 4, b1 = h & 2, b0 = h & 1;
+    float a[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) a[i] = (b2 ? d[4 + i] : d[i]) + __shfl_xor_sync(kFull, b2 ? d[i] : d[4 + i], 4);
+    float e[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) e[i] = (b1 ? a[2 + i] : a[i]) + __shfl_xor_sync(kFull, b1 ? a[i] : a[2 + i], 2);
+    return (b0 ? e[1] : e[0]) + __shfl_xor_sync(kFull, b0 ? e[0] : e[1], 1);
+}
+__device__ __forceinline__ int sel8i(const int (&v)[8], int k) {
+    int r = v[0];
+#pragma unroll
+    for (int u = 1; u < 8; ++u) r = (k == u) ? v[u] : r;
+    return r;
+}
+__device__ __forceinline__ bool bit_of(const uint32_t (&w)[kNB], int node) {
+    return (sel4u(w, node >> 5) >> (node & 31)) & 1u;
+}
+
+// masked 8-head glimpse of the warp's four rows (attention.py:308-322), online softmax in chunks of four nodes
+__device__ __forceinline__ void glimpse_rows(const float* s_gk, const float* s_gv, const float (&qs)[16],
+                                             const uint32_t (&w)[kNB], const uint32_t (&wu)[kNB], int h, float (&o)[16],
+                                             float& lse) {
+    float m = -INFINITY, l = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) o[i] = 0.f;
+#pragma unroll 1
     for (int blk = 0; blk < kNB; ++blk) {
-        lg[blk] = -INFINITY;
-        uint32_t w = which[blk];
-        while (w) {
+        uint32_t wb = sel4u(wu, blk);
+        const uint32_t own = sel4u(w, blk);
+        while (wb) {
             int j[4];
             bool ok[4];
+            next_nodes<4>(wb, j, ok);
+            float s[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                ok[u] = w != 0u;
-                j[u] = ok[u] ? (__ffs(w) - 1) : 0;
-                w &= w - 1u;
+                const float v = dot16(qs, s_gk + (blk * 32 + j[u]) * kE + 4 * h);
+                s[u] = (ok[u] && ((own >> j[u]) & 1u)) ? v : -INFINITY;
             }
+            const float mn = fmaxf(fmaxf(fmaxf(s[0], s[1]), fmaxf(s[2], s[3])), m);
+            const float mref = (mn == -INFINITY) ? 0.f : mn;      // nothing feasible for this row so far
+            const float c = fexp(m - mref);
+            float p[4];
 #pragma unroll
-            for (int u = 1; u < 4; ++u) j[u] = ok[u] ? j[u] : j[0];
-            float d[4];
+            for (int u = 0; u < 4; ++u) p[u] = fexp(s[u] - mref);
+            l = fmaf(l, c, (p[0] + p[1]) + (p[2] + p[3]));
 #pragma unroll
-            for (int u = 0; u < 4; ++u) d[u] = dot4(hd, ld4(lk + (blk * 32 + j[u]) * kE + off));
-            float a0 = h16 ? d[2] : d[0], a1 = h16 ? d[3] : d[1];
-            a0 += __shfl_xor_sync(kFull, h16 ? d[0] : d[2], 16);
-            a1 += __shfl_xor_sync(kFull, h16 ? d[1] : d[3], 16);
-            float t = h8 ? a1 : a0;
-            t += __shfl_xor_sync(kFull, h8 ? a0 : a1, 8);
-            t += __shfl_xor_sync(kFull, t, 4);
-            t += __shfl_xor_sync(kFull, t, 2);
-            t += __shfl_xor_sync(kFull, t, 1);        // lanes [8 u, 8 u + 8) hold the dot product of node u
+            for (int i = 0; i < 16; ++i) o[i] *= c;
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const float v = __shfl_sync(kFull, t, 8 * u);
-                if (ok[u] && lane == j[u]) lg[blk] = v * kInvSqrtE;
-            }
+            for (int u = 0; u < 4; ++u) axpy16(o, p[u], s_gv + (blk * 32 + j[u]) * kE + 4 * h);
+            m = mn;
         }
     }
+    const bool any = l > 0.f;
+    const float inv = any ? 1.0f / l : 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) o[i] *= inv;
+    lse = any ? m + logf(l) : 0.f;
 }
 
 // ---- forward: logp[b,r]; saved for the backward: heads [B,R,E], lse_h [B,R,H], lse_z [B,R], maskw [B,R,4] -----------------
@@ -152,50 +202,89 @@ __global__ void __launch_bounds__(kThreads, 1)
     float* s_gv = sm + n * kE;
     float* s_lk = sm + 2 * n * kE;
     const int64_t b = blockIdx.x;
-    copy_table(s_gk, gk + b * n * kE, n);
-    copy_table(s_gv, gv + b * n * kE, n);
-    copy_table(s_lk, lkf + b * n * kE, n);
+    copy_table_swz(s_gk, gk + b * n * kE, n);
+    copy_table_swz(s_gv, gv + b * n * kE, n);
+    copy_table_swz(s_lk, lkf + b * n * kE, n);
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    const int ri = lane >> 3, h = lane & 7;
     int64_t r0, r1;
     row_range(R, r0, r1);
-    for (int64_t r = r0 + warp; r < r1; r += nw) {
-        const int64_t row = b * R + r;
-        const float4 q4 = ld4(q + row * kE + 4 * lane);
-        uint32_t w[kNB];
-        load_mask_words(mask + row * n, n, lane, w);
-        if (lane < kNB) maskw[row * kNB + lane] = sel4u(w, lane);
-        const float4 qs = make_float4(q4.x * 0.25f, q4.y * 0.25f, q4.z * 0.25f, q4.w * 0.25f);
-        float m = -INFINITY, l = 0.f;
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int blk = 0; blk < kNB; ++blk) glimpse_accum_f(s_gk, s_gv, qs, w[blk], blk * 32, lane, m, l, acc);
-        const bool any = l > 0.f;
-        const float inv = any ? 1.0f / l : 0.f;
-        const float4 o4 = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
-        *reinterpret_cast<float4*>(heads + row * kE + 4 * lane) = o4;
-        if ((lane & 3) == 0) lse_h[row * kH + (lane >> 2)] = any ? m + logf(l) : 0.f;
-        float lg[kNB];
-        warp_logits_f(s_lk, o4, w, lane, lg);           // raw logits / sqrt(E), lane owns nodes; -inf off the mask
-        float z[kNB], mx = -INFINITY;
+    for (int64_t rb = r0 + 4 * warp; rb < r1; rb += 4 * nw) {
+        const bool valid = rb + ri < r1;
+        const int64_t row = b * R + (valid ? rb + ri : r1 - 1);
+        // the four rows' masks as bit words: 32 lanes read 32 bytes of a row, one ballot per word
+        uint32_t w[kNB], wu[kNB];
 #pragma unroll
         for (int blk = 0; blk < kNB; ++blk) {
-            const bool f = (w[blk] >> lane) & 1u;
-            float v = lg[blk];
-            if (clip > 0.f) v = tanhf(v) * clip;        // decoding.py:171-172
-            z[blk] = f ? v / temperature : -INFINITY;   // :177, :180
-            mx = fmaxf(mx, z[blk]);
+            w[blk] = 0u;
+            wu[blk] = 0u;
         }
-        mx = warp_max(mx);
-        float sum = 0.f;
 #pragma unroll
-        for (int blk = 0; blk < kNB; ++blk) sum += (z[blk] == -INFINITY) ? 0.f : expf(z[blk] - mx);
-        sum = warp_sum(sum);
-        const float lz = any ? mx + logf(sum) : 0.f;
+        for (int rr = 0; rr < 4; ++rr) {
+            const int64_t rrow = b * R + (rb + rr < r1 ? rb + rr : r1 - 1);
+#pragma unroll
+            for (int blk = 0; blk < kNB; ++blk) {
+                const int i = 32 * blk + lane;
+                const uint32_t bal = __ballot_sync(kFull, i < n && mask[rrow * n + i] != 0);
+                w[blk] = (ri == rr) ? bal : w[blk];
+                wu[blk] |= bal;
+            }
+        }
+        if (valid && h < kNB) maskw[row * kNB + h] = sel4u(w, h);
+        float qs[16];
+        ld16(q + row * kE + 16 * h, qs);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) qs[i] *= 0.25f;
+        float o[16], lh;
+        glimpse_rows(s_gk, s_gv, qs, w, wu, h, o, lh);
+        if (valid) {
+            st16(heads + row * kE + 16 * h, o);
+            lse_h[row * kH + h] = lh;
+        }
+        // pointer: eight nodes per iteration; after the transposed reduction lane h holds the logit of node j[h]
         const int a = (int)taken[row];
-        const float za = __shfl_sync(kFull, sel4(z, (a >> 5) & 3), a & 31);
-        if (lane == 0) {
-            logp[row] = any ? za - lz : 0.f;            // :190 log_softmax, :462 gather
+        float zmax = -INFINITY, zsum = 0.f, za = -INFINITY;
+#pragma unroll 1
+        for (int blk = 0; blk < kNB; ++blk) {
+            uint32_t wb = sel4u(wu, blk);
+            while (wb) {
+                int j[8];
+                bool ok[8];
+                next_nodes<8>(wb, j, ok);
+                float d[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) d[u] = dot16(o, s_lk + (blk * 32 + j[u]) * kE + 4 * h);
+                const float tot = reduce_scatter8(d, h);
+                const int jm = sel8i(j, h);
+                bool f = (sel4u(w, blk) >> jm) & 1u;
+#pragma unroll
+                for (int u = 1; u < 8; ++u) f = f && (ok[u] || h != u);
+                float z = tot * kInvSqrtE;
+                if (clip > 0.f) z = tanhf(z) * clip;            // decoding.py:171-172
+                z = f ? z / temperature : -INFINITY;            // :177, :180
+                const float mn = fmaxf(zmax, z);
+                const float mref = (mn == -INFINITY) ? 0.f : mn;
+                zsum = zsum * expf(zmax - mref) + expf(z - mref);
+                zmax = mn;
+                if (f && blk * 32 + jm == a) za = z;
+            }
+        }
+        // combine the eight lanes of the row: log-sum-exp and the taken action's z
+#pragma unroll
+        for (int o2 = 4; o2 > 0; o2 >>= 1) {
+            const float om = __shfl_xor_sync(kFull, zmax, o2), os = __shfl_xor_sync(kFull, zsum, o2);
+            const float oa = __shfl_xor_sync(kFull, za, o2);
+            const float mn = fmaxf(zmax, om);
+            const float mref = (mn == -INFINITY) ? 0.f : mn;
+            zsum = zsum * expf(zmax - mref) + os * expf(om - mref);
+            zmax = mn;
+            za = fmaxf(za, oa);
+        }
+        if (valid && h == 0) {
+            const bool any = zsum > 0.f;
+            const float lz = any ? zmax + logf(zsum) : 0.f;
+            logp[row] = any ? za - lz : 0.f;                    // :190 log_softmax, :462 gather
             lse_z[row] = lz;
         }
     }
@@ -205,126 +294,154 @@ __global__ void __launch_bounds__(kThreads, 1)
 // (n = w, w + 16, ..., w + 96) are the eight contiguous floats [8 w, 8 w + 8)
 __device__ __forceinline__ int du_index(int node) { return (node & 15) * 8 + (node >> 4); }
 
-// ---- backward, row pass (one warp per row, no atomics): dheads, dq, du_t ---------------------------------------------------------
+// ---- backward, row pass of the pointer (no atomics): du_t, dheads ------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads, 1)
-    eval_row_bwd_kernel(const float* __restrict__ q, const float* __restrict__ gk, const float* __restrict__ gv,
-                        const float* __restrict__ lkf, const uint32_t* __restrict__ maskw, const int64_t* __restrict__ taken,
-                        const float* __restrict__ heads, const float* __restrict__ lse_h, const float* __restrict__ lse_z,
-                        const float* __restrict__ dlogp, float* __restrict__ dheads, float* __restrict__ dq,
-                        float* __restrict__ du_t, float* __restrict__ dd_out, int64_t R, int n, float clip,
-                        float temperature) {
+    eval_row_bwd_pointer_kernel(const float* __restrict__ lkf, const uint32_t* __restrict__ maskw,
+                                const int64_t* __restrict__ taken, const float* __restrict__ heads,
+                                const float* __restrict__ lse_z, const float* __restrict__ dlogp, float* __restrict__ dheads,
+                                float* __restrict__ du_t, int64_t R, int n, float clip, float temperature) {
+    extern __shared__ __align__(16) float sm[];
+    float* s_lk = sm;
+    const int64_t b = blockIdx.x;
+    copy_table_swz(s_lk, lkf + b * n * kE, n);
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    const int ri = lane >> 3, h = lane & 7;
+    int64_t r0, r1;
+    row_range(R, r0, r1);
+    for (int64_t rb = r0 + 4 * warp; rb < r1; rb += 4 * nw) {
+        const bool valid = rb + ri < r1;
+        const int64_t row = b * R + (valid ? rb + ri : r1 - 1);
+        uint32_t w[kNB], wu[kNB];
+        {
+            const uint4 mw = *reinterpret_cast<const uint4*>(maskw + row * kNB);
+            w[0] = mw.x, w[1] = mw.y, w[2] = mw.z, w[3] = mw.w;
+        }
+#pragma unroll
+        for (int blk = 0; blk < kNB; ++blk) wu[blk] = or_rows(w[blk]);
+        float o[16];
+        ld16(heads + row * kE + 16 * h, o);
+        const float g = dlogp[row], lz = lse_z[row];
+        const int a = (int)taken[row];
+        // zero this row's du_t (lane h: entries [16 h, 16 h + 16)), then the visited nodes overwrite their entries
+        if (valid) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                *reinterpret_cast<float4*>(du_t + row * kE + 16 * h + 4 * i) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        __syncwarp();
+        // pointer: du[n] = g (1[n = a] - softmax(z)[n]) dz/du / sqrt(E);  dheads = sum_n du[n] lkf[n]
+        float dh[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) dh[i] = 0.f;
+#pragma unroll 1
+        for (int blk = 0; blk < kNB; ++blk) {
+            uint32_t wb = sel4u(wu, blk);
+            while (wb) {
+                int j[8];
+                bool ok[8];
+                next_nodes<8>(wb, j, ok);
+                float d[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) d[u] = dot16(o, s_lk + (blk * 32 + j[u]) * kE + 4 * h);
+                const float tot = reduce_scatter8(d, h);
+                const int jm = sel8i(j, h);
+                bool f = (sel4u(w, blk) >> jm) & 1u;
+#pragma unroll
+                for (int u = 1; u < 8; ++u) f = f && (ok[u] || h != u);
+                const float uv = tot * kInvSqrtE;
+                float zv, dzu;
+                if (clip > 0.f) {
+                    const float t = tanhf(uv);
+                    zv = t * clip / temperature;
+                    dzu = clip * (1.0f - t * t) / temperature;
+                } else {
+                    zv = uv / temperature;
+                    dzu = 1.0f / temperature;
+                }
+                const float du = f ? g * ((blk * 32 + jm == a ? 1.0f : 0.0f) - expf(zv - lz)) * dzu * kInvSqrtE : 0.f;
+                if (valid && f) du_t[row * kE + du_index(blk * 32 + jm)] = du;
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const float dn = __shfl_sync(kFull, du, (lane & 24) | u);
+                    if (ok[u]) axpy16(dh, dn, s_lk + (blk * 32 + j[u]) * kE + 4 * h);   // warp-uniform
+                    asm volatile("" ::: "memory");   // one table row in flight at a time: eight hoisted rows spill
+                }
+            }
+        }
+        if (valid) st16(dheads + row * kE + 16 * h, dh);
+    }
+}
+
+// ---- backward, row pass of the glimpse: dq = 0.25 sum_n dS[n] k[n], dS = P (dP - D), P from the saved log-sum-exp; dd = D ------
+__global__ void __launch_bounds__(kThreads, 1)
+    eval_row_bwd_glimpse_kernel(const float* __restrict__ q, const float* __restrict__ gk, const float* __restrict__ gv,
+                                const uint32_t* __restrict__ maskw, const float* __restrict__ heads,
+                                const float* __restrict__ lse_h, const float* __restrict__ dheads, float* __restrict__ dq,
+                                float* __restrict__ dd_out, int64_t R, int n) {
     extern __shared__ __align__(16) float sm[];
     float* s_gk = sm;
     float* s_gv = sm + n * kE;
-    float* s_lk = sm + 2 * n * kE;
     const int64_t b = blockIdx.x;
-    copy_table(s_gk, gk + b * n * kE, n);
-    copy_table(s_gv, gv + b * n * kE, n);
-    copy_table(s_lk, lkf + b * n * kE, n);
+    copy_table_swz(s_gk, gk + b * n * kE, n);
+    copy_table_swz(s_gv, gv + b * n * kE, n);
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-    const int off = 4 * lane;
+    const int ri = lane >> 3, h = lane & 7;
     int64_t r0, r1;
     row_range(R, r0, r1);
-    for (int64_t r = r0 + warp; r < r1; r += nw) {
-        const int64_t row = b * R + r;
-        const float4 o4 = ld4(heads + row * kE + off);
-        const float g = dlogp[row], lz = lse_z[row];
-        const int a = (int)taken[row];
-        uint32_t w[kNB];
-#pragma unroll
-        for (int blk = 0; blk < kNB; ++blk) w[blk] = maskw[row * kNB + blk];
-        // pointer: du[n] = g (1[n = a] - softmax(z)[n]) dz/du / sqrt(E), lane owns nodes
-        float lg[kNB], du[kNB];
-        warp_logits_f(s_lk, o4, w, lane, lg);
-#pragma unroll
-        for (int blk = 0; blk < kNB; ++blk) {
-            const bool f = (w[blk] >> lane) & 1u;
-            const float uv = f ? lg[blk] : 0.f;
-            float zv, dzu;
-            if (clip > 0.f) {
-                const float t = tanhf(uv);
-                zv = t * clip / temperature;
-                dzu = clip * (1.0f - t * t) / temperature;
-            } else {
-                zv = uv / temperature;
-                dzu = 1.0f / temperature;
-            }
-            const float pz = expf(zv - lz);
-            du[blk] = f ? g * ((32 * blk + lane == a ? 1.0f : 0.0f) - pz) * dzu * kInvSqrtE : 0.f;
-            du_t[row * kE + du_index(32 * blk + lane)] = du[blk];
+    for (int64_t rb = r0 + 4 * warp; rb < r1; rb += 4 * nw) {
+        const bool valid = rb + ri < r1;
+        const int64_t row = b * R + (valid ? rb + ri : r1 - 1);
+        uint32_t w[kNB], wu[kNB];
+        {
+            const uint4 mw = *reinterpret_cast<const uint4*>(maskw + row * kNB);
+            w[0] = mw.x, w[1] = mw.y, w[2] = mw.z, w[3] = mw.w;
         }
-        // dheads = sum_n du[n] lkf[n]
-        float4 d4 = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int blk = 0; blk < kNB; ++blk) {
-            uint32_t wb = w[blk];
-            while (wb) {
-                const int j = __ffs(wb) - 1;
-                wb &= wb - 1u;
-                const float dn = __shfl_sync(kFull, du[blk], j);
-                const float4 l4 = ld4(s_lk + (blk * 32 + j) * kE + off);
-                d4.x = fmaf(dn, l4.x, d4.x);
-                d4.y = fmaf(dn, l4.y, d4.y);
-                d4.z = fmaf(dn, l4.z, d4.z);
-                d4.w = fmaf(dn, l4.w, d4.w);
-            }
+        for (int blk = 0; blk < kNB; ++blk) wu[blk] = or_rows(w[blk]);
+        float dh[16];
+        ld16(dheads + row * kE + 16 * h, dh);
+        float dd = 0.f;
+        {
+            float o[16];
+            ld16(heads + row * kE + 16 * h, o);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) dd = fmaf(dh[i], o[i], dd);
         }
-        *reinterpret_cast<float4*>(dheads + row * kE + off) = d4;
-        // glimpse: dq = 0.25 sum_n dS[n] k[n], dS = P (dP - D), P recomputed from the saved log-sum-exp
-        const float4 q4 = ld4(q + row * kE + off);
-        const float4 qs = make_float4(q4.x * 0.25f, q4.y * 0.25f, q4.z * 0.25f, q4.w * 0.25f);
-        const float lh = lse_h[row * kH + (lane >> 2)];
-        float dd = dot4(d4, o4);
-        dd += __shfl_xor_sync(kFull, dd, 1);
-        dd += __shfl_xor_sync(kFull, dd, 2);
-        if ((lane & 3) == 0) dd_out[row * kH + (lane >> 2)] = dd;
-        float4 dqs = make_float4(0.f, 0.f, 0.f, 0.f);
+        float qs[16];
+        ld16(q + row * kE + 16 * h, qs);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) qs[i] *= 0.25f;
+        const float lh = lse_h[row * kH + h];
+        if (valid) dd_out[row * kH + h] = dd;
+        float dqs[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) dqs[i] = 0.f;
 #pragma unroll 1
         for (int blk = 0; blk < kNB; ++blk) {
-            uint32_t wb = w[blk];
+            uint32_t wb = sel4u(wu, blk);
+            const uint32_t own = sel4u(w, blk);
             while (wb) {
-                int j[4];
-                bool ok[4];
+                int j[2];
+                bool ok[2];
+                next_nodes<2>(wb, j, ok);
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    ok[u] = wb != 0u;
-                    j[u] = ok[u] ? (__ffs(wb) - 1) : 0;
-                    wb &= wb - 1u;
-                }
-#pragma unroll
-                for (int u = 1; u < 4; ++u) j[u] = ok[u] ? j[u] : j[0];
-                float4 k4[4];
-                float s[4], dp[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    k4[u] = ld4(s_gk + (blk * 32 + j[u]) * kE + off);
-                    const float4 v4 = ld4(s_gv + (blk * 32 + j[u]) * kE + off);
-                    s[u] = dot4(qs, k4[u]);
-                    dp[u] = dot4(d4, v4);
-                }
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    s[u] += __shfl_xor_sync(kFull, s[u], 1);
-                    dp[u] += __shfl_xor_sync(kFull, dp[u], 1);
-                }
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    s[u] += __shfl_xor_sync(kFull, s[u], 2);
-                    dp[u] += __shfl_xor_sync(kFull, dp[u], 2);
-                }
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const float ds = ok[u] ? fexp(s[u] - lh) * (dp[u] - dd) : 0.f;
-                    dqs.x = fmaf(ds, k4[u].x, dqs.x);
-                    dqs.y = fmaf(ds, k4[u].y, dqs.y);
-                    dqs.z = fmaf(ds, k4[u].z, dqs.z);
-                    dqs.w = fmaf(ds, k4[u].w, dqs.w);
+                for (int u = 0; u < 2; ++u) {
+                    const float* kr = s_gk + (blk * 32 + j[u]) * kE + 4 * h;
+                    const float sv = dot16(qs, kr);
+                    const float dp = dot16(dh, s_gv + (blk * 32 + j[u]) * kE + 4 * h);
+                    const bool f = ok[u] && ((own >> j[u]) & 1u);
+                    const float ds = f ? fexp(sv - lh) * (dp - dd) : 0.f;
+                    axpy16(dqs, ds, kr);
                 }
             }
         }
-        *reinterpret_cast<float4*>(dq + row * kE + off) =
-            make_float4(dqs.x * 0.25f, dqs.y * 0.25f, dqs.z * 0.25f, dqs.w * 0.25f);
+        if (valid) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) dqs[i] *= 0.25f;
+            st16(dq + row * kE + 16 * h, dqs);
+        }
     }
 }
 
@@ -335,21 +452,33 @@ __global__ void __launch_bounds__(kThreads, 1)
 // Lane L holds channels 4L..4L+3 of every accumulator; a CTA's sums reach global memory with one red per element.
 constexpr int kOwn = 7;   // 16 warps x 7 nodes = 112 = rl4co_eval_ll_max_nodes()
 
-struct NodeRow {   // what the glimpse part of the node pass reads per row
-    float4 q4, d4;
-    float lh, dd;
-    uint4 mw;
-};
-__device__ __forceinline__ NodeRow load_node_row(const float* __restrict__ q, const float* __restrict__ dheads,
-                                                 const float* __restrict__ lse_h, const float* __restrict__ dd,
-                                                 const uint32_t* __restrict__ maskw, int64_t row, int lane) {
-    NodeRow x;
-    x.q4 = ld4(q + row * kE + 4 * lane);
-    x.d4 = ld4(dheads + row * kE + 4 * lane);
-    x.lh = lse_h[row * kH + (lane >> 2)];
-    x.dd = dd[row * kH + (lane >> 2)];
-    x.mw = *reinterpret_cast<const uint4*>(maskw + row * kNB);
-    return x;
+// cp.async staging of row tiles: every warp of a node-pass CTA consumes the same rows, so a tile is fetched once per CTA
+// and read from shared memory (a first version in which each warp loaded its rows from global memory itself was bound by
+// one L2 round trip per row group and warp: 6.3 of 11.7 ms of the backward).
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* dst, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+constexpr int kTR = 32;   // rows per tile
+
+// [rows, 128] fp32 rows -> shared, linear (swz = false) or in the (chunk, head) order of copy_table_swz (swz = true)
+template <bool SWZ>
+__device__ __forceinline__ void stage_rows(float* dst, const float* __restrict__ src, int rows) {
+    for (int i = threadIdx.x; i < rows * 32; i += blockDim.x) {
+        const int r = i >> 5, c4 = i & 31;
+        const int d = SWZ ? r * 32 + (c4 & 3) * 8 + (c4 >> 2) : i;
+        cp_async16(dst + 4 * d, src + 4 * i);
+    }
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -360,34 +489,53 @@ __global__ void __launch_bounds__(kThreads, 1)
     extern __shared__ __align__(16) float sm[];
     const int64_t b = blockIdx.x;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int off = 4 * lane;
     int64_t r0, r1;
     row_range(R, r0, r1);
     if (r0 >= r1) return;
+    const int ntiles = (int)((r1 - r0 + kTR - 1) / kTR);
     if (blockIdx.z == 0) {
+        // pointer: warp w owns nodes w + 16 i (i < 7), lane L channels 4L..4L+3; du_t holds the warp's eight du values of a
+        // row contiguously.  Tiles: heads rows and du_t rows, two stages.
+        float* st_o[2] = {sm, sm + 2 * kTR * kE};
+        float* st_d[2] = {sm + kTR * kE, sm + 3 * kTR * kE};
+        const int off = 4 * lane;
         float4 acc[kOwn];
 #pragma unroll
         for (int i = 0; i < kOwn; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        // the next row's loads are in flight while a row is accumulated (every warp of the CTA streams the same rows)
-        float4 o4 = ld4(heads + (b * R + r0) * kE + off);
-        float4 da = ld4(du_t + (b * R + r0) * kE + 8 * warp);
-        float4 db = ld4(du_t + (b * R + r0) * kE + 8 * warp + 4);
-        for (int64_t r = r0; r < r1; ++r) {
-            const int64_t nxt = b * R + (r + 1 < r1 ? r + 1 : r);
-            const float4 o4n = ld4(heads + nxt * kE + off);
-            const float4 dan = ld4(du_t + nxt * kE + 8 * warp);
-            const float4 dbn = ld4(du_t + nxt * kE + 8 * warp + 4);
-            const float dn[8] = {da.x, da.y, da.z, da.w, db.x, db.y, db.z, db.w};
-#pragma unroll
-            for (int i = 0; i < kOwn; ++i) {
-                acc[i].x = fmaf(dn[i], o4.x, acc[i].x);
-                acc[i].y = fmaf(dn[i], o4.y, acc[i].y);
-                acc[i].z = fmaf(dn[i], o4.z, acc[i].z);
-                acc[i].w = fmaf(dn[i], o4.w, acc[i].w);
+        auto issue = [&](int t) {
+            const int64_t rt = r0 + (int64_t)t * kTR;
+            const int rows = (int)(r1 - rt < kTR ? r1 - rt : kTR);
+            stage_rows<false>(st_o[t & 1], heads + (b * R + rt) * kE, rows);
+            stage_rows<false>(st_d[t & 1], du_t + (b * R + rt) * kE, rows);
+            cp_async_commit();
+        };
+        issue(0);
+        for (int t = 0; t < ntiles; ++t) {
+            if (t + 1 < ntiles) {
+                issue(t + 1);
+                cp_async_wait<1>();
+            } else {
+                cp_async_wait<0>();
             }
-            o4 = o4n;
-            da = dan;
-            db = dbn;
+            __syncthreads();
+            const int64_t rt = r0 + (int64_t)t * kTR;
+            const int rows = (int)(r1 - rt < kTR ? r1 - rt : kTR);
+            const float* so = st_o[t & 1];
+            const float* sd = st_d[t & 1];
+#pragma unroll 4
+            for (int r = 0; r < rows; ++r) {
+                const float4 o4 = ld4(so + r * kE + off);
+                const float4 da = ld4(sd + r * kE + 8 * warp), db = ld4(sd + r * kE + 8 * warp + 4);
+                const float dn[8] = {da.x, da.y, da.z, da.w, db.x, db.y, db.z, db.w};
+#pragma unroll
+                for (int i = 0; i < kOwn; ++i) {
+                    acc[i].x = fmaf(dn[i], o4.x, acc[i].x);
+                    acc[i].y = fmaf(dn[i], o4.y, acc[i].y);
+                    acc[i].z = fmaf(dn[i], o4.z, acc[i].z);
+                    acc[i].w = fmaf(dn[i], o4.w, acc[i].w);
+                }
+            }
+            __syncthreads();   // the stage is refilled two tiles later
         }
 #pragma unroll
         for (int i = 0; i < kOwn; ++i) {
@@ -402,66 +550,115 @@ __global__ void __launch_bounds__(kThreads, 1)
         }
         return;
     }
+    // glimpse, node quarter qd (the nodes of mask word qd): warp w owns nodes 32 qd + w and 32 qd + w + 16; lane = (row of
+    // a four-row group, head) as in the row kernels, so P and dS of (row, head, node) cost two 16-FMA dot products and
+    // the accumulators are 2 nodes x 2 tables x 16 channels per lane; the four row lanes are summed at the end.
+    const int qd = blockIdx.z - 1;
+    if (32 * qd >= n) return;
+    const int ri = lane >> 3, h = lane & 7;
+    const int nq = n - 32 * qd < 32 ? n - 32 * qd : 32;
     float* s_gk = sm;
-    float* s_gv = sm + n * kE;
-    copy_table(s_gk, gk + b * n * kE, n);
-    copy_table(s_gv, gv + b * n * kE, n);
-    __syncthreads();
-    float4 ak[kOwn], av[kOwn];
-#pragma unroll
-    for (int i = 0; i < kOwn; ++i) {
-        ak[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        av[i] = ak[i];
-    }
-    NodeRow x = load_node_row(q, dheads, lse_h, dd, maskw, b * R + r0, lane);
-    for (int64_t r = r0; r < r1; ++r) {
-        const NodeRow xn = load_node_row(q, dheads, lse_h, dd, maskw, b * R + (r + 1 < r1 ? r + 1 : r), lane);
-        // feasibility of the warp's nodes: node w + 16 i = bit (w + 16 (i & 1)) of word i / 2
-        const uint32_t m0 = (x.mw.x >> warp) & 0x10001u, m1 = (x.mw.y >> warp) & 0x10001u,
-                       m2 = (x.mw.z >> warp) & 0x10001u, m3 = (x.mw.w >> warp) & 0x10001u;
-        const uint32_t own = (m0 & 1u) | ((m0 >> 15) & 2u) | ((m1 & 1u) << 2) | ((m1 >> 13) & 8u) | ((m2 & 1u) << 4) |
-                             ((m2 >> 11) & 32u) | ((m3 & 1u) << 6);
-        const float4 qs = make_float4(x.q4.x * 0.25f, x.q4.y * 0.25f, x.q4.z * 0.25f, x.q4.w * 0.25f);
-#pragma unroll
-        for (int i = 0; i < kOwn; ++i) {
-            if (!((own >> i) & 1u)) continue;            // warp-uniform
-            const int node = warp + 16 * i;
-            const float4 k4 = ld4(s_gk + node * kE + off);
-            const float4 v4 = ld4(s_gv + node * kE + off);
-            float s = dot4(qs, k4), dp = dot4(x.d4, v4);
-            s += __shfl_xor_sync(kFull, s, 1);
-            dp += __shfl_xor_sync(kFull, dp, 1);
-            s += __shfl_xor_sync(kFull, s, 2);
-            dp += __shfl_xor_sync(kFull, dp, 2);
-            const float p = fexp(s - x.lh);
-            const float ds = p * (dp - x.dd);
-            ak[i].x = fmaf(ds, qs.x, ak[i].x);
-            ak[i].y = fmaf(ds, qs.y, ak[i].y);
-            ak[i].z = fmaf(ds, qs.z, ak[i].z);
-            ak[i].w = fmaf(ds, qs.w, ak[i].w);
-            av[i].x = fmaf(p, x.d4.x, av[i].x);
-            av[i].y = fmaf(p, x.d4.y, av[i].y);
-            av[i].z = fmaf(p, x.d4.z, av[i].z);
-            av[i].w = fmaf(p, x.d4.w, av[i].w);
+    float* s_gv = sm + 32 * kE;
+    float* base = sm + 64 * kE;
+    constexpr int kStage = 2 * kTR * kE + 2 * kTR * kH + kTR;     // q, dheads, lse_h, dd, mask word
+    auto st_q = [&](int st) { return base + st * kStage; };
+    auto st_dh = [&](int st) { return base + st * kStage + kTR * kE; };
+    auto st_lh = [&](int st) { return base + st * kStage + 2 * kTR * kE; };
+    auto st_dd = [&](int st) { return base + st * kStage + 2 * kTR * kE + kTR * kH; };
+    auto st_mw = [&](int st) { return reinterpret_cast<uint32_t*>(base + st * kStage + 2 * kTR * kE + 2 * kTR * kH); };
+    copy_table_swz(s_gk, gk + (b * n + 32 * qd) * kE, nq);
+    copy_table_swz(s_gv, gv + (b * n + 32 * qd) * kE, nq);
+    auto issue = [&](int t) {
+        const int64_t rt = r0 + (int64_t)t * kTR;
+        const int rows = (int)(r1 - rt < kTR ? r1 - rt : kTR);
+        const int st = t & 1;
+        stage_rows<true>(st_q(st), q + (b * R + rt) * kE, rows);
+        stage_rows<true>(st_dh(st), dheads + (b * R + rt) * kE, rows);
+        for (int i = threadIdx.x; i < rows * 2; i += blockDim.x) {
+            cp_async16(st_lh(st) + 4 * i, lse_h + (b * R + rt) * kH + 4 * i);
+            cp_async16(st_dd(st) + 4 * i, dd + (b * R + rt) * kH + 4 * i);
         }
-        x = xn;
-    }
+        if (threadIdx.x < rows) cp_async4(st_mw(st) + threadIdx.x, maskw + (b * R + rt + threadIdx.x) * kNB + qd);
+        cp_async_commit();
+    };
+    float ak[2][16], av[2][16];
 #pragma unroll
-    for (int i = 0; i < kOwn; ++i) {
-        const int node = warp + 16 * i;
-        if (node < n) {
-            float* dk = dgk + (b * n + node) * kE + off;
-            float* dv = dgv + (b * n + node) * kE + off;
-            atomicAdd(dk + 0, ak[i].x);
-            atomicAdd(dk + 1, ak[i].y);
-            atomicAdd(dk + 2, ak[i].z);
-            atomicAdd(dk + 3, ak[i].w);
-            atomicAdd(dv + 0, av[i].x);
-            atomicAdd(dv + 1, av[i].y);
-            atomicAdd(dv + 2, av[i].z);
-            atomicAdd(dv + 3, av[i].w);
+    for (int i = 0; i < 2; ++i) {
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+            ak[i][c] = 0.f;
+            av[i][c] = 0.f;
         }
     }
+    issue(0);
+    for (int t = 0; t < ntiles; ++t) {
+        if (t + 1 < ntiles) {
+            issue(t + 1);
+            cp_async_wait<1>();
+        } else {
+            cp_async_wait<0>();
+        }
+        __syncthreads();                                 // also covers the tables on the first tile
+        const int64_t rt = r0 + (int64_t)t * kTR;
+        const int rows = (int)(r1 - rt < kTR ? r1 - rt : kTR);
+        const int st = t & 1;
+#pragma unroll 1
+        for (int g = 0; g < rows; g += 4) {
+            const int r = g + ri;
+            const uint32_t wq = r < rows ? st_mw(st)[r] : 0u;
+            const bool f0 = (wq >> warp) & 1u, f1 = (wq >> (warp + 16)) & 1u;
+            const bool any0 = __any_sync(kFull, f0), any1 = __any_sync(kFull, f1);
+            if (!(any0 || any1)) continue;
+            const int rc = r < rows ? r : rows - 1;
+            float qs[16], dh[16];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float4 a4 = ld4(st_q(st) + rc * kE + 32 * i + 4 * h);
+                const float4 d4 = ld4(st_dh(st) + rc * kE + 32 * i + 4 * h);
+                qs[4 * i] = a4.x * 0.25f, qs[4 * i + 1] = a4.y * 0.25f, qs[4 * i + 2] = a4.z * 0.25f;
+                qs[4 * i + 3] = a4.w * 0.25f;
+                dh[4 * i] = d4.x, dh[4 * i + 1] = d4.y, dh[4 * i + 2] = d4.z, dh[4 * i + 3] = d4.w;
+            }
+            const float lh = st_lh(st)[rc * kH + h], dv = st_dd(st)[rc * kH + h];
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                if (!(i ? any1 : any0)) continue;        // warp-uniform
+                const int nd = warp + 16 * i;
+                const float sv = dot16(qs, s_gk + nd * kE + 4 * h);
+                const float dp = dot16(dh, s_gv + nd * kE + 4 * h);
+                const float p = (i ? f1 : f0) ? fexp(sv - lh) : 0.f;
+                const float ds = p * (dp - dv);
+#pragma unroll
+                for (int c = 0; c < 16; ++c) {
+                    ak[i][c] = fmaf(ds, qs[c], ak[i][c]);
+                    av[i][c] = fmaf(p, dh[c], av[i][c]);
+                }
+            }
+        }
+        __syncthreads();   // the stage is refilled two tiles later
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int node = 32 * qd + warp + 16 * i;
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+            float a = ak[i][c], v = av[i][c];
+            a += __shfl_xor_sync(kFull, a, 8);
+            v += __shfl_xor_sync(kFull, v, 8);
+            a += __shfl_xor_sync(kFull, a, 16);
+            v += __shfl_xor_sync(kFull, v, 16);
+            if (ri == 0 && node < n) {
+                atomicAdd(dgk + (b * n + node) * kE + 16 * h + c, a);
+                atomicAdd(dgv + (b * n + node) * kE + 16 * h + c, v);
+            }
+        }
+    }
+}
+
+// node pass: two [32,128] table quarters + two stages of (q, dheads, lse_h, dd, mask word) tiles; the pointer part (two stages
+// of two row tiles) needs less
+static size_t node_smem_bytes() {
+    return (size_t)(64 * kE + 2 * (2 * kTR * kE + 2 * kTR * kH + kTR)) * sizeof(float);
 }
 
 // Row split per instance: `units` equal CTAs per split step over sms * ctas_per_sm slots, the split in [1, 32] with the
@@ -540,15 +737,21 @@ extern "C" int rl4co_eval_ll_bwd(const float* q, const float* gk, const float* g
     if (B == 0 || R == 0) return RL4CO_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t table = (size_t)n_nodes * kE * sizeof(float);
-    if ((rc = ev::set_smem(ev::eval_row_bwd_kernel, 3 * table, "eval_ll_bwd (row pass)"))) return rc;
-    if ((rc = ev::set_smem(ev::eval_node_bwd_kernel, 2 * table, "eval_ll_bwd (node pass)"))) return rc;
+    if ((rc = ev::set_smem(ev::eval_row_bwd_pointer_kernel, table, "eval_ll_bwd (row pass, pointer)"))) return rc;
+    if ((rc = ev::set_smem(ev::eval_row_bwd_glimpse_kernel, 2 * table, "eval_ll_bwd (row pass, glimpse)"))) return rc;
+    if ((rc = ev::set_smem(ev::eval_node_bwd_kernel, ev::node_smem_bytes(), "eval_ll_bwd (node pass)"))) return rc;
     dim3 g1((unsigned)B, (unsigned)ev::grid_split(B, 1));
-    ev::eval_row_bwd_kernel<<<g1, ev::kThreads, 3 * table, st>>>(q, gk, gv, lkf, maskw, taken, heads, lse_h, lse_z, dlogp,
-                                                                dheads, dq, du_t, dd, R, n_nodes, tanh_clipping, temperature);
+    ev::eval_row_bwd_pointer_kernel<<<g1, ev::kThreads, table, st>>>(lkf, maskw, taken, heads, lse_z, dlogp, dheads, du_t, R,
+                                                                    n_nodes, tanh_clipping, temperature);
+    R4_CHECK_LAUNCH("eval_ll_bwd (row pass, pointer)");
+    ev::eval_row_bwd_glimpse_kernel<<<g1, ev::kThreads, 2 * table, st>>>(q, gk, gv, maskw, heads, lse_h, dheads, dq, dd, R,
+                                                                        n_nodes);
     R4_CHECK_LAUNCH("eval_ll_bwd (row pass)");
-    // pointer part (z = 0) and glimpse part (z = 1) of the node pass share the grid: twice grid_split CTAs per instance
-    dim3 g2((unsigned)B, (unsigned)ev::grid_split(2 * B, 1), 2u);
-    ev::eval_node_bwd_kernel<<<g2, ev::kThreads, 2 * table, st>>>(q, gk, gv, maskw, heads, lse_h, dheads, du_t, dd, dgk, dgv,
+    // pointer part (z = 0) and the glimpse part's node quarters (z = 1 + mask word) share one grid
+    const unsigned nz = 1u + (unsigned)((n_nodes + 31) / 32);
+    dim3 g2((unsigned)B, (unsigned)ev::grid_split(nz * B, 1), nz);
+    const size_t smem2 = ev::node_smem_bytes();
+    ev::eval_node_bwd_kernel<<<g2, ev::kThreads, smem2, st>>>(q, gk, gv, maskw, heads, lse_h, dheads, du_t, dd, dgk, dgv,
                                                                  dlkf, R, n_nodes);
     R4_CHECK_LAUNCH("eval_ll_bwd (node pass)");
     return RL4CO_OK;
