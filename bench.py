@@ -280,8 +280,9 @@ def train_leg(dev, rank, world, steps=8, warmup=3):
         ar_ms = a0.elapsed_time(a1) / 10
     step_ms = statistics.median(times)
     step_ms, = sharding.max_over_ranks([step_ms], device=dev)
-    return {"workload": "CVRP100 POMO REINFORCE step (multistart sampling S=100, shared baseline, backward, "
-                        "flat all-reduce, clip, Adam), 64 instances per GPU",
+    return {"workload": "CVRP100 POMO REINFORCE step (multistart sampling S=100 on the rollout kernel, teacher-forced "
+                        "log-likelihood forward + backward on rl4co_eval_ll_fwd / rl4co_eval_ll_bwd, shared baseline, "
+                        "encoder + table products in PyTorch autograd, flat all-reduce, clip, Adam), 64 instances per GPU",
             "ms_per_step": step_ms, "instances_per_s": world * B / (step_ms * 1e-3), "n_gpus": world,
             "allreduce_ms": ar_ms, "allreduce_bytes": 4 * (n_par + 3), "collectives_per_step": 1 if world > 1 else 0,
             "backend": "nccl" if world > 1 else None, "loss": stats["loss"], "reward": stats["reward"],

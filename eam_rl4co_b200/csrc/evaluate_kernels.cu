@@ -469,7 +469,7 @@ __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-constexpr int kTR = 32;   // rows per tile
+constexpr int kTR = 64;   // rows per tile (a CTA barrier per tile: 32-row tiles cost 4 % more)
 
 // [rows, 128] fp32 rows -> shared, linear (swz = false) or in the (chunk, head) order of copy_table_swz (swz = true)
 template <bool SWZ>

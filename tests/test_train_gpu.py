@@ -151,3 +151,43 @@ def test_fused_evaluate_rejects_unsupported_sizes():
     assert rc != 0 and b"n_nodes" in L.rl4co_last_error()
     h = torch.zeros(1, 120, 128, device=DEV)
     assert not train.fused_evaluate_supported(h, 120) and train.fused_evaluate_supported(h, 101)
+
+
+def _eager_rows(q, gk, gv, lkf, mask, taken, clip, temp):
+    """fp64 PyTorch statement of one evaluate row batch (attention.py:308-328, decoding.py:140-190,452-465)."""
+    B, R, E = q.shape
+    n = gk.shape[1]
+    H = 8
+    hd = lambda x, L: x.reshape(B, L, H, E // H).transpose(1, 2)
+    s = torch.matmul(hd(q, R), hd(gk, n).transpose(-1, -2)) / 4.0
+    s = s.masked_fill(~mask[:, None], float("-inf"))
+    o = torch.matmul(torch.softmax(s, -1), hd(gv, n)).transpose(1, 2).reshape(B, R, E)
+    u = torch.matmul(o, lkf.transpose(1, 2)) / (E ** 0.5)
+    z = (torch.tanh(u) * clip if clip > 0 else u).masked_fill(~mask, float("-inf")) / temp
+    return torch.log_softmax(z, -1).gather(-1, taken[..., None])[..., 0]
+
+
+@pytest.mark.parametrize("B,R,n,clip,temp", [(3, 37, 101, 10.0, 1.0), (2, 5, 2, 10.0, 1.0), (1, 1, 112, 0.0, 0.5),
+                                              (5, 130, 64, 10.0, 2.0), (70, 9, 21, 10.0, 1.0)])
+def test_fused_evaluate_rows_against_fp64(B, R, n, clip, temp):
+    """Ragged row counts (not a multiple of the four-row groups or of the CTA split), the smallest and largest node
+    counts, rows with a single feasible node, more instances than SMs / 2."""
+    g = torch.Generator().manual_seed(B * 1000 + R * 10 + n)
+    rnd = lambda *s: torch.randn(*s, generator=g)
+    q, gk, gv, lkf = rnd(B, R, 128), rnd(B, n, 128), rnd(B, n, 128), rnd(B, n, 128) * 0.3
+    mask = torch.rand(B, R, n, generator=g) < 0.4
+    taken = torch.randint(0, n, (B, R), generator=g)
+    mask[:, ::3] = False                                          # every third row: only the taken node is feasible
+    mask.scatter_(2, taken[..., None], True)
+    cot = rnd(B, R)
+    args64 = [t.double().to(DEV).requires_grad_(True) for t in (q, gk, gv, lkf)]
+    ref = _eager_rows(*args64, mask.to(DEV), taken.to(DEV), clip, temp)
+    (ref * cot.double().to(DEV)).sum().backward()
+    args32 = [t.to(DEV).requires_grad_(True) for t in (q, gk, gv, lkf)]
+    got = train._FusedEvaluate.apply(*args32, mask.to(DEV), taken.to(DEV), clip, temp)
+    (got * cot.to(DEV)).sum().backward()
+    assert (got.double() - ref).abs().max().item() < 2e-5 * max(1.0, ref.abs().max().item())
+    assert (got[:, ::3].abs() < 1e-6).all()                       # a single feasible node has probability one
+    for a32, a64, name in zip(args32, args64, ("q", "gk", "gv", "lkf")):
+        scale = max(a64.grad.abs().max().item(), 1e-6)
+        assert (a32.grad.double() - a64.grad).abs().max().item() / scale < 1e-4, name
