@@ -447,18 +447,22 @@ __global__ void __launch_bounds__(kThreads, 1)
 // ---- fused feed-forward block: Y[b] = Norm(X[b] + relu(X[b] W1^T + b1) W2^T + b2) (attnnet.py:50-60, nn/mlp.py) -----
 // The hidden activations (n x 512 fp32 = 205 KB per instance, written and read back by the two-kernel form) never
 // leave the SM.  Per 128-wide hidden block k:  M1(k): acc1[k&1] = X W1[k]^T  (24 MMAs, operands in shared memory);
-// the four epilogue warps drain acc1, add b1, apply relu, split to fp16 hi/lo and store the block as a TS-form A
-// operand in TMEM;  M2(k): out += A W2[:, k]^T (24 MMAs, A from TMEM).  The MMAs are issued in the order
-// M1(0) M1(1) M2(0) M1(2) M2(1) ... so that the tensor pipe works on M1(k+1) while the epilogue warps convert block k.
-// W tiles stream through the two 64 KB buffers in that same order.  TMEM: acc1 x 2 [0,256), A hi [256,320), A lo
-// [320,384), out [384,512).  The final residual + norm epilogue is the one of enc_linear_kernel.
+// the four epilogue warps drain acc1, add b1, apply relu, split to fp16 hi/lo and write the block back IN PLACE as a
+// TS-form A operand (16-column chunk c: hi pairs in [c, c+8), lo pairs in [c+8, c+16));  M2(k): out += A W2[:, k]^T
+// (24 MMAs, A from TMEM).  The MMAs are issued in the order M1(0) M1(1) M2(0) M1(2) M2(1) ... : the tensor pipe works on
+// M1(k+1) while block k is converted, block k+1 is converted (other buffer) while M2(k) runs, and M1(k+2) overwrites
+// acc1[k & 1] behind M2(k) in the pipe's issue order.  W tiles stream through the two 64 KB buffers in that same order.
+// TMEM: acc1 / A x 2 [0,256), out [256,384).  The final residual + norm epilogue is the one of enc_linear_kernel.
+//
+// Measured and NOT kept (profiles/r02_enc_ffn_phases.md): eight conversion warps + a ninth issuing warp, the X tile as a
+// TS-form A operand in TMEM (first GEMM without shared-memory A reads), a per-CTA rotation of the hidden-block order (L2
+// hot-spot test) - each left the kernel at 0.150 ms: it is bound by the 512 KB of W tiles every instance streams from L2
+// (~20 B/clk per SM with all SMs streaming, 9.5 k of 41 k cycles per instance exposed as W-tile waits).
 struct FfnSmem {
     uint64_t tma_bar[2];     // W tile landed in buffer i
     uint64_t wfree_bar[2];   // the MMAs reading W buffer i are complete
     uint64_t acc_full[2];    // M1 into acc1[i] is complete
-    uint64_t acc_free[2];    // the epilogue warps have drained acc1[i]            (128 arrivals)
-    uint64_t a_ready;        // the epilogue warps have written the A operand      (128 arrivals)
-    uint64_t a_free;         // the M2 reading the A operand is complete
+    uint64_t a_ready[2];     // the epilogue warps have converted acc1[i] in place into the A operand   (128 arrivals)
     uint64_t done_bar;       // every MMA of the instance is complete
     uint32_t tmem_ptr;
     uint32_t pad_;
@@ -473,14 +477,17 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 }
 
 // out (+)= A[tmem] W2tile^T : 8 k-steps x (hi*hi + hi*lo + lo*hi), A = 128 channels as fp16 pairs (64 + 64 columns)
+// A_STEP = TMEM columns between consecutive k-steps of the A operand: 8 (hi block [0,64) then lo block [64,128)) or 16
+// (k-step ks: hi at 16 ks, lo at 16 ks + 8 - the layout an accumulator converted IN PLACE has)
+template <uint32_t A_STEP = 8>
 __device__ __forceinline__ void issue_tile_ts(uint32_t dcol_addr, uint32_t a_hi, uint32_t a_lo, uint32_t ws, bool first) {
     const uint32_t id = idesc_f16(kRows, 128);
     uint64_t b_hi = smem_desc(ws, kLBO, kSBO), b_lo = smem_desc(ws + kHalf, kLBO, kSBO);
 #pragma unroll
     for (int ks = 0; ks < 8; ++ks) {
-        mma_ts(dcol_addr, a_hi + 8u * ks, b_hi, id, (first && ks == 0) ? 0u : 1u);
-        mma_ts(dcol_addr, a_hi + 8u * ks, b_lo, id, 1u);
-        mma_ts(dcol_addr, a_lo + 8u * ks, b_hi, id, 1u);
+        mma_ts(dcol_addr, a_hi + A_STEP * ks, b_hi, id, (first && ks == 0) ? 0u : 1u);
+        mma_ts(dcol_addr, a_hi + A_STEP * ks, b_lo, id, 1u);
+        mma_ts(dcol_addr, a_lo + A_STEP * ks, b_hi, id, 1u);
         b_hi += (2u * kLBO) >> 4;
         b_lo += (2u * kLBO) >> 4;
     }
@@ -501,10 +508,8 @@ __global__ void __launch_bounds__(kThreads, 1)
             mbar_init(&s->tma_bar[i], 1);
             mbar_init(&s->wfree_bar[i], 1);
             mbar_init(&s->acc_full[i], 1);
-            mbar_init(&s->acc_free[i], 128);
+            mbar_init(&s->a_ready[i], 128);
         }
-        mbar_init(&s->a_ready, 128);
-        mbar_init(&s->a_free, 1);
         mbar_init(&s->done_bar, 1);
         fence_mbar_init();
     }
@@ -517,12 +522,11 @@ __global__ void __launch_bounds__(kThreads, 1)
     const uint32_t xs_a = smem_u32(xs), ws_a = smem_u32(wsm);
     const bool producer = warp >= 4;
     const uint32_t lane_base = tmem + ((uint32_t)(32 * (warp & 3)) << 16);
-    constexpr uint32_t kColA = 256, kColOut = 384;
+    constexpr uint32_t kColOut = 256;   // [0,256): the two M1 accumulators, each converted in place into an A operand
     const int nSeq = 2 * nH;
     // completed-phase counters (identical in every thread; each role only uses its own)
-    uint32_t n_tma[2] = {0, 0}, n_wfree[2] = {0, 0}, n_full[2] = {0, 0}, n_free[2] = {0, 0};
-    uint32_t n_aready = 0, n_afree = 0, n_done = 0;
-    bool have_prev_m2 = false;     // epilogue warps: an earlier M2 (this or the previous instance) read the A operand
+    uint32_t n_tma[2] = {0, 0}, n_wfree[2] = {0, 0}, n_full[2] = {0, 0}, n_aready[2] = {0, 0};
+    uint32_t n_done = 0;
 #ifdef R4_ENC_PROF
     // g_enc_prof: [0] issuer: wait W tile, [1] wait acc_free, [2] wait a_ready, [3] wait wfree, [4] issue, [5] tail waits,
     // [6] wait done (all threads, thread 0), [7] final epilogue + conversion, [8] epilogue warps: wait acc_full,
@@ -558,23 +562,21 @@ __global__ void __launch_bounds__(kThreads, 1)
                     FFN_STAMP(0);
                     const bool is_m1 = (sq == 0) || ((sq & 1) && sq != nSeq - 1);
                     if (is_m1) {
+                        // acc1[k & 1] held the A operand of M2(k-2), issued before this M1: the tensor pipe keeps the order
                         const int k = (sq == 0) ? 0 : (sq + 1) >> 1;
-                        if (k >= 2) {             // acc1[k&1] was drained by the epilogue of block k-2
-                            mbar_wait(&s->acc_free[k & 1], n_free[k & 1] & 1u);
-                            ++n_free[k & 1];
-                        }
                         FFN_STAMP(1);
                         tc_fence_after();
                         issue_tile(tmem, (uint32_t)(k & 1) * 128u, xs_a, ws_a + (uint32_t)buf * kTile, true);
                         tc_commit(&s->acc_full[k & 1]);
                     } else {
                         const int k = (sq == nSeq - 1) ? nH - 1 : (sq >> 1) - 1;
-                        mbar_wait(&s->a_ready, n_aready & 1u);
-                        ++n_aready;
+                        mbar_wait(&s->a_ready[k & 1], n_aready[k & 1] & 1u);
+                        ++n_aready[k & 1];
                         FFN_STAMP(2);
                         tc_fence_after();
-                        issue_tile_ts(tmem + kColOut, tmem + kColA, tmem + kColA + 64u, ws_a + (uint32_t)buf * kTile, k == 0);
-                        tc_commit(&s->a_free);
+                        issue_tile_ts<16>(tmem + kColOut, tmem + (uint32_t)(k & 1) * 128u, tmem + (uint32_t)(k & 1) * 128u + 8u,
+                                          ws_a + (uint32_t)buf * kTile, k == 0);
+                        FFN_STAMP(6);                    // issue of an M2 (A from TMEM); [4] then holds the M1 issues
                     }
                     tc_commit(sq + 1 < nSeq ? &s->wfree_bar[buf] : &s->done_bar);
                     FFN_STAMP(4);
@@ -594,26 +596,18 @@ __global__ void __launch_bounds__(kThreads, 1)
                 // (by now they are all complete or about to be; the instance ends at done_bar)
                 mbar_wait(&s->wfree_bar[(nSeq - 2) & 1], n_wfree[(nSeq - 2) & 1] & 1u);
                 ++n_wfree[(nSeq - 2) & 1];
-                for (int k = (nH >= 2 ? nH - 2 : 0); k < nH; ++k) {
-                    mbar_wait(&s->acc_free[k & 1], n_free[k & 1] & 1u);
-                    ++n_free[k & 1];
-                }
                 FFN_STAMP(5);
             }
             __syncwarp();
         } else if (!producer) {
-            // the four epilogue warps: hidden block k -> relu -> A operand
+            // the four epilogue warps: hidden block k -> + b1 -> relu -> fp16 hi/lo A operand
             for (int k = 0; k < nH; ++k) {
                 mbar_wait(&s->acc_full[k & 1], n_full[k & 1] & 1u);
                 ++n_full[k & 1];
                 if (threadIdx.x == 0) { FFN_STAMP(8); }
-                if (have_prev_m2) {               // the M2 of the previous block has finished reading the A operand
-                    mbar_wait(&s->a_free, n_afree & 1u);
-                    ++n_afree;
-                }
-                have_prev_m2 = true;
-                if (threadIdx.x == 0) { FFN_STAMP(9); }
                 tc_fence_after();
+                // in place: chunk c (16 fp32 columns) -> hi pairs in [c, c+8), lo pairs in [c+8, c+16); M2(k) then reads
+                // this buffer while block k+1 is converted in the other one
                 const uint32_t src = lane_base + (uint32_t)(k & 1) * 128u;
 #pragma unroll 2
                 for (int c = 0; c < 128; c += 16) {
@@ -630,14 +624,12 @@ __global__ void __launch_bounds__(kThreads, 1)
                         split2(f0, f1, hi[i >> 1], lo[i >> 1]);
                         split2(f2, f3, hi[(i >> 1) + 1], lo[(i >> 1) + 1]);
                     }
-                    tmem_st8(lane_base + kColA + (uint32_t)(c >> 1), hi);
-                    tmem_st8(lane_base + kColA + 64u + (uint32_t)(c >> 1), lo);
+                    tmem_st8(src + (uint32_t)c, hi);
+                    tmem_st8(src + (uint32_t)c + 8u, lo);
                 }
-                tc_fence_before();
-                mbar_arrive(&s->acc_free[k & 1]);     // every load of acc1[k&1] has completed (tc_wait_ld above)
                 tc_wait_st();
                 tc_fence_before();
-                mbar_arrive(&s->a_ready);
+                mbar_arrive(&s->a_ready[k & 1]);
                 if (threadIdx.x == 0) { FFN_STAMP(10); }
             }
         }

@@ -13,8 +13,8 @@ mha, norm1, mlp, norm2 = layer[0].module, layer[1], layer[2].module, layer[3]
 x = torch.randn(B, n, 128, device=dev)
 L = _lib.lib()
 out = (C.c_longlong * 16)()
-names = ["issuer wait W tile", "issuer wait acc_free", "issuer wait a_ready", "issuer wait wfree", "issuer issue", "issuer tail waits",
-         "-", "final epilogue + next X (thread 0)", "epi wait acc_full", "epi wait a_free", "epi drain/relu/split/store"]
+names = ["issuer wait W tile", "issuer (unused)", "issuer wait a_ready", "issuer wait wfree", "issuer issue", "issuer tail waits",
+         "-", "final epilogue + next X (thread 0)", "epi wait acc_full", "conv (unused)", "epi drain/relu/split/store"]
 with torch.no_grad():
     net._ffn(x, mlp, norm2); torch.cuda.synchronize()
     L.rl4co_enc_debug_prof(out, 1)
