@@ -49,6 +49,16 @@ def test_argument_errors_return_codes_without_launching():
     rc = L.rl4co_decode_step(0, C.byref(cache), None, None, None, None, None, None, None, None,
                              C.c_int64(1), None)
     assert rc == -1 and b"embed_dim=128" in L.rl4co_last_error()
+    # the evaluate kernels check their arguments before any CUDA call
+    assert L.rl4co_eval_ll_max_nodes() == 112
+    rc = L.rl4co_eval_ll_fwd(None, None, None, None, None, None, None, None, None, None, None, C.c_int64(1), C.c_int64(1),
+                             C.c_int32(20), C.c_float(10.0), C.c_float(1.0), None)
+    assert rc == -1 and b"null pointer" in L.rl4co_last_error()
+    one = C.c_void_p(16)                                           # never dereferenced: the size checks come first
+    rc = L.rl4co_eval_ll_bwd(*([one] * 17), C.c_int64(2), C.c_int64(3), C.c_int32(200), C.c_float(10.0), C.c_float(1.0), None)
+    assert rc == -1 and b"n_nodes=200" in L.rl4co_last_error()
+    rc = L.rl4co_eval_ll_bwd(*([one] * 17), C.c_int64(2), C.c_int64(3), C.c_int32(50), C.c_float(10.0), C.c_float(0.0), None)
+    assert rc == -1 and b"temperature" in L.rl4co_last_error()
 
 
 def test_no_fallback_when_library_missing(monkeypatch):
