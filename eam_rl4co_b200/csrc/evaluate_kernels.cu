@@ -18,6 +18,7 @@
 // fp32 CUDA-core arithmetic; exp of the glimpse softmax on MUFU ex2 (as the tensor-path rollout), tanhf / expf / logf in the
 // pointer.
 #include "decode_core.cuh"
+#include "tc_ptx.cuh"
 
 namespace r4 {
 namespace ev {
@@ -445,12 +446,12 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
 }
 
-// ---- backward, node pass: the GEMM-shaped reductions over rows with the accumulators in REGISTERS -------------------------------
-// Warp w of the CTA owns nodes w, w + 16, ..., w + 96 and visits every row of the CTA's row range:
-//   blockIdx.z = 0 (pointer): dlkf[n] += du[row, n] heads[row]                          (dL = dU^T O)
-//   blockIdx.z = 1 (glimpse): P, dS of (row, its nodes) recomputed; dgv[n] += P dheads[row], dgk[n] += dS 0.25 q[row]
-// Lane L holds channels 4L..4L+3 of every accumulator; a CTA's sums reach global memory with one red per element.
-constexpr int kOwn = 7;   // 16 warps x 7 nodes = 112 = rl4co_eval_ll_max_nodes()
+// ---- backward, node pass: the GEMM-shaped reductions over ROWS ----------------------------------------------------------------
+//   dlkf = dU^T O                      : eval_dlk_tc_kernel, tcgen05 (below);
+//   dgv = P^T dO, dgk = dS^T (0.25 Q)  : eval_node_bwd_kernel, CUDA cores - P and dS of (row, head, node) are recomputed for the
+//     FEASIBLE (row, node) pairs only, with the accumulators in registers (a warp owns two nodes of a mask word and visits
+//     every row of the CTA's row range; a CTA's sums reach global memory with one red per element).
+constexpr int kMaxNodes = 112;   // four [n,128] fp32 tables in shared memory (row pass); du_t holds 128 columns
 
 // cp.async staging of row tiles: every warp of a node-pass CTA consumes the same rows, so a tile is fetched once per CTA
 // and read from shared memory (a first version in which each warp loaded its rows from global memory itself was bound by
@@ -483,9 +484,9 @@ __device__ __forceinline__ void stage_rows(float* dst, const float* __restrict__
 
 __global__ void __launch_bounds__(kThreads, 1)
     eval_node_bwd_kernel(const float* __restrict__ q, const float* __restrict__ gk, const float* __restrict__ gv,
-                         const uint32_t* __restrict__ maskw, const float* __restrict__ heads, const float* __restrict__ lse_h,
-                         const float* __restrict__ dheads, const float* __restrict__ du_t, const float* __restrict__ dd,
-                         float* __restrict__ dgk, float* __restrict__ dgv, float* __restrict__ dlkf, int64_t R, int n) {
+                         const uint32_t* __restrict__ maskw, const float* __restrict__ lse_h,
+                         const float* __restrict__ dheads, const float* __restrict__ dd, float* __restrict__ dgk,
+                         float* __restrict__ dgv, int64_t R, int n) {
     extern __shared__ __align__(16) float sm[];
     const int64_t b = blockIdx.x;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -493,67 +494,10 @@ __global__ void __launch_bounds__(kThreads, 1)
     row_range(R, r0, r1);
     if (r0 >= r1) return;
     const int ntiles = (int)((r1 - r0 + kTR - 1) / kTR);
-    if (blockIdx.z == 0) {
-        // pointer: warp w owns nodes w + 16 i (i < 7), lane L channels 4L..4L+3; du_t holds the warp's eight du values of a
-        // row contiguously.  Tiles: heads rows and du_t rows, two stages.
-        float* st_o[2] = {sm, sm + 2 * kTR * kE};
-        float* st_d[2] = {sm + kTR * kE, sm + 3 * kTR * kE};
-        const int off = 4 * lane;
-        float4 acc[kOwn];
-#pragma unroll
-        for (int i = 0; i < kOwn; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        auto issue = [&](int t) {
-            const int64_t rt = r0 + (int64_t)t * kTR;
-            const int rows = (int)(r1 - rt < kTR ? r1 - rt : kTR);
-            stage_rows<false>(st_o[t & 1], heads + (b * R + rt) * kE, rows);
-            stage_rows<false>(st_d[t & 1], du_t + (b * R + rt) * kE, rows);
-            cp_async_commit();
-        };
-        issue(0);
-        for (int t = 0; t < ntiles; ++t) {
-            if (t + 1 < ntiles) {
-                issue(t + 1);
-                cp_async_wait<1>();
-            } else {
-                cp_async_wait<0>();
-            }
-            __syncthreads();
-            const int64_t rt = r0 + (int64_t)t * kTR;
-            const int rows = (int)(r1 - rt < kTR ? r1 - rt : kTR);
-            const float* so = st_o[t & 1];
-            const float* sd = st_d[t & 1];
-#pragma unroll 4
-            for (int r = 0; r < rows; ++r) {
-                const float4 o4 = ld4(so + r * kE + off);
-                const float4 da = ld4(sd + r * kE + 8 * warp), db = ld4(sd + r * kE + 8 * warp + 4);
-                const float dn[8] = {da.x, da.y, da.z, da.w, db.x, db.y, db.z, db.w};
-#pragma unroll
-                for (int i = 0; i < kOwn; ++i) {
-                    acc[i].x = fmaf(dn[i], o4.x, acc[i].x);
-                    acc[i].y = fmaf(dn[i], o4.y, acc[i].y);
-                    acc[i].z = fmaf(dn[i], o4.z, acc[i].z);
-                    acc[i].w = fmaf(dn[i], o4.w, acc[i].w);
-                }
-            }
-            __syncthreads();   // the stage is refilled two tiles later
-        }
-#pragma unroll
-        for (int i = 0; i < kOwn; ++i) {
-            const int node = warp + 16 * i;
-            if (node < n) {
-                float* dst = dlkf + (b * n + node) * kE + off;
-                atomicAdd(dst + 0, acc[i].x);
-                atomicAdd(dst + 1, acc[i].y);
-                atomicAdd(dst + 2, acc[i].z);
-                atomicAdd(dst + 3, acc[i].w);
-            }
-        }
-        return;
-    }
     // glimpse, node quarter qd (the nodes of mask word qd): warp w owns nodes 32 qd + w and 32 qd + w + 16; lane = (row of
     // a four-row group, head) as in the row kernels, so P and dS of (row, head, node) cost two 16-FMA dot products and
     // the accumulators are 2 nodes x 2 tables x 16 channels per lane; the four row lanes are summed at the end.
-    const int qd = blockIdx.z - 1;
+    const int qd = blockIdx.z;
     if (32 * qd >= n) return;
     const int ri = lane >> 3, h = lane & 7;
     const int nq = n - 32 * qd < 32 ? n - 32 * qd : 32;
@@ -655,6 +599,138 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
 }
 
+// ---- backward, pointer part of the node pass on the tensor cores: dlkf[b] = dU^T O (tcgen05, split fp16) -------------------------
+// Per CTA a [128 x 128] fp32 accumulator in TMEM (rows = the 128 du_t columns, i.e. nodes in du_index order; columns = the 128
+// head channels), summed over the CTA's row tiles of 64 rows (the K dimension).  A tile of du_t and heads is staged as fp32
+// with cp.async (rows padded to 132 floats), converted by the CUDA cores into two K-major fp16 hi/lo operand tiles - the
+// conversion IS the transposition: a thread reads eight consecutive rows of one column and writes one 16-byte K chunk - and
+// multiplied with 12 MMAs (hi*hi + hi*lo + lo*hi, four k-steps).  0.45e9 FMA warp-instructions of the register version
+// become ~1.5 k conversion instructions per tile.
+namespace dlk {
+constexpr int kT = 64;                          // rows per tile = K of one tile product
+constexpr int kStride = 132;                    // staged fp32 row stride (floats)
+constexpr uint32_t kOpHalf = 16 * 1024;         // [128 rows][64 K] fp16: 16 row groups x (8 chunks x 128 B)
+constexpr uint32_t kOffStage = 4 * kOpHalf;     // A hi, A lo, B hi, B lo, then 2 stages x (du tile, heads tile)
+constexpr uint32_t kStageFloats = 2 * kT * kStride;
+constexpr uint32_t kOffBar = kOffStage + 2 * kStageFloats * 4;
+constexpr size_t kSmem = kOffBar + 64;
+}  // namespace dlk
+
+__global__ void __launch_bounds__(256, 1)
+    eval_dlk_tc_kernel(const float* __restrict__ heads, const float* __restrict__ du_t, float* __restrict__ dlkf, int64_t R,
+                       int n) {
+    using namespace tc;
+    extern __shared__ __align__(128) unsigned char smb[];
+    unsigned char* op = smb;
+    float* stage = reinterpret_cast<float*>(smb + dlk::kOffStage);
+    uint64_t* mma_bar = reinterpret_cast<uint64_t*>(smb + dlk::kOffBar);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smb + dlk::kOffBar + 16);
+    const int64_t b = blockIdx.x;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int64_t r0, r1;
+    row_range(R, r0, r1);
+    if (r0 >= r1) return;
+    const int ntiles = (int)((r1 - r0 + dlk::kT - 1) / dlk::kT);
+    if (threadIdx.x == 0) {
+        mbar_init(mma_bar, 1);
+        fence_mbar_init();
+    }
+    __syncwarp();
+    if (warp == 0) tmem_alloc(tmem_slot, 128);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    auto issue = [&](int t) {
+        const int64_t rt = r0 + (int64_t)t * dlk::kT;
+        const int rows = (int)(r1 - rt < dlk::kT ? r1 - rt : dlk::kT);
+        float* st = stage + (t & 1) * dlk::kStageFloats;
+        for (int i = threadIdx.x; i < rows * 32; i += blockDim.x) {
+            const int r = i >> 5, c4 = i & 31;
+            cp_async16(st + r * dlk::kStride + 4 * c4, du_t + (b * R + rt + r) * kE + 4 * c4);
+            cp_async16(st + (dlk::kT + r) * dlk::kStride + 4 * c4, heads + (b * R + rt + r) * kE + 4 * c4);
+        }
+        cp_async_commit();
+    };
+    uint32_t par = 0;
+    issue(0);
+    for (int t = 0; t < ntiles; ++t) {
+        if (t + 1 < ntiles) {
+            issue(t + 1);
+            cp_async_wait<1>();
+        } else {
+            cp_async_wait<0>();
+        }
+        __syncthreads();
+        if (t > 0) {                                     // the MMAs of tile t-1 have read the operand tiles
+            mbar_wait(mma_bar, par);
+            par ^= 1u;
+        }
+        const int64_t rt = r0 + (int64_t)t * dlk::kT;
+        const int rows = (int)(r1 - rt < dlk::kT ? r1 - rt : dlk::kT);
+        const float* st = stage + (t & 1) * dlk::kStageFloats;
+#pragma unroll 2
+        for (int j = 0; j < 8; ++j) {
+            const int i = threadIdx.x + 256 * j;         // item = (operand, 8-row group g, column m)
+            const int which = i >> 10, g = (i >> 7) & 7, m = i & 127;
+            const float* src = st + (which * dlk::kT + 8 * g) * dlk::kStride + m;
+            float v[8];
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk) v[kk] = (8 * g + kk < rows) ? src[kk * dlk::kStride] : 0.f;
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int w = 0; w < 4; ++w) split2(v[2 * w], v[2 * w + 1], hi[w], lo[w]);
+            unsigned char* dst = op + (uint32_t)which * 2u * dlk::kOpHalf + (uint32_t)(m >> 3) * 1024u + (uint32_t)g * 128u +
+                                 (uint32_t)(m & 7) * 16u;
+            *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(dst + dlk::kOpHalf) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        }
+        fence_proxy_async();
+        __syncthreads();
+        if (warp == 0) {
+            if (elect_one()) {
+                tc_fence_after();
+                const uint32_t id = idesc_f16(128, 128);
+                const uint32_t oa = smem_u32(op);
+                uint64_t a_hi = smem_desc(oa, 128, 1024), a_lo = smem_desc(oa + dlk::kOpHalf, 128, 1024);
+                uint64_t b_hi = smem_desc(oa + 2 * dlk::kOpHalf, 128, 1024), b_lo = smem_desc(oa + 3 * dlk::kOpHalf, 128, 1024);
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {
+                    mma_ss(tmem, a_hi, b_hi, id, (t == 0 && ks == 0) ? 0u : 1u);
+                    mma_ss(tmem, a_hi, b_lo, id, 1u);
+                    mma_ss(tmem, a_lo, b_hi, id, 1u);
+                    a_hi += 256u >> 4;
+                    a_lo += 256u >> 4;
+                    b_hi += 256u >> 4;
+                    b_lo += 256u >> 4;
+                }
+                tc_commit(mma_bar);
+            }
+            __syncwarp();
+        }
+    }
+    mbar_wait(mma_bar, par);
+    tc_fence_after();
+    {   // accumulator row m = du_t column m = node (m >> 3) + 16 (m & 7); one red per element
+        const int m = 32 * (warp & 3) + lane, node = (m >> 3) + 16 * (m & 7);
+        const uint32_t src = tmem + ((uint32_t)(32 * (warp & 3)) << 16) + 64u * (uint32_t)(warp >> 2);
+#pragma unroll 1
+        for (int c = 0; c < 64; c += 16) {
+            uint32_t v[16];
+            tmem_ld16(src + (uint32_t)c, v);
+            tc_wait_ld();
+            if (node < n) {
+                float* dst = dlkf + (b * n + node) * kE + 64 * (warp >> 2) + c;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) atomicAdd(dst + i, __uint_as_float(v[i]));
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, 128);
+}
+
 // node pass: two [32,128] table quarters + two stages of (q, dheads, lse_h, dd, mask word) tiles; the pointer part (two stages
 // of two row tiles) needs less
 static size_t node_smem_bytes() {
@@ -695,7 +771,7 @@ static int set_smem(K kern, size_t bytes, const char* who) {
 
 using namespace r4;
 
-extern "C" int32_t rl4co_eval_ll_max_nodes(void) { return 16 * ev::kOwn; }   // 112: node pass = 16 warps x 7 nodes
+extern "C" int32_t rl4co_eval_ll_max_nodes(void) { return ev::kMaxNodes; }
 
 static int eval_check(const char* who, int64_t B, int64_t R, int32_t n_nodes, float temperature) {
     R4_CHECK_ARG(B >= 0 && R >= 0 && B <= 65535, "%s: bad sizes B=%lld R=%lld", who, (long long)B, (long long)R);
@@ -747,12 +823,15 @@ extern "C" int rl4co_eval_ll_bwd(const float* q, const float* gk, const float* g
     ev::eval_row_bwd_glimpse_kernel<<<g1, ev::kThreads, 2 * table, st>>>(q, gk, gv, maskw, heads, lse_h, dheads, dq, dd, R,
                                                                         n_nodes);
     R4_CHECK_LAUNCH("eval_ll_bwd (row pass)");
-    // pointer part (z = 0) and the glimpse part's node quarters (z = 1 + mask word) share one grid
-    const unsigned nz = 1u + (unsigned)((n_nodes + 31) / 32);
+    // node pass: dlkf = dU^T O on the tensor cores; the glimpse part's node quarters (z = mask word) on the CUDA cores
+    if ((rc = ev::set_smem(ev::eval_dlk_tc_kernel, ev::dlk::kSmem, "eval_ll_bwd (dlkf)"))) return rc;
+    dim3 g3((unsigned)B, (unsigned)ev::grid_split(B, 1));
+    ev::eval_dlk_tc_kernel<<<g3, 256, ev::dlk::kSmem, st>>>(heads, du_t, dlkf, R, n_nodes);
+    R4_CHECK_LAUNCH("eval_ll_bwd (dlkf)");
+    const unsigned nz = (unsigned)((n_nodes + 31) / 32);
     dim3 g2((unsigned)B, (unsigned)ev::grid_split(nz * B, 1), nz);
     const size_t smem2 = ev::node_smem_bytes();
-    ev::eval_node_bwd_kernel<<<g2, ev::kThreads, smem2, st>>>(q, gk, gv, maskw, heads, lse_h, dheads, du_t, dd, dgk, dgv,
-                                                                 dlkf, R, n_nodes);
+    ev::eval_node_bwd_kernel<<<g2, ev::kThreads, smem2, st>>>(q, gk, gv, maskw, lse_h, dheads, dd, dgk, dgv, R, n_nodes);
     R4_CHECK_LAUNCH("eval_ll_bwd (node pass)");
     return RL4CO_OK;
 }
