@@ -10,13 +10,13 @@
 //            temperature, log_softmax, gather at the taken action.
 // Only FEASIBLE nodes are visited (masked nodes have probability exactly 0 in both softmaxes and contribute no gradient).
 // The backward recomputes the probabilities from the saved log-sum-exps (flash-attention style) in two passes:
-//   row pass  (a warp per row)            : dheads, dq and du = d loss / d raw logit - everything that reduces over NODES;
-//   node pass (a warp per 7 nodes, all rows): dgk = dS^T Q, dgv = P^T dO, dlkf = dU^T O - the reductions over ROWS, with the
-//             accumulators in registers (fp32 shared-memory atomics are CAS loops on sm_100: a first version that
-//             accumulated the table gradients in shared memory spent 25 of 31 ms of the c5 evaluate in ATOMS.CAST.SPIN).
+//   row pass  (CUDA cores, a warp per four rows): dheads, dq and du = d loss / d raw logit - everything that reduces over NODES;
+//   node pass (tcgen05)                         : dgk = dS^T Q, dgv = P^T dO, dlkf = dU^T O - the reductions over ROWS as MMAs with
+//             split-fp16 operands and fp32 accumulators that stay in TMEM across a CTA's row tiles.  (fp32 shared-memory
+//             atomics are CAS loops on sm_100: a first version that accumulated the table gradients in shared memory spent
+//             25 of 31 ms of the c5 evaluate in ATOMS.CAST.SPIN.)
 //
-// fp32 CUDA-core arithmetic; exp of the glimpse softmax on MUFU ex2 (as the tensor-path rollout), tanhf / expf / logf in the
-// pointer.
+// exp of the glimpse softmax on MUFU ex2 (as the tensor-path rollout), tanhf / expf / logf in the pointer.
 #include "decode_core.cuh"
 #include "tc_ptx.cuh"
 
@@ -446,157 +446,22 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
 }
 
-// ---- backward, node pass: the GEMM-shaped reductions over ROWS ----------------------------------------------------------------
-//   dlkf = dU^T O                      : eval_dlk_tc_kernel, tcgen05 (below);
-//   dgv = P^T dO, dgk = dS^T (0.25 Q)  : eval_node_bwd_kernel, CUDA cores - P and dS of (row, head, node) are recomputed for the
-//     FEASIBLE (row, node) pairs only, with the accumulators in registers (a warp owns two nodes of a mask word and visits
-//     every row of the CTA's row range; a CTA's sums reach global memory with one red per element).
+// ---- backward, node pass: the GEMM-shaped reductions over ROWS, on tcgen05 ---------------------------------------------------------
+//   dlkf = dU^T O                      : eval_dlk_tc_kernel;
+//   dgv = P^T dO, dgk = dS^T (0.25 Q)  : eval_dkv_tc_kernel (transposed score tiles, P^T / dS^T as TS-form A operands in TMEM).
+// (Round-2 history: a CUDA-core node pass with register accumulators - a warp per two nodes visiting every row, row tiles
+// staged with cp.async - took 4.3 ms for the three reductions; the two tensor-core kernels take 0.23 + 1.9 ms.)
 constexpr int kMaxNodes = 112;   // four [n,128] fp32 tables in shared memory (row pass); du_t holds 128 columns
 
-// cp.async staging of row tiles: every warp of a node-pass CTA consumes the same rows, so a tile is fetched once per CTA
-// and read from shared memory (a first version in which each warp loaded its rows from global memory itself was bound by
-// one L2 round trip per row group and warp: 6.3 of 11.7 ms of the backward).
+// cp.async staging of row tiles (eval_dlk_tc_kernel)
 __device__ __forceinline__ void cp_async16(void* dst, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src)
-                 : "memory");
-}
-__device__ __forceinline__ void cp_async4(void* dst, const void* src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src)
                  : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-
-constexpr int kTR = 64;   // rows per tile (a CTA barrier per tile: 32-row tiles cost 4 % more)
-
-// [rows, 128] fp32 rows -> shared, linear (swz = false) or in the (chunk, head) order of copy_table_swz (swz = true)
-template <bool SWZ>
-__device__ __forceinline__ void stage_rows(float* dst, const float* __restrict__ src, int rows) {
-    for (int i = threadIdx.x; i < rows * 32; i += blockDim.x) {
-        const int r = i >> 5, c4 = i & 31;
-        const int d = SWZ ? r * 32 + (c4 & 3) * 8 + (c4 >> 2) : i;
-        cp_async16(dst + 4 * d, src + 4 * i);
-    }
-}
-
-__global__ void __launch_bounds__(kThreads, 1)
-    eval_node_bwd_kernel(const float* __restrict__ q, const float* __restrict__ gk, const float* __restrict__ gv,
-                         const uint32_t* __restrict__ maskw, const float* __restrict__ lse_h,
-                         const float* __restrict__ dheads, const float* __restrict__ dd, float* __restrict__ dgk,
-                         float* __restrict__ dgv, int64_t R, int n) {
-    extern __shared__ __align__(16) float sm[];
-    const int64_t b = blockIdx.x;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int64_t r0, r1;
-    row_range(R, r0, r1);
-    if (r0 >= r1) return;
-    const int ntiles = (int)((r1 - r0 + kTR - 1) / kTR);
-    // glimpse, node quarter qd (the nodes of mask word qd): warp w owns nodes 32 qd + w and 32 qd + w + 16; lane = (row of
-    // a four-row group, head) as in the row kernels, so P and dS of (row, head, node) cost two 16-FMA dot products and
-    // the accumulators are 2 nodes x 2 tables x 16 channels per lane; the four row lanes are summed at the end.
-    const int qd = blockIdx.z;
-    if (32 * qd >= n) return;
-    const int ri = lane >> 3, h = lane & 7;
-    const int nq = n - 32 * qd < 32 ? n - 32 * qd : 32;
-    float* s_gk = sm;
-    float* s_gv = sm + 32 * kE;
-    float* base = sm + 64 * kE;
-    constexpr int kStage = 2 * kTR * kE + 2 * kTR * kH + kTR;     // q, dheads, lse_h, dd, mask word
-    auto st_q = [&](int st) { return base + st * kStage; };
-    auto st_dh = [&](int st) { return base + st * kStage + kTR * kE; };
-    auto st_lh = [&](int st) { return base + st * kStage + 2 * kTR * kE; };
-    auto st_dd = [&](int st) { return base + st * kStage + 2 * kTR * kE + kTR * kH; };
-    auto st_mw = [&](int st) { return reinterpret_cast<uint32_t*>(base + st * kStage + 2 * kTR * kE + 2 * kTR * kH); };
-    copy_table_swz(s_gk, gk + (b * n + 32 * qd) * kE, nq);
-    copy_table_swz(s_gv, gv + (b * n + 32 * qd) * kE, nq);
-    auto issue = [&](int t) {
-        const int64_t rt = r0 + (int64_t)t * kTR;
-        const int rows = (int)(r1 - rt < kTR ? r1 - rt : kTR);
-        const int st = t & 1;
-        stage_rows<true>(st_q(st), q + (b * R + rt) * kE, rows);
-        stage_rows<true>(st_dh(st), dheads + (b * R + rt) * kE, rows);
-        for (int i = threadIdx.x; i < rows * 2; i += blockDim.x) {
-            cp_async16(st_lh(st) + 4 * i, lse_h + (b * R + rt) * kH + 4 * i);
-            cp_async16(st_dd(st) + 4 * i, dd + (b * R + rt) * kH + 4 * i);
-        }
-        if (threadIdx.x < rows) cp_async4(st_mw(st) + threadIdx.x, maskw + (b * R + rt + threadIdx.x) * kNB + qd);
-        cp_async_commit();
-    };
-    float ak[2][16], av[2][16];
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-#pragma unroll
-        for (int c = 0; c < 16; ++c) {
-            ak[i][c] = 0.f;
-            av[i][c] = 0.f;
-        }
-    }
-    issue(0);
-    for (int t = 0; t < ntiles; ++t) {
-        if (t + 1 < ntiles) {
-            issue(t + 1);
-            cp_async_wait<1>();
-        } else {
-            cp_async_wait<0>();
-        }
-        __syncthreads();                                 // also covers the tables on the first tile
-        const int64_t rt = r0 + (int64_t)t * kTR;
-        const int rows = (int)(r1 - rt < kTR ? r1 - rt : kTR);
-        const int st = t & 1;
-#pragma unroll 1
-        for (int g = 0; g < rows; g += 4) {
-            const int r = g + ri;
-            const uint32_t wq = r < rows ? st_mw(st)[r] : 0u;
-            const bool f0 = (wq >> warp) & 1u, f1 = (wq >> (warp + 16)) & 1u;
-            const bool any0 = __any_sync(kFull, f0), any1 = __any_sync(kFull, f1);
-            if (!(any0 || any1)) continue;
-            const int rc = r < rows ? r : rows - 1;
-            float qs[16], dh[16];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float4 a4 = ld4(st_q(st) + rc * kE + 32 * i + 4 * h);
-                const float4 d4 = ld4(st_dh(st) + rc * kE + 32 * i + 4 * h);
-                qs[4 * i] = a4.x * 0.25f, qs[4 * i + 1] = a4.y * 0.25f, qs[4 * i + 2] = a4.z * 0.25f;
-                qs[4 * i + 3] = a4.w * 0.25f;
-                dh[4 * i] = d4.x, dh[4 * i + 1] = d4.y, dh[4 * i + 2] = d4.z, dh[4 * i + 3] = d4.w;
-            }
-            const float lh = st_lh(st)[rc * kH + h], dv = st_dd(st)[rc * kH + h];
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                if (!(i ? any1 : any0)) continue;        // warp-uniform
-                const int nd = warp + 16 * i;
-                const float sv = dot16(qs, s_gk + nd * kE + 4 * h);
-                const float dp = dot16(dh, s_gv + nd * kE + 4 * h);
-                const float p = (i ? f1 : f0) ? fexp(sv - lh) : 0.f;
-                const float ds = p * (dp - dv);
-#pragma unroll
-                for (int c = 0; c < 16; ++c) {
-                    ak[i][c] = fmaf(ds, qs[c], ak[i][c]);
-                    av[i][c] = fmaf(p, dh[c], av[i][c]);
-                }
-            }
-        }
-        __syncthreads();   // the stage is refilled two tiles later
-    }
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        const int node = 32 * qd + warp + 16 * i;
-#pragma unroll
-        for (int c = 0; c < 16; ++c) {
-            float a = ak[i][c], v = av[i][c];
-            a += __shfl_xor_sync(kFull, a, 8);
-            v += __shfl_xor_sync(kFull, v, 8);
-            a += __shfl_xor_sync(kFull, a, 16);
-            v += __shfl_xor_sync(kFull, v, 16);
-            if (ri == 0 && node < n) {
-                atomicAdd(dgk + (b * n + node) * kE + 16 * h + c, a);
-                atomicAdd(dgv + (b * n + node) * kE + 16 * h + c, v);
-            }
-        }
-    }
 }
 
 // ---- backward, pointer part of the node pass on the tensor cores: dlkf[b] = dU^T O (tcgen05, split fp16) -------------------------
@@ -731,10 +596,292 @@ __global__ void __launch_bounds__(256, 1)
     if (warp == 0) tmem_dealloc(tmem, 128);
 }
 
-// node pass: two [32,128] table quarters + two stages of (q, dheads, lse_h, dd, mask word) tiles; the pointer part (two stages
-// of two row tiles) needs less
-static size_t node_smem_bytes() {
-    return (size_t)(64 * kE + 2 * (2 * kTR * kE + 2 * kTR * kH + kTR)) * sizeof(float);
+// ---- backward, glimpse part of the node pass on the tensor cores: dgk = dS^T (0.25 Q), dgv = P^T dO ------------------------------
+// The TRANSPOSED score tile is computed so that P^T and dS^T come out with TMEM lane = node, which is the M dimension the two
+// reductions over rows need (the flash-attention backward arrangement).  Per CTA (instance, row range), per tile of 128 rows,
+// per head h:
+//   S^T  = K_h (0.25 Q_h)^T   [nodes x rows]   3 MMAs (split fp16), A = K_h tile (resident), B = Q_h tile   -> TMEM [0,128)
+//   dP^T = V_h dO_h^T          [nodes x rows]   3 MMAs,              A = V_h tile (resident), B = dO_h tile  -> TMEM [128,256)
+//   thread (node, 64 of the tile's rows): P^T = exp(S^T - lse_h[row]) on the feasible (row, node) pairs, dS^T = P^T (dP^T - D_h[row]),
+//     both written back IN PLACE as fp16 hi/lo TS-form A operands (16-column chunk: hi pairs [c, c+8), lo pairs [c+8, c+16))
+//   dgv_h += P^T dO_h, dgk_h += dS^T (0.25 Q_h): 2 x 24 TS-form MMAs (N = 16, K = the tile's 128 rows) into TMEM [256 + 32 h, +32)
+// The accumulators of the 8 heads (256 columns) live in TMEM across all row tiles of the CTA.  The B operands of the second
+// pair of products are the transposed head slices, produced by the same transposing conversion as in eval_dlk_tc_kernel.
+namespace dkv {
+constexpr int kT = 128;                         // rows per tile
+constexpr uint32_t kHeadTile = 4096;            // [128 x 16] fp16, K-major: 16 row groups x 2 chunks x 128 B (hi or lo)
+constexpr uint32_t kOffK = 0;                   // K_h hi | lo for 8 heads: 8 x 8 KB
+constexpr uint32_t kOffV = 8 * 2 * kHeadTile;   // 64 KB
+constexpr uint32_t kOffBq = 2 * kOffV;          // 128 KB: Q_h tile hi | lo   (B of S^T: N = rows, K = 16)
+constexpr uint32_t kOffBdo = kOffBq + 2 * kHeadTile;
+constexpr uint32_t kOffBqT = kOffBdo + 2 * kHeadTile;   // Q_h^T hi | lo: [16 dims x 128 rows], 2 row groups x 16 chunks
+constexpr uint32_t kOffBdoT = kOffBqT + 2 * kHeadTile;
+constexpr uint32_t kOffStage = kOffBdoT + 2 * kHeadTile;   // fp32 head slices [2][128][17]
+constexpr uint32_t kStagePitch = 17;
+constexpr uint32_t kOffLse = kOffStage + 2 * kT * kStagePitch * 4;   // [8][128] f32 (head-major)
+constexpr uint32_t kOffDd = kOffLse + 8 * kT * 4;
+constexpr uint32_t kOffMaskW = kOffDd + 8 * kT * 4;                  // [128 rows][4] u32
+constexpr uint32_t kOffColMask = kOffMaskW + kT * 16;                // [128 nodes][4] u32: bit r of word j = row 32 j + r feasible
+constexpr uint32_t kOffBar = kOffColMask + kT * 16;
+constexpr size_t kSmem = kOffBar + 64;
+}  // namespace dkv
+
+__global__ void __launch_bounds__(256, 1)
+    eval_dkv_tc_kernel(const float* __restrict__ q, const float* __restrict__ gk, const float* __restrict__ gv,
+                       const uint32_t* __restrict__ maskw, const float* __restrict__ lse_h, const float* __restrict__ dheads,
+                       const float* __restrict__ dd, float* __restrict__ dgk, float* __restrict__ dgv, int64_t R, int n) {
+    using namespace tc;
+    extern __shared__ __align__(128) unsigned char smb[];
+    float* stage = reinterpret_cast<float*>(smb + dkv::kOffStage);
+    float* s_lse = reinterpret_cast<float*>(smb + dkv::kOffLse);
+    float* s_dd = reinterpret_cast<float*>(smb + dkv::kOffDd);
+    uint32_t* s_mw = reinterpret_cast<uint32_t*>(smb + dkv::kOffMaskW);
+    uint32_t* s_cm = reinterpret_cast<uint32_t*>(smb + dkv::kOffColMask);
+    uint64_t* bar1 = reinterpret_cast<uint64_t*>(smb + dkv::kOffBar);
+    uint64_t* bar2 = bar1 + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smb + dkv::kOffBar + 32);
+    const int64_t b = blockIdx.x;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    int64_t r0, r1;
+    row_range(R, r0, r1);
+    if (r0 >= r1) return;
+    const int ntiles = (int)((r1 - r0 + dkv::kT - 1) / dkv::kT);
+    if (tid == 0) {
+        mbar_init(bar1, 1);
+        mbar_init(bar2, 1);
+        fence_mbar_init();
+    }
+    __syncwarp();
+    if (warp == 0) tmem_alloc(tmem_slot, 512);
+    // resident A operands: K_h and V_h of the 8 heads, [128 nodes x 16 dims] K-major hi | lo (nodes >= n are zero rows)
+    for (int i = tid; i < 2 * 8 * 128 * 2; i += 256) {
+        const int tab = i >> 11, h = (i >> 8) & 7, m = (i >> 1) & 127, c = i & 1;
+        const float* src = (tab ? gv : gk) + ((size_t)b * n + m) * kE + 16 * h + 8 * c;
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a;
+        if (m < n) {
+            a = ld4(src);
+            bb = ld4(src + 4);
+        }
+        uint32_t hi[4], lo[4];
+        split2(a.x, a.y, hi[0], lo[0]);
+        split2(a.z, a.w, hi[1], lo[1]);
+        split2(bb.x, bb.y, hi[2], lo[2]);
+        split2(bb.z, bb.w, hi[3], lo[3]);
+        unsigned char* dst = smb + (tab ? dkv::kOffV : dkv::kOffK) + (uint32_t)h * 2u * dkv::kHeadTile + (uint32_t)(m >> 3) * 256u +
+                             (uint32_t)c * 128u + (uint32_t)(m & 7) * 16u;
+        *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(dst + dkv::kHeadTile) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t sb = smem_u32(smb);
+    const int q4 = warp & 3, chalf = warp >> 2;          // TMEM lane quadrant (node = 32 q4 + lane), row half of the tile
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * q4) << 16);
+    uint32_t p1 = 0, p2 = 0;
+    bool mma2_pending = false;
+    for (int t = 0; t < ntiles; ++t) {
+        const int64_t rt = r0 + (int64_t)t * dkv::kT;
+        const int rows = (int)(r1 - rt < dkv::kT ? r1 - rt : dkv::kT);
+        // per-row vectors of the tile: lse and D head-major, mask words (zero beyond the valid rows)
+        for (int i = tid; i < dkv::kT * 8; i += 256) {
+            const int r = i >> 3, h = i & 7;
+            const bool ok = r < rows;
+            s_lse[h * dkv::kT + r] = ok ? lse_h[(b * R + rt + r) * kH + h] : 0.f;
+            s_dd[h * dkv::kT + r] = ok ? dd[(b * R + rt + r) * kH + h] : 0.f;
+        }
+        for (int i = tid; i < dkv::kT * 4; i += 256) s_mw[i] = (i >> 2) < rows ? maskw[(b * R + rt) * kNB + i] : 0u;
+        __syncthreads();
+        // feasibility transposed to (node, 32-row word): warp w takes row word w & 3 and nodes [64 (w >> 2), +64)
+        {
+            const int j = warp & 3;
+            uint32_t mw[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) mw[k] = s_mw[(32 * j + lane) * 4 + k];
+            for (int nd = 64 * (warp >> 2); nd < 64 * (warp >> 2) + 64; ++nd) {
+                const uint32_t word = (nd >> 5) == 0 ? mw[0] : ((nd >> 5) == 1 ? mw[1] : ((nd >> 5) == 2 ? mw[2] : mw[3]));
+                const uint32_t bal = __ballot_sync(kFull, (word >> (nd & 31)) & 1u);
+                if (lane == 0) s_cm[nd * 4 + j] = bal;
+            }
+        }
+        __syncthreads();
+        const int node = 32 * q4 + lane;
+        const uint32_t cm0 = s_cm[node * 4 + 2 * chalf], cm1 = s_cm[node * 4 + 2 * chalf + 1];   // this thread's 64 rows
+        // fp32 head slices of q and dheads of the tile's rows: loaded into registers one head ahead (the loads of head h + 1
+        // fly under the MMAs and the elementwise pass of head h), then staged as [128][17]
+        float4 pre[4];
+        auto prefetch = [&](int h) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int i = tid + 256 * k;
+                const int which = i >> 9, r = (i >> 2) & 127, c4 = i & 3;
+                pre[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (r < rows) pre[k] = ld4((which ? dheads : q) + (b * R + rt + r) * kE + 16 * h + 4 * c4);
+            }
+        };
+        prefetch(0);
+        for (int h = 0; h < kH; ++h) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int i = tid + 256 * k;
+                const int which = i >> 9, r = (i >> 2) & 127, c4 = i & 3;
+                float* d = stage + (which * dkv::kT + r) * dkv::kStagePitch + 4 * c4;
+                d[0] = pre[k].x, d[1] = pre[k].y, d[2] = pre[k].z, d[3] = pre[k].w;
+            }
+            if (h + 1 < kH) prefetch(h + 1);
+            // (double-buffering these four operand tiles over consecutive heads was measured: 2.03 against 1.88 ms)
+            if (mma2_pending) {                          // the TS MMAs of the previous head have read BqT / BdoT (and Bq / Bdo)
+                mbar_wait(bar2, p2);
+                p2 ^= 1u;
+                mma2_pending = false;
+            }
+            __syncthreads();
+            // K-major operand tiles: (a) [rows x 16] for the S^T / dP^T products, (b) transposed [16 x rows] for dgk / dgv
+            {
+                const int which = tid >> 7, r = tid & 127;                       // (a): thread = (tensor, row), two 8-dim chunks
+                const float sc = which ? 1.0f : 0.25f;
+                const float* src = stage + (which * dkv::kT + r) * dkv::kStagePitch;
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t hi[4], lo[4];
+#pragma unroll
+                    for (int w = 0; w < 4; ++w) split2(src[8 * c + 2 * w] * sc, src[8 * c + 2 * w + 1] * sc, hi[w], lo[w]);
+                    unsigned char* dst = smb + (which ? dkv::kOffBdo : dkv::kOffBq) + (uint32_t)(r >> 3) * 256u +
+                                         (uint32_t)c * 128u + (uint32_t)(r & 7) * 16u;
+                    *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                    *reinterpret_cast<uint4*>(dst + dkv::kHeadTile) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                }
+            }
+#pragma unroll
+            for (int jj = 0; jj < 2; ++jj) {                                     // (b): item = (tensor, 8-row group g, dim)
+                const int i = tid + 256 * jj;
+                const int which = i >> 8, g = (i >> 4) & 15, dm = i & 15;
+                const float sc = which ? 1.0f : 0.25f;
+                const float* src = stage + (which * dkv::kT + 8 * g) * dkv::kStagePitch + dm;
+                uint32_t hi[4], lo[4];
+#pragma unroll
+                for (int w = 0; w < 4; ++w)
+                    split2(src[(2 * w) * dkv::kStagePitch] * sc, src[(2 * w + 1) * dkv::kStagePitch] * sc, hi[w], lo[w]);
+                unsigned char* dst = smb + (which ? dkv::kOffBdoT : dkv::kOffBqT) + (uint32_t)(dm >> 3) * 2048u +
+                                     (uint32_t)g * 128u + (uint32_t)(dm & 7) * 16u;
+                *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4*>(dst + dkv::kHeadTile) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            }
+            fence_proxy_async();
+            __syncthreads();
+            if (warp == 0) {
+                if (elect_one()) {
+                    tc_fence_after();
+                    const uint32_t id = idesc_f16(128, 128);
+                    const uint64_t k_hi = smem_desc(sb + dkv::kOffK + (uint32_t)h * 2u * dkv::kHeadTile, 128, 256);
+                    const uint64_t k_lo = smem_desc(sb + dkv::kOffK + (uint32_t)h * 2u * dkv::kHeadTile + dkv::kHeadTile, 128, 256);
+                    const uint64_t v_hi = smem_desc(sb + dkv::kOffV + (uint32_t)h * 2u * dkv::kHeadTile, 128, 256);
+                    const uint64_t v_lo = smem_desc(sb + dkv::kOffV + (uint32_t)h * 2u * dkv::kHeadTile + dkv::kHeadTile, 128, 256);
+                    const uint64_t q_hi = smem_desc(sb + dkv::kOffBq, 128, 256);
+                    const uint64_t q_lo = smem_desc(sb + dkv::kOffBq + dkv::kHeadTile, 128, 256);
+                    const uint64_t o_hi = smem_desc(sb + dkv::kOffBdo, 128, 256);
+                    const uint64_t o_lo = smem_desc(sb + dkv::kOffBdo + dkv::kHeadTile, 128, 256);
+                    mma_ss(tmem, k_hi, q_hi, id, 0u);                            // S^T
+                    mma_ss(tmem, k_hi, q_lo, id, 1u);
+                    mma_ss(tmem, k_lo, q_hi, id, 1u);
+                    mma_ss(tmem + 128u, v_hi, o_hi, id, 0u);                     // dP^T
+                    mma_ss(tmem + 128u, v_hi, o_lo, id, 1u);
+                    mma_ss(tmem + 128u, v_lo, o_hi, id, 1u);
+                    tc_commit(bar1);
+                }
+                __syncwarp();
+            }
+            mbar_wait(bar1, p1);
+            p1 ^= 1u;
+            tc_fence_after();
+            // thread = (node, rows [64 chalf, +64) of the tile): P^T and dS^T in place
+#pragma unroll 1
+            for (int c = 0; c < 64; c += 16) {
+                const int col = 64 * chalf + c;
+                uint32_t sv[16], dv[16];
+                tmem_ld16(lane_base + (uint32_t)col, sv);
+                tmem_ld16(lane_base + 128u + (uint32_t)col, dv);
+                tc_wait_ld();
+                const uint32_t bits = ((c < 32 ? cm0 : cm1) >> (c & 31)) & 0xffffu;
+                uint32_t phi[8], plo[8], dhi[8], dlo[8];
+#pragma unroll
+                for (int i = 0; i < 16; i += 4) {
+                    const float4 l4 = ld4(s_lse + h * dkv::kT + col + i), d4 = ld4(s_dd + h * dkv::kT + col + i);
+                    const float pa = (bits >> i) & 1u ? fexp(__uint_as_float(sv[i]) - l4.x) : 0.f;
+                    const float pb = (bits >> (i + 1)) & 1u ? fexp(__uint_as_float(sv[i + 1]) - l4.y) : 0.f;
+                    const float pc = (bits >> (i + 2)) & 1u ? fexp(__uint_as_float(sv[i + 2]) - l4.z) : 0.f;
+                    const float pd = (bits >> (i + 3)) & 1u ? fexp(__uint_as_float(sv[i + 3]) - l4.w) : 0.f;
+                    split2(pa, pb, phi[i >> 1], plo[i >> 1]);
+                    split2(pc, pd, phi[(i >> 1) + 1], plo[(i >> 1) + 1]);
+                    split2(pa * (__uint_as_float(dv[i]) - d4.x), pb * (__uint_as_float(dv[i + 1]) - d4.y), dhi[i >> 1], dlo[i >> 1]);
+                    split2(pc * (__uint_as_float(dv[i + 2]) - d4.z), pd * (__uint_as_float(dv[i + 3]) - d4.w), dhi[(i >> 1) + 1],
+                           dlo[(i >> 1) + 1]);
+                }
+                tmem_st8(lane_base + (uint32_t)col, phi);
+                tmem_st8(lane_base + (uint32_t)col + 8u, plo);
+                tmem_st8(lane_base + 128u + (uint32_t)col, dhi);
+                tmem_st8(lane_base + 128u + (uint32_t)col + 8u, dlo);
+            }
+            tc_wait_st();
+            tc_fence_before();
+            __syncthreads();
+            if (warp == 0) {
+                if (elect_one()) {
+                    tc_fence_after();
+                    const uint32_t id = idesc_f16(128, 16);
+                    uint64_t ot_hi = smem_desc(sb + dkv::kOffBdoT, 128, 2048);
+                    uint64_t ot_lo = smem_desc(sb + dkv::kOffBdoT + dkv::kHeadTile, 128, 2048);
+                    uint64_t qt_hi = smem_desc(sb + dkv::kOffBqT, 128, 2048);
+                    uint64_t qt_lo = smem_desc(sb + dkv::kOffBqT + dkv::kHeadTile, 128, 2048);
+                    const uint32_t dv_col = tmem + 256u + 32u * (uint32_t)h, dk_col = dv_col + 16u;
+#pragma unroll
+                    for (int ks = 0; ks < 8; ++ks) {
+                        const uint32_t acc = (t == 0 && ks == 0) ? 0u : 1u;
+                        mma_ts(dv_col, tmem + 16u * ks, ot_hi, id, acc);          // dgv_h += P^T dO_h
+                        mma_ts(dv_col, tmem + 16u * ks, ot_lo, id, 1u);
+                        mma_ts(dv_col, tmem + 16u * ks + 8u, ot_hi, id, 1u);
+                        mma_ts(dk_col, tmem + 128u + 16u * ks, qt_hi, id, acc);   // dgk_h += dS^T (0.25 Q_h)
+                        mma_ts(dk_col, tmem + 128u + 16u * ks, qt_lo, id, 1u);
+                        mma_ts(dk_col, tmem + 128u + 16u * ks + 8u, qt_hi, id, 1u);
+                        ot_hi += 256u >> 4;
+                        ot_lo += 256u >> 4;
+                        qt_hi += 256u >> 4;
+                        qt_lo += 256u >> 4;
+                    }
+                    tc_commit(bar2);
+                }
+                __syncwarp();
+            }
+            mma2_pending = true;
+        }
+        __syncthreads();   // s_lse / s_dd / masks of this tile are rewritten by the next one
+    }
+    if (mma2_pending) mbar_wait(bar2, p2);
+    tc_fence_after();
+    {   // accumulators: lane = node, columns 256 + 32 h + (0: dgv, 16: dgk) + d; warp halves split the heads
+        const int node = 32 * q4 + lane;
+#pragma unroll 1
+        for (int h = 4 * chalf; h < 4 * chalf + 4; ++h) {
+            uint32_t v[16], k[16];
+            tmem_ld16(lane_base + 256u + 32u * (uint32_t)h, v);
+            tmem_ld16(lane_base + 256u + 32u * (uint32_t)h + 16u, k);
+            tc_wait_ld();
+            if (node < n) {
+                float* pv = dgv + ((size_t)b * n + node) * kE + 16 * h;
+                float* pk = dgk + ((size_t)b * n + node) * kE + 16 * h;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    atomicAdd(pv + i, __uint_as_float(v[i]));
+                    atomicAdd(pk + i, __uint_as_float(k[i]));
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
 // Row split per instance: `units` equal CTAs per split step over sms * ctas_per_sm slots, the split in [1, 32] with the
@@ -815,7 +962,6 @@ extern "C" int rl4co_eval_ll_bwd(const float* q, const float* gk, const float* g
     const size_t table = (size_t)n_nodes * kE * sizeof(float);
     if ((rc = ev::set_smem(ev::eval_row_bwd_pointer_kernel, table, "eval_ll_bwd (row pass, pointer)"))) return rc;
     if ((rc = ev::set_smem(ev::eval_row_bwd_glimpse_kernel, 2 * table, "eval_ll_bwd (row pass, glimpse)"))) return rc;
-    if ((rc = ev::set_smem(ev::eval_node_bwd_kernel, ev::node_smem_bytes(), "eval_ll_bwd (node pass)"))) return rc;
     dim3 g1((unsigned)B, (unsigned)ev::grid_split(B, 1));
     ev::eval_row_bwd_pointer_kernel<<<g1, ev::kThreads, table, st>>>(lkf, maskw, taken, heads, lse_z, dlogp, dheads, du_t, R,
                                                                     n_nodes, tanh_clipping, temperature);
@@ -823,15 +969,13 @@ extern "C" int rl4co_eval_ll_bwd(const float* q, const float* gk, const float* g
     ev::eval_row_bwd_glimpse_kernel<<<g1, ev::kThreads, 2 * table, st>>>(q, gk, gv, maskw, heads, lse_h, dheads, dq, dd, R,
                                                                         n_nodes);
     R4_CHECK_LAUNCH("eval_ll_bwd (row pass)");
-    // node pass: dlkf = dU^T O on the tensor cores; the glimpse part's node quarters (z = mask word) on the CUDA cores
+    // node pass (tcgen05): dlkf = dU^T O, then dgv = P^T dO and dgk = dS^T (0.25 Q)
     if ((rc = ev::set_smem(ev::eval_dlk_tc_kernel, ev::dlk::kSmem, "eval_ll_bwd (dlkf)"))) return rc;
     dim3 g3((unsigned)B, (unsigned)ev::grid_split(B, 1));
     ev::eval_dlk_tc_kernel<<<g3, 256, ev::dlk::kSmem, st>>>(heads, du_t, dlkf, R, n_nodes);
     R4_CHECK_LAUNCH("eval_ll_bwd (dlkf)");
-    const unsigned nz = (unsigned)((n_nodes + 31) / 32);
-    dim3 g2((unsigned)B, (unsigned)ev::grid_split(nz * B, 1), nz);
-    const size_t smem2 = ev::node_smem_bytes();
-    ev::eval_node_bwd_kernel<<<g2, ev::kThreads, smem2, st>>>(q, gk, gv, maskw, lse_h, dheads, dd, dgk, dgv, R, n_nodes);
-    R4_CHECK_LAUNCH("eval_ll_bwd (node pass)");
+    if ((rc = ev::set_smem(ev::eval_dkv_tc_kernel, ev::dkv::kSmem, "eval_ll_bwd (dgk, dgv)"))) return rc;
+    ev::eval_dkv_tc_kernel<<<g3, 256, ev::dkv::kSmem, st>>>(q, gk, gv, maskw, lse_h, dheads, dd, dgk, dgv, R, n_nodes);
+    R4_CHECK_LAUNCH("eval_ll_bwd (dgk, dgv)");
     return RL4CO_OK;
 }
