@@ -10,9 +10,11 @@
 //            temperature, log_softmax, gather at the taken action.
 // Only FEASIBLE nodes are visited (masked nodes have probability exactly 0 in both softmaxes and contribute no gradient).
 // The backward recomputes the probabilities from the saved log-sum-exps (flash-attention style) in two passes:
-//   row pass  (CUDA cores, a warp per four rows): dheads, dq and du = d loss / d raw logit - everything that reduces over NODES;
-//   node pass (tcgen05)                         : dgk = dS^T Q, dgv = P^T dO, dlkf = dU^T O - the reductions over ROWS as MMAs with
-//             split-fp16 operands and fp32 accumulators that stay in TMEM across a CTA's row tiles.  (fp32 shared-memory
+//   row pass : everything that reduces over NODES - du = d loss / d raw logit and dheads = dU lkf on tcgen05 (the logits are
+//             recomputed as an MMA per 128-row tile, du converted in place into the A operand of the second product); dq on
+//             the CUDA cores (a warp per four rows, only feasible nodes visited);
+//   node pass (tcgen05): dgk = dS^T Q, dgv = P^T dO, dlkf = dU^T O - the reductions over ROWS as MMAs with split-fp16 operands
+//             and fp32 accumulators that stay in TMEM across a CTA's row tiles.  (fp32 shared-memory
 //             atomics are CAS loops on sm_100: a first version that accumulated the table gradients in shared memory spent
 //             25 of 31 ms of the c5 evaluate in ATOMS.CAST.SPIN.)
 //
@@ -291,88 +293,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
 }
 
-// du_t [B,R,128]: d loss / d (raw logit of node n), stored so that the nodes one warp of the node pass owns
-// (n = w, w + 16, ..., w + 96) are the eight contiguous floats [8 w, 8 w + 8)
-__device__ __forceinline__ int du_index(int node) { return (node & 15) * 8 + (node >> 4); }
-
-// ---- backward, row pass of the pointer (no atomics): du_t, dheads ------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 1)
-    eval_row_bwd_pointer_kernel(const float* __restrict__ lkf, const uint32_t* __restrict__ maskw,
-                                const int64_t* __restrict__ taken, const float* __restrict__ heads,
-                                const float* __restrict__ lse_z, const float* __restrict__ dlogp, float* __restrict__ dheads,
-                                float* __restrict__ du_t, int64_t R, int n, float clip, float temperature) {
-    extern __shared__ __align__(16) float sm[];
-    float* s_lk = sm;
-    const int64_t b = blockIdx.x;
-    copy_table_swz(s_lk, lkf + b * n * kE, n);
-    __syncthreads();
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-    const int ri = lane >> 3, h = lane & 7;
-    int64_t r0, r1;
-    row_range(R, r0, r1);
-    for (int64_t rb = r0 + 4 * warp; rb < r1; rb += 4 * nw) {
-        const bool valid = rb + ri < r1;
-        const int64_t row = b * R + (valid ? rb + ri : r1 - 1);
-        uint32_t w[kNB], wu[kNB];
-        {
-            const uint4 mw = *reinterpret_cast<const uint4*>(maskw + row * kNB);
-            w[0] = mw.x, w[1] = mw.y, w[2] = mw.z, w[3] = mw.w;
-        }
-#pragma unroll
-        for (int blk = 0; blk < kNB; ++blk) wu[blk] = or_rows(w[blk]);
-        float o[16];
-        ld16(heads + row * kE + 16 * h, o);
-        const float g = dlogp[row], lz = lse_z[row];
-        const int a = (int)taken[row];
-        // zero this row's du_t (lane h: entries [16 h, 16 h + 16)), then the visited nodes overwrite their entries
-        if (valid) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                *reinterpret_cast<float4*>(du_t + row * kE + 16 * h + 4 * i) = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-        __syncwarp();
-        // pointer: du[n] = g (1[n = a] - softmax(z)[n]) dz/du / sqrt(E);  dheads = sum_n du[n] lkf[n]
-        float dh[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) dh[i] = 0.f;
-#pragma unroll 1
-        for (int blk = 0; blk < kNB; ++blk) {
-            uint32_t wb = sel4u(wu, blk);
-            while (wb) {
-                int j[8];
-                bool ok[8];
-                next_nodes<8>(wb, j, ok);
-                float d[8];
-#pragma unroll
-                for (int u = 0; u < 8; ++u) d[u] = dot16(o, s_lk + (blk * 32 + j[u]) * kE + 4 * h);
-                const float tot = reduce_scatter8(d, h);
-                const int jm = sel8i(j, h);
-                bool f = (sel4u(w, blk) >> jm) & 1u;
-#pragma unroll
-                for (int u = 1; u < 8; ++u) f = f && (ok[u] || h != u);
-                const float uv = tot * kInvSqrtE;
-                float zv, dzu;
-                if (clip > 0.f) {
-                    const float t = tanhf(uv);
-                    zv = t * clip / temperature;
-                    dzu = clip * (1.0f - t * t) / temperature;
-                } else {
-                    zv = uv / temperature;
-                    dzu = 1.0f / temperature;
-                }
-                const float du = f ? g * ((blk * 32 + jm == a ? 1.0f : 0.0f) - expf(zv - lz)) * dzu * kInvSqrtE : 0.f;
-                if (valid && f) du_t[row * kE + du_index(blk * 32 + jm)] = du;
-#pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    const float dn = __shfl_sync(kFull, du, (lane & 24) | u);
-                    if (ok[u]) axpy16(dh, dn, s_lk + (blk * 32 + j[u]) * kE + 4 * h);   // warp-uniform
-                    asm volatile("" ::: "memory");   // one table row in flight at a time: eight hoisted rows spill
-                }
-            }
-        }
-        if (valid) st16(dheads + row * kE + 16 * h, dh);
-    }
-}
+// du_t [B,R,128]: d loss / d (raw logit of node n), column = node; columns >= n are zero
 
 // ---- backward, row pass of the glimpse: dq = 0.25 sum_n dS[n] k[n], dS = P (dP - D), P from the saved log-sum-exp; dd = D ------
 __global__ void __launch_bounds__(kThreads, 1)
@@ -465,7 +386,7 @@ __device__ __forceinline__ void cp_async_wait() {
 }
 
 // ---- backward, pointer part of the node pass on the tensor cores: dlkf[b] = dU^T O (tcgen05, split fp16) -------------------------
-// Per CTA a [128 x 128] fp32 accumulator in TMEM (rows = the 128 du_t columns, i.e. nodes in du_index order; columns = the 128
+// Per CTA a [128 x 128] fp32 accumulator in TMEM (rows = the 128 du_t columns = nodes; columns = the 128
 // head channels), summed over the CTA's row tiles of 64 rows (the K dimension).  A tile of du_t and heads is staged as fp32
 // with cp.async (rows padded to 132 floats), converted by the CUDA cores into two K-major fp16 hi/lo operand tiles - the
 // conversion IS the transposition: a thread reads eight consecutive rows of one column and writes one 16-byte K chunk - and
@@ -576,8 +497,8 @@ __global__ void __launch_bounds__(256, 1)
     }
     mbar_wait(mma_bar, par);
     tc_fence_after();
-    {   // accumulator row m = du_t column m = node (m >> 3) + 16 (m & 7); one red per element
-        const int m = 32 * (warp & 3) + lane, node = (m >> 3) + 16 * (m & 7);
+    {   // accumulator row m = du_t column m = node m; one red per element
+        const int m = 32 * (warp & 3) + lane, node = m;
         const uint32_t src = tmem + ((uint32_t)(32 * (warp & 3)) << 16) + 64u * (uint32_t)(warp >> 2);
 #pragma unroll 1
         for (int c = 0; c < 64; c += 16) {
@@ -594,6 +515,233 @@ __global__ void __launch_bounds__(256, 1)
     tc_fence_before();
     __syncthreads();
     if (warp == 0) tmem_dealloc(tmem, 128);
+}
+
+// ---- backward, row pass of the pointer on the tensor cores: du_t and dheads ------------------------------------------------------
+// Per tile of 128 rows: U = heads lkf^T (24 split-fp16 MMAs, A = the heads tile converted from global fp32, B = the resident
+// lkf tile) lands with TMEM lane = row; thread (row, 64 nodes) computes du = g (1[n = a] - softmax(z)[n]) dz/du / sqrt(E) on
+// the feasible nodes (softmax from the saved lse_z), stores it (du_t feeds eval_dlk_tc_kernel) and writes it back IN PLACE as
+// a TS-form A operand; dheads = du lkf is 24 TS-form MMAs against the resident TRANSPOSED lkf tile.  The dot products that
+// made up most of the CUDA-core version's instructions (1.6 ms) are gone.
+namespace pbw {
+constexpr int kT = 128;
+constexpr uint32_t kHalf = 32 * 1024;           // [128 x 128] fp16 K-major: 16 row groups x 16 chunks x 128 B
+constexpr uint32_t kOffL = 0;                   // lkf   [node][ch] hi | lo   (B of U:      N = nodes, K = channels)
+constexpr uint32_t kOffLT = 2 * kHalf;          // lkf^T [ch][node] hi | lo   (B of dheads: N = channels, K = nodes)
+constexpr uint32_t kOffH = 4 * kHalf;           // heads tile [row][ch] hi | lo (A of U)
+constexpr uint32_t kOffRow = 6 * kHalf;         // per row of the tile: g, lse_z (f32), taken (i32), 4 mask words
+constexpr uint32_t kOffBar = kOffRow + kT * 28;
+constexpr size_t kSmem = kOffBar + 64;
+}  // namespace pbw
+
+__device__ __forceinline__ float tanh_fast_ev(float v) {   // 1 - 2 / (1 + e^(2v)) on MUFU ex2 / rcp: abs. error ~2e-7
+    const float e2 = __expf(2.0f * v);
+    return 1.0f - __fdividef(2.0f, e2 + 1.0f);
+}
+
+__global__ void __launch_bounds__(256, 1)
+    eval_ptr_bwd_tc_kernel(const float* __restrict__ lkf, const uint32_t* __restrict__ maskw, const int64_t* __restrict__ taken,
+                           const float* __restrict__ heads, const float* __restrict__ lse_z, const float* __restrict__ dlogp,
+                           float* __restrict__ dheads, float* __restrict__ du_t, int64_t R, int n, float clip, float temperature) {
+    using namespace tc;
+    extern __shared__ __align__(128) unsigned char smb[];
+    float* s_g = reinterpret_cast<float*>(smb + pbw::kOffRow);
+    float* s_lz = s_g + pbw::kT;
+    int* s_a = reinterpret_cast<int*>(s_lz + pbw::kT);
+    uint32_t* s_mw = reinterpret_cast<uint32_t*>(s_a + pbw::kT);
+    uint64_t* bar1 = reinterpret_cast<uint64_t*>(smb + pbw::kOffBar);
+    uint64_t* bar2 = bar1 + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smb + pbw::kOffBar + 32);
+    const int64_t b = blockIdx.x;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    int64_t r0, r1;
+    row_range(R, r0, r1);
+    if (r0 >= r1) return;
+    const int ntiles = (int)((r1 - r0 + pbw::kT - 1) / pbw::kT);
+    if (tid == 0) {
+        mbar_init(bar1, 1);
+        mbar_init(bar2, 1);
+        fence_mbar_init();
+    }
+    __syncwarp();
+    if (warp == 0) tmem_alloc(tmem_slot, 256);
+    // resident B operands: lkf (K = channels) and its transpose (K = nodes); nodes >= n are zero
+    for (int i = tid; i < 128 * 16; i += 256) {
+        const int m = i >> 4, c = i & 15;                // lkf: (node m, 8-channel chunk c)
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a;
+        if (m < n) {
+            a = ld4(lkf + ((size_t)b * n + m) * kE + 8 * c);
+            bb = ld4(lkf + ((size_t)b * n + m) * kE + 8 * c + 4);
+        }
+        uint32_t hi[4], lo[4];
+        split2(a.x, a.y, hi[0], lo[0]);
+        split2(a.z, a.w, hi[1], lo[1]);
+        split2(bb.x, bb.y, hi[2], lo[2]);
+        split2(bb.z, bb.w, hi[3], lo[3]);
+        unsigned char* dst = smb + pbw::kOffL + (uint32_t)(m >> 3) * 2048u + (uint32_t)c * 128u + (uint32_t)(m & 7) * 16u;
+        *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(dst + pbw::kHalf) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+    for (int i = tid; i < 128 * 16; i += 256) {
+        const int ch = i & 127, g = i >> 7;              // lkf^T: (channel ch, 8-node group g); lanes run over channels
+        float v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = (8 * g + k < n) ? lkf[((size_t)b * n + 8 * g + k) * kE + ch] : 0.f;
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int w = 0; w < 4; ++w) split2(v[2 * w], v[2 * w + 1], hi[w], lo[w]);
+        unsigned char* dst = smb + pbw::kOffLT + (uint32_t)(ch >> 3) * 2048u + (uint32_t)g * 128u + (uint32_t)(ch & 7) * 16u;
+        *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(dst + pbw::kHalf) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t sb = smem_u32(smb);
+    const int q4 = warp & 3, chalf = warp >> 2;          // TMEM lane quadrant (row = 32 q4 + lane), node half
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * q4) << 16);
+    const float sc = (clip > 0.f ? clip : 1.0f) / temperature;
+    uint32_t p1 = 0, p2 = 0;
+    for (int t = 0; t < ntiles; ++t) {
+        const int64_t rt = r0 + (int64_t)t * pbw::kT;
+        const int rows = (int)(r1 - rt < pbw::kT ? r1 - rt : pbw::kT);
+        // heads tile -> K-major fp16 hi | lo (item = (row, 8-channel chunk)); per-row scalars
+        for (int i = tid; i < pbw::kT * 16; i += 256) {
+            const int r = i >> 4, c = i & 15;
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a;
+            if (r < rows) {
+                a = ld4(heads + (b * R + rt + r) * kE + 8 * c);
+                bb = ld4(heads + (b * R + rt + r) * kE + 8 * c + 4);
+            }
+            uint32_t hi[4], lo[4];
+            split2(a.x, a.y, hi[0], lo[0]);
+            split2(a.z, a.w, hi[1], lo[1]);
+            split2(bb.x, bb.y, hi[2], lo[2]);
+            split2(bb.z, bb.w, hi[3], lo[3]);
+            unsigned char* dst = smb + pbw::kOffH + (uint32_t)(r >> 3) * 2048u + (uint32_t)c * 128u + (uint32_t)(r & 7) * 16u;
+            *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(dst + pbw::kHalf) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        }
+        if (tid < pbw::kT) {
+            const bool ok = tid < rows;
+            const int64_t row = b * R + rt + (ok ? tid : 0);
+            s_g[tid] = ok ? dlogp[row] : 0.f;
+            s_lz[tid] = ok ? lse_z[row] : 0.f;
+            s_a[tid] = ok ? (int)taken[row] : -1;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) s_mw[tid * 4 + k] = ok ? maskw[row * kNB + k] : 0u;
+        }
+        fence_proxy_async();
+        __syncthreads();
+        if (warp == 0) {
+            if (elect_one()) {
+                tc_fence_after();
+                const uint32_t id = idesc_f16(128, 128);
+                uint64_t a_hi = smem_desc(sb + pbw::kOffH, 128, 2048), a_lo = smem_desc(sb + pbw::kOffH + pbw::kHalf, 128, 2048);
+                uint64_t b_hi = smem_desc(sb + pbw::kOffL, 128, 2048), b_lo = smem_desc(sb + pbw::kOffL + pbw::kHalf, 128, 2048);
+#pragma unroll
+                for (int ks = 0; ks < 8; ++ks) {
+                    mma_ss(tmem, a_hi, b_hi, id, ks == 0 ? 0u : 1u);     // U = heads lkf^T
+                    mma_ss(tmem, a_hi, b_lo, id, 1u);
+                    mma_ss(tmem, a_lo, b_hi, id, 1u);
+                    a_hi += 256u >> 4;
+                    a_lo += 256u >> 4;
+                    b_hi += 256u >> 4;
+                    b_lo += 256u >> 4;
+                }
+                tc_commit(bar1);
+            }
+            __syncwarp();
+        }
+        mbar_wait(bar1, p1);
+        p1 ^= 1u;
+        tc_fence_after();
+        {
+            const int r = 32 * q4 + lane;
+            const bool rv = r < rows;
+            const float g = s_g[r], lz = s_lz[r];
+            const int a = s_a[r];
+            const uint32_t m0 = s_mw[r * 4 + 2 * chalf], m1 = s_mw[r * 4 + 2 * chalf + 1];
+            float* dut = du_t + (b * R + rt + (rv ? r : 0)) * kE;
+#pragma unroll 1
+            for (int c = 0; c < 64; c += 16) {
+                const int col = 64 * chalf + c;
+                uint32_t uv[16];
+                tmem_ld16(lane_base + (uint32_t)col, uv);
+                tc_wait_ld();
+                const uint32_t bits = ((c < 32 ? m0 : m1) >> (c & 31)) & 0xffffu;
+                float du[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const float u = __uint_as_float(uv[i]) * kInvSqrtE;
+                    float zv, dzu;
+                    if (clip > 0.f) {
+                        const float th = tanh_fast_ev(u);
+                        zv = th * sc;
+                        dzu = sc * (1.0f - th * th);
+                    } else {
+                        zv = u * sc;
+                        dzu = sc;
+                    }
+                    const float pz = __expf(zv - lz);
+                    du[i] = (bits >> i) & 1u ? g * ((col + i == a ? 1.0f : 0.0f) - pz) * dzu * kInvSqrtE : 0.f;
+                }
+                if (rv) {
+#pragma unroll
+                    for (int i = 0; i < 16; i += 4)
+                        *reinterpret_cast<float4*>(dut + col + i) = make_float4(du[i], du[i + 1], du[i + 2], du[i + 3]);
+                }
+                uint32_t hi[8], lo[8];
+#pragma unroll
+                for (int i = 0; i < 16; i += 2) split2(du[i], du[i + 1], hi[i >> 1], lo[i >> 1]);
+                tmem_st8(lane_base + (uint32_t)col, hi);
+                tmem_st8(lane_base + (uint32_t)col + 8u, lo);
+            }
+        }
+        tc_wait_st();
+        tc_fence_before();
+        __syncthreads();
+        if (warp == 0) {
+            if (elect_one()) {
+                tc_fence_after();
+                const uint32_t id = idesc_f16(128, 128);
+                uint64_t b_hi = smem_desc(sb + pbw::kOffLT, 128, 2048), b_lo = smem_desc(sb + pbw::kOffLT + pbw::kHalf, 128, 2048);
+#pragma unroll
+                for (int ks = 0; ks < 8; ++ks) {
+                    mma_ts(tmem + 128u, tmem + 16u * ks, b_hi, id, ks == 0 ? 0u : 1u);   // dheads = du lkf
+                    mma_ts(tmem + 128u, tmem + 16u * ks, b_lo, id, 1u);
+                    mma_ts(tmem + 128u, tmem + 16u * ks + 8u, b_hi, id, 1u);
+                    b_hi += 256u >> 4;
+                    b_lo += 256u >> 4;
+                }
+                tc_commit(bar2);
+            }
+            __syncwarp();
+        }
+        mbar_wait(bar2, p2);
+        p2 ^= 1u;
+        tc_fence_after();
+        {
+            const int r = 32 * q4 + lane;
+            float* dh = dheads + (b * R + rt + (r < rows ? r : 0)) * kE + 64 * chalf;
+#pragma unroll 1
+            for (int c = 0; c < 64; c += 16) {
+                uint32_t v[16];
+                tmem_ld16(lane_base + 128u + 64u * (uint32_t)chalf + (uint32_t)c, v);
+                tc_wait_ld();
+                if (r < rows) {
+#pragma unroll
+                    for (int i = 0; i < 16; i += 4)
+                        *reinterpret_cast<float4*>(dh + c + i) = make_float4(__uint_as_float(v[i]), __uint_as_float(v[i + 1]),
+                                                                            __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
+                }
+            }
+        }
+        tc_fence_before();
+        __syncthreads();   // the heads tile, the row scalars and the TMEM columns are reused by the next tile
+    }
+    if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
 // ---- backward, glimpse part of the node pass on the tensor cores: dgk = dS^T (0.25 Q), dgv = P^T dO ------------------------------
@@ -960,11 +1108,11 @@ extern "C" int rl4co_eval_ll_bwd(const float* q, const float* gk, const float* g
     if (B == 0 || R == 0) return RL4CO_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t table = (size_t)n_nodes * kE * sizeof(float);
-    if ((rc = ev::set_smem(ev::eval_row_bwd_pointer_kernel, table, "eval_ll_bwd (row pass, pointer)"))) return rc;
     if ((rc = ev::set_smem(ev::eval_row_bwd_glimpse_kernel, 2 * table, "eval_ll_bwd (row pass, glimpse)"))) return rc;
     dim3 g1((unsigned)B, (unsigned)ev::grid_split(B, 1));
-    ev::eval_row_bwd_pointer_kernel<<<g1, ev::kThreads, table, st>>>(lkf, maskw, taken, heads, lse_z, dlogp, dheads, du_t, R,
-                                                                    n_nodes, tanh_clipping, temperature);
+    if ((rc = ev::set_smem(ev::eval_ptr_bwd_tc_kernel, ev::pbw::kSmem, "eval_ll_bwd (row pass, pointer)"))) return rc;
+    ev::eval_ptr_bwd_tc_kernel<<<g1, 256, ev::pbw::kSmem, st>>>(lkf, maskw, taken, heads, lse_z, dlogp, dheads, du_t, R, n_nodes,
+                                                               tanh_clipping, temperature);
     R4_CHECK_LAUNCH("eval_ll_bwd (row pass, pointer)");
     ev::eval_row_bwd_glimpse_kernel<<<g1, ev::kThreads, 2 * table, st>>>(q, gk, gv, maskw, heads, lse_h, dheads, dq, dd, R,
                                                                         n_nodes);
