@@ -372,7 +372,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 //   dgv = P^T dO, dgk = dS^T (0.25 Q)  : eval_dkv_tc_kernel (transposed score tiles, P^T / dS^T as TS-form A operands in TMEM).
 // (Round-2 history: a CUDA-core node pass with register accumulators - a warp per two nodes visiting every row, row tiles
 // staged with cp.async - took 4.3 ms for the three reductions; the two tensor-core kernels take 0.23 + 1.9 ms.)
-constexpr int kMaxNodes = 112;   // four [n,128] fp32 tables in shared memory (row pass); du_t holds 128 columns
+constexpr int kMaxNodes = 128;   // four mask words per row, 128-node MMA tiles, three [n,128] fp32 tables in shared memory (forward)
 
 // cp.async staging of row tiles (eval_dlk_tc_kernel)
 __device__ __forceinline__ void cp_async16(void* dst, const void* src) {

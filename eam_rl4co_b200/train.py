@@ -142,7 +142,7 @@ def batched_log_likelihood(decoder, h: torch.Tensor, states: Dict[str, torch.Ten
     logits / sqrt(E)), decoding.py:140-190 (tanh clip, mask, temperature, log_softmax).  `h` is the encoder output with its
     graph attached.  The table products and the query gathers are PyTorch (autograd); the masked attention, pointer and
     log-softmax of the B*S*(T-1) rows run on the fused forward / backward kernels (`_FusedEvaluate`) on CUDA, and as plain
-    PyTorch ops (`fused=False`, CPU tensors, n > 112) otherwise - the form the host tests pin against the oracle."""
+    PyTorch ops (`fused=False`, CPU tensors, n > 128) otherwise - the form the host tests pin against the oracle."""
     B, n, E = h.shape
     H = decoder.num_heads
     cur, mask, taken = states["cur"], states["mask"], states["taken"]

@@ -279,7 +279,7 @@ int rl4co_best_of_starts(const float* reward, const int64_t* actions, int64_t B,
  *      backward reuses: heads [B,R,128], lse_h [B,R,8] (log-sum-exp of each head's scores), lse_z [B,R], maskw [B,R,4]
  *      (the mask as bit words).
  * bwd: given dlogp [B,R]: dq [B,R,128] (written), dgk / dgv / dlkf [B,n,128] (ACCUMULATED: zero them first);
- *      dheads, du_t [B,R,128] and dd [B,R,8] are scratch.  n_nodes <= rl4co_eval_ll_max_nodes() (112).                                  */
+ *      dheads, du_t [B,R,128] and dd [B,R,8] are scratch.  n_nodes <= rl4co_eval_ll_max_nodes() (128).                                  */
 int32_t rl4co_eval_ll_max_nodes(void);
 int rl4co_eval_ll_fwd(const float* q, const float* gk, const float* gv, const float* lkf, const uint8_t* mask,
                       const int64_t* taken, float* logp, float* heads, float* lse_h, float* lse_z, uint32_t* maskw,

@@ -50,7 +50,7 @@ def test_argument_errors_return_codes_without_launching():
                              C.c_int64(1), None)
     assert rc == -1 and b"embed_dim=128" in L.rl4co_last_error()
     # the evaluate kernels check their arguments before any CUDA call
-    assert L.rl4co_eval_ll_max_nodes() == 112
+    assert L.rl4co_eval_ll_max_nodes() == 128
     rc = L.rl4co_eval_ll_fwd(None, None, None, None, None, None, None, None, None, None, None, C.c_int64(1), C.c_int64(1),
                              C.c_int32(20), C.c_float(10.0), C.c_float(1.0), None)
     assert rc == -1 and b"null pointer" in L.rl4co_last_error()

@@ -143,14 +143,14 @@ def test_fused_evaluate_rejects_unsupported_sizes():
     from eam_rl4co_b200 import _lib
     import ctypes as C
     L = _lib.lib()
-    assert L.rl4co_eval_ll_max_nodes() == 112
+    assert L.rl4co_eval_ll_max_nodes() == 128
     z = torch.zeros(8, device=DEV)
     p = C.c_void_p(z.data_ptr())
-    rc = L.rl4co_eval_ll_fwd(p, p, p, p, p, p, p, p, p, p, p, C.c_int64(1), C.c_int64(1), C.c_int32(113), C.c_float(10.0),
+    rc = L.rl4co_eval_ll_fwd(p, p, p, p, p, p, p, p, p, p, p, C.c_int64(1), C.c_int64(1), C.c_int32(129), C.c_float(10.0),
                              C.c_float(1.0), None)
     assert rc != 0 and b"n_nodes" in L.rl4co_last_error()
-    h = torch.zeros(1, 120, 128, device=DEV)
-    assert not train.fused_evaluate_supported(h, 120) and train.fused_evaluate_supported(h, 101)
+    h = torch.zeros(1, 130, 128, device=DEV)
+    assert not train.fused_evaluate_supported(h, 130) and train.fused_evaluate_supported(h, 128)
 
 
 def _eager_rows(q, gk, gv, lkf, mask, taken, clip, temp):
@@ -167,7 +167,7 @@ def _eager_rows(q, gk, gv, lkf, mask, taken, clip, temp):
     return torch.log_softmax(z, -1).gather(-1, taken[..., None])[..., 0]
 
 
-@pytest.mark.parametrize("B,R,n,clip,temp", [(3, 37, 101, 10.0, 1.0), (2, 5, 2, 10.0, 1.0), (1, 1, 112, 0.0, 0.5),
+@pytest.mark.parametrize("B,R,n,clip,temp", [(3, 37, 101, 10.0, 1.0), (2, 5, 2, 10.0, 1.0), (1, 1, 112, 0.0, 0.5), (2, 131, 128, 10.0, 1.0),
                                               (5, 130, 64, 10.0, 2.0), (70, 9, 21, 10.0, 1.0)])
 def test_fused_evaluate_rows_against_fp64(B, R, n, clip, temp):
     """Ragged row counts (not a multiple of the four-row groups or of the CTA split), the smallest and largest node
