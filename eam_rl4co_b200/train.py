@@ -8,9 +8,10 @@ Here the sampling rollout runs on the fused kernel (no autograd), and the log-li
 actions is re-evaluated by `evaluate_log_likelihood`: the same arithmetic as the reference's evaluate mode
 (`decoding.py:452-465`, `constructive/base.py:204-206,221-229`), but teacher-forced over ALL decoding steps at
 once - with the actions known, every step's context (first / current node, remaining capacity) and feasibility
-mask follows from the action prefix, so the T sequential decoder steps become one batched masked attention that
-PyTorch autograd differentiates.  Same actions => same log-likelihood => same gradient as the reference's
-sample-while-recording pass.
+mask follows from the action prefix, so the T sequential decoder steps become one batch of independent rows: on CUDA
+the fused kernels `rl4co_eval_ll_fwd` / `rl4co_eval_ll_bwd` (csrc/evaluate_kernels.cu, the backward's reductions on
+tcgen05) behind a `torch.autograd.Function`, elsewhere one batched masked attention in plain PyTorch.  Same actions =>
+same log-likelihood => same gradient as the reference's sample-while-recording pass.
 
 Multi-GPU: instances are sharded, the shared baseline is per instance and therefore local,
 and the step ends with ONE flat-buffer all-reduce of gradients + logged sums (`sharding.allreduce_mean_`).
@@ -87,7 +88,8 @@ def _replay_states_kernel(td, actions: torch.Tensor, S: int, cvrp: bool) -> Dict
 class _FusedEvaluate(torch.autograd.Function):
     """log p(taken | row) [B,R] from the fused kernels rl4co_eval_ll_fwd / rl4co_eval_ll_bwd (csrc/evaluate_kernels.cu):
     masked 8-head glimpse + pointer + log_softmax + gather per row, tables of an instance in shared memory; the backward
-    recomputes the probabilities from the saved log-sum-exps.  Differentiable in q, gk, gv, lkf."""
+    recomputes the probabilities from the saved log-sum-exps (row pass) and reduces over rows on the tensor cores
+    (dgk, dgv, dlkf with their accumulators in TMEM).  Differentiable in q, gk, gv, lkf."""
 
     @staticmethod
     def forward(ctx, q, gk, gv, lkf, mask, taken, tanh_clipping, temperature):
@@ -117,12 +119,13 @@ class _FusedEvaluate(torch.autograd.Function):
         B, R, E = q.shape
         n = gk.shape[1]
         dlogp = dlogp.contiguous().float()
-        dheads, du_t = torch.empty_like(heads), torch.empty_like(heads)
+        dheads, du_t, dd = torch.empty_like(heads), torch.empty_like(heads), torch.empty_like(lse_h)   # scratch
         dq = torch.empty_like(q)
         dgk, dgv, dlkf = torch.zeros_like(gk), torch.zeros_like(gv), torch.zeros_like(lkf)
         rc = _lib.lib().rl4co_eval_ll_bwd(_lib.ptr(q), _lib.ptr(gk), _lib.ptr(gv), _lib.ptr(lkf), _lib.ptr(maskw),
                                           _lib.ptr(taken), _lib.ptr(heads), _lib.ptr(lse_h), _lib.ptr(lse_z), _lib.ptr(dlogp),
-                                          _lib.ptr(dheads), _lib.ptr(du_t), _lib.ptr(torch.empty_like(lse_h)), _lib.ptr(dq), _lib.ptr(dgk), _lib.ptr(dgv), _lib.ptr(dlkf),
+                                          _lib.ptr(dheads), _lib.ptr(du_t), _lib.ptr(dd), _lib.ptr(dq), _lib.ptr(dgk), _lib.ptr(dgv),
+                                          _lib.ptr(dlkf),
                                           C.c_int64(B), C.c_int64(R), C.c_int32(n), C.c_float(ctx.scalars[0]),
                                           C.c_float(ctx.scalars[1]), _lib.stream_ptr())
         _lib.check(rc, "rl4co_eval_ll_bwd")
@@ -151,7 +154,10 @@ def batched_log_likelihood(decoder, h: torch.Tensor, states: Dict[str, torch.Ten
     Wk, Wv, Wl = decoder.project_node_embeddings.weight.chunk(3, dim=0)           # decoder.py:206-235
     Wc = decoder.context_embedding.project_context.weight
     gk, gv, lk = F.linear(h, Wk), F.linear(h, Wv), F.linear(h, Wl)
-    idx = lambda tab, i: tab.gather(1, i.reshape(B, -1, 1).expand(B, i[0].numel(), E))
+    # row gathers tab[b, i[b, ...]] as ONE index_select over the flattened table (a gather with an index expanded to the
+    # 128 channels reads 8 bytes of index per element; its backward is the same scatter-add either way)
+    boff = (torch.arange(B, device=h.device) * n).view(B, 1)
+    idx = lambda tab, i: tab.reshape(B * n, E).index_select(0, (i.reshape(B, -1) + boff).reshape(-1)).view(B, -1, E)
     if decoder.env_name == "tsp":                                                  # context.py:118-140
         pa, pb = F.linear(h, Wc[:, :E]), F.linear(h, Wc[:, E:])
         q = idx(pa, states["first"]).view(B, S, 1, E) + idx(pb, cur).view(B, S, Tm, E)
