@@ -132,6 +132,45 @@ class _FusedEvaluate(torch.autograd.Function):
         return dq, dgk, dgv, dlkf, None, None, None, None
 
 
+class _FusedQuery(torch.autograd.Function):
+    """Glimpse query q [B, S*Tm, 128] of all teacher-forced rows from rl4co_eval_query_fwd / rl4co_eval_query_bwd
+    (csrc/evaluate_query.cu): pb[b, cur] (+ pa[b, first]) (+ rem * wcap) (+ gctx[b]) in one streaming pass; the backward
+    sums dq over the rows of each node (counting sort by node inside a CTA, register sums, one red.global per 64 rows and
+    channel) where PyTorch runs index_add_ with 128 colliding atomics per row.  Differentiable in pb, pa, wcap, gctx."""
+
+    @staticmethod
+    def forward(ctx, pb, pa, wcap, gctx, cur, first, rem):
+        B, n, E = pb.shape
+        S, Tm = cur.shape[1], cur.shape[2]
+        f32 = lambda t: None if t is None else t.contiguous().float()
+        pb, pa, wcap, gctx = f32(pb), f32(pa), f32(wcap), f32(gctx)
+        cur = cur.contiguous()
+        first = first.contiguous() if pa is not None else None
+        rem = f32(rem) if wcap is not None else None
+        q = torch.empty(B, S * Tm, E, device=pb.device)
+        rc = _lib.lib().rl4co_eval_query_fwd(_lib.ptr(pb), _lib.ptr(pa), _lib.ptr(wcap), _lib.ptr(gctx), _lib.ptr(cur),
+                                             _lib.ptr(first), _lib.ptr(rem), _lib.ptr(q), C.c_int64(B), C.c_int64(S),
+                                             C.c_int64(Tm), C.c_int32(n), _lib.stream_ptr())
+        _lib.check(rc, "rl4co_eval_query_fwd")
+        ctx.save_for_backward(cur, first, rem)
+        ctx.meta = (B, n, S, Tm, gctx is not None)
+        return q
+
+    @staticmethod
+    def backward(ctx, dq):
+        cur, first, rem = ctx.saved_tensors
+        B, n, S, Tm, has_gctx = ctx.meta
+        dq = dq.contiguous().float()
+        dpb = torch.zeros(B, n, dq.shape[-1], device=dq.device)
+        dpa = torch.zeros_like(dpb) if first is not None else None
+        dwcap = torch.zeros(dq.shape[-1], device=dq.device) if rem is not None else None
+        rc = _lib.lib().rl4co_eval_query_bwd(_lib.ptr(dq), _lib.ptr(cur), _lib.ptr(first), _lib.ptr(rem), _lib.ptr(dpb),
+                                             _lib.ptr(dpa), _lib.ptr(dwcap), C.c_int64(B), C.c_int64(S), C.c_int64(Tm),
+                                             C.c_int32(n), _lib.stream_ptr())
+        _lib.check(rc, "rl4co_eval_query_bwd")
+        return dpb, dpa, dwcap, (dpb.sum(1) if has_gctx else None), None, None, None
+
+
 def fused_evaluate_supported(h: torch.Tensor, n: int) -> bool:
     """The fused kernels cover CUDA fp32 embeddings of width 128 (8 heads) and n <= rl4co_eval_ll_max_nodes()."""
     return h.is_cuda and h.shape[-1] == 128 and n <= int(_lib.lib().rl4co_eval_ll_max_nodes())
@@ -143,9 +182,10 @@ def batched_log_likelihood(decoder, h: torch.Tensor, states: Dict[str, torch.Ten
 
     am/decoder.py:133-198 (context -> glimpse query), attention.py:282-328 (masked MHA glimpse, project_out,
     logits / sqrt(E)), decoding.py:140-190 (tanh clip, mask, temperature, log_softmax).  `h` is the encoder output with its
-    graph attached.  The table products and the query gathers are PyTorch (autograd); the masked attention, pointer and
-    log-softmax of the B*S*(T-1) rows run on the fused forward / backward kernels (`_FusedEvaluate`) on CUDA, and as plain
-    PyTorch ops (`fused=False`, CPU tensors, n > 128) otherwise - the form the host tests pin against the oracle."""
+    graph attached.  The per-instance table products are PyTorch (autograd); the query of every row (`_FusedQuery`) and
+    the masked attention, pointer and log-softmax of the B*S*(T-1) rows (`_FusedEvaluate`) run on the fused forward /
+    backward kernels on CUDA, and as plain PyTorch ops (`fused=False`, CPU tensors, n > 128) otherwise - the form the host
+    tests pin against the oracle."""
     B, n, E = h.shape
     H = decoder.num_heads
     cur, mask, taken = states["cur"], states["mask"], states["taken"]
@@ -154,20 +194,26 @@ def batched_log_likelihood(decoder, h: torch.Tensor, states: Dict[str, torch.Ten
     Wk, Wv, Wl = decoder.project_node_embeddings.weight.chunk(3, dim=0)           # decoder.py:206-235
     Wc = decoder.context_embedding.project_context.weight
     gk, gv, lk = F.linear(h, Wk), F.linear(h, Wv), F.linear(h, Wl)
-    # row gathers tab[b, i[b, ...]] as ONE index_select over the flattened table (a gather with an index expanded to the
-    # 128 channels reads 8 bytes of index per element; its backward is the same scatter-add either way)
-    boff = (torch.arange(B, device=h.device) * n).view(B, 1)
-    idx = lambda tab, i: tab.reshape(B * n, E).index_select(0, (i.reshape(B, -1) + boff).reshape(-1)).view(B, -1, E)
-    if decoder.env_name == "tsp":                                                  # context.py:118-140
-        pa, pb = F.linear(h, Wc[:, :E]), F.linear(h, Wc[:, E:])
-        q = idx(pa, states["first"]).view(B, S, 1, E) + idx(pb, cur).view(B, S, Tm, E)
-    else:                                                                          # context.py:70-74,143-157
-        pb = F.linear(h, Wc[:, :E])
-        q = idx(pb, cur).view(B, S, Tm, E) + states["rem"].unsqueeze(-1) * Wc[:, E]
-    if decoder.use_graph_context:                                                  # decoder.py:223-224
-        q = q + F.linear(h.mean(1), decoder.project_fixed_context.weight).view(B, 1, 1, E)
     if fused is None:
         fused = fused_evaluate_supported(h, n) and H == 8
+    tsp = decoder.env_name == "tsp"
+    # project_context is linear: apply its halves to the n node embeddings, the rows gather the products
+    pa = F.linear(h, Wc[:, :E]) if tsp else None                                   # context.py:118-140
+    pb = F.linear(h, Wc[:, E:] if tsp else Wc[:, :E])                              # context.py:70-74,143-157
+    gctx = (F.linear(h.mean(1), decoder.project_fixed_context.weight)              # decoder.py:223-224
+            if decoder.use_graph_context else None)
+    if fused:
+        q = _FusedQuery.apply(pb, pa, None if tsp else Wc[:, E], gctx, cur, states["first"] if tsp else None,
+                              None if tsp else states["rem"])
+    else:
+        # row gathers tab[b, i[b, ...]] as ONE index_select over the flattened table (a gather with an index expanded to
+        # the 128 channels reads 8 bytes of index per element; its backward is the same scatter-add either way)
+        boff = (torch.arange(B, device=h.device) * n).view(B, 1)
+        idx = lambda tab, i: tab.reshape(B * n, E).index_select(0, (i.reshape(B, -1) + boff).reshape(-1)).view(B, -1, E)
+        q = idx(pb, cur).view(B, S, Tm, E)
+        q = q + (idx(pa, states["first"]).view(B, S, 1, E) if tsp else states["rem"].unsqueeze(-1) * Wc[:, E])
+        if gctx is not None:
+            q = q + gctx.view(B, 1, 1, E)
     if fused:
         # logits = (glimpse W_out^T) lk^T = glimpse (lk W_out)^T: the fold the rollout kernels use (decoder.py cache)
         lkf = torch.matmul(lk, decoder.pointer.project_out.weight)

@@ -289,6 +289,19 @@ int rl4co_eval_ll_bwd(const float* q, const float* gk, const float* gv, const fl
                       float* dheads, float* du_t, float* dd, float* dq, float* dgk, float* dgv, float* dlkf, int64_t B,
                       int64_t R, int32_t n_nodes, float tanh_clipping, float temperature, void* stream);
 
+/* ---- the glimpse query of all teacher-forced rows and its gradient (context.py:118-157, am/decoder.py:223-224) ----------
+ * q[b,s,t,:] = pb[b,cur[b,s,t],:] (+ pa[b,first[b,s],:]) (+ rem[b,s,t] * wcap[:]) (+ ctx[b,:]), 128 channels, where
+ * pb / pa [B,n,128] are the node embeddings under the two halves of project_context (TSP: [first, current]; CVRP: current
+ * node only and wcap = the remaining-capacity column) and ctx [B,128] the projected graph mean; optional terms are NULL
+ * (pa with first, wcap with rem).  cur [B,S,Tm] and first [B,S] int64, rem [B,S,Tm] f32; node ids outside [0, n) are
+ * clamped.  bwd: dpb (and dpa, dwcap [128]) are ACCUMULATED from dq [B,S*Tm,128] (zero them first); the gradient of ctx
+ * is the sum of dpb over its node axis.  n_nodes <= 128.                                                              */
+int rl4co_eval_query_fwd(const float* pb, const float* pa, const float* wcap, const float* ctx, const int64_t* cur,
+                         const int64_t* first, const float* rem, float* q, int64_t B, int64_t S, int64_t Tm,
+                         int32_t n_nodes, void* stream);
+int rl4co_eval_query_bwd(const float* dq, const int64_t* cur, const int64_t* first, const float* rem, float* dpb,
+                         float* dpa, float* dwcap, int64_t B, int64_t S, int64_t Tm, int32_t n_nodes, void* stream);
+
 /* ---- on-device instance generation: the input spec of tsp/generator.py:53-62 and cvrp/generator.py:120-147 -----------
  * locs [B, n_loc, 2] uniform in [0,1); CVRP also depot [B,2] and demand [B, n_loc] = integer 1..9 / capacity.  Values come
  * from the counter hash keyed (seed, inst_offset + b, element), so shards of a global batch agree with the whole.   */

@@ -59,6 +59,15 @@ def test_argument_errors_return_codes_without_launching():
     assert rc == -1 and b"n_nodes=200" in L.rl4co_last_error()
     rc = L.rl4co_eval_ll_bwd(*([one] * 17), C.c_int64(2), C.c_int64(3), C.c_int32(50), C.c_float(10.0), C.c_float(0.0), None)
     assert rc == -1 and b"temperature" in L.rl4co_last_error()
+    sz = (C.c_int64(2), C.c_int64(3), C.c_int64(4))
+    rc = L.rl4co_eval_query_fwd(one, None, None, None, one, None, None, one, *sz, C.c_int32(129), None)
+    assert rc == -1 and b"n_nodes=129" in L.rl4co_last_error()
+    rc = L.rl4co_eval_query_fwd(one, one, None, None, one, None, None, one, *sz, C.c_int32(20), None)
+    assert rc == -1 and b"pa and first" in L.rl4co_last_error()
+    rc = L.rl4co_eval_query_bwd(one, one, None, one, one, None, None, *sz, C.c_int32(20), None)
+    assert rc == -1 and b"dwcap and rem" in L.rl4co_last_error()
+    rc = L.rl4co_eval_query_bwd(one, one, None, None, None, None, None, *sz, C.c_int32(20), None)
+    assert rc == -1 and b"null dq / cur / dpb" in L.rl4co_last_error()
 
 
 def test_no_fallback_when_library_missing(monkeypatch):

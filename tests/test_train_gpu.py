@@ -191,3 +191,42 @@ def test_fused_evaluate_rows_against_fp64(B, R, n, clip, temp):
     for a32, a64, name in zip(args32, args64, ("q", "gk", "gv", "lkf")):
         scale = max(a64.grad.abs().max().item(), 1e-6)
         assert (a32.grad.double() - a64.grad).abs().max().item() / scale < 1e-4, name
+
+
+@pytest.mark.parametrize("B,S,Tm,n,tsp,skew", [(3, 7, 11, 21, True, False), (2, 5, 9, 101, False, False),
+                                                (70, 3, 5, 2, False, False), (1, 1, 1, 128, True, False),
+                                                (2, 100, 111, 101, False, True), (1, 2, 140000, 50, True, True)])
+def test_fused_query_against_fp64(B, S, Tm, n, tsp, skew):
+    """rl4co_eval_query_fwd / rl4co_eval_query_bwd against the PyTorch statement of context.py:118-157 + decoder.py:223-224
+    in fp64: ragged sizes, more instances than SMs, one node collecting most rows (a CVRP depot), and a row range longer
+    than one sorting pass of the backward kernel."""
+    g = torch.Generator().manual_seed(B * 7 + S * 5 + Tm * 3 + n)
+    rnd = lambda *s: torch.randn(*s, generator=g)
+    pb, pa, wcap, gctx = rnd(B, n, 128), rnd(B, n, 128), rnd(128), rnd(B, 128)
+    cur = torch.randint(0, n, (B, S, Tm), generator=g)
+    if skew:
+        cur[torch.rand(B, S, Tm, generator=g) < 0.7] = 0
+    first = torch.randint(0, n, (B, S), generator=g)
+    rem = torch.rand(B, S, Tm, generator=g)
+    cot = rnd(B, S * Tm, 128)
+    cur, first, rem, cot = cur.to(DEV), first.to(DEV), rem.to(DEV), cot.to(DEV)
+
+    def eager(pb, pa, wcap, gctx):
+        bi = torch.arange(B, device=DEV).view(B, 1, 1)
+        q = pb[bi, cur] + gctx.view(B, 1, 1, 128)
+        q = q + (pa[bi[:, :, 0], first].view(B, S, 1, 128) if tsp else rem.unsqueeze(-1).to(pb.dtype) * wcap)
+        return q.reshape(B, S * Tm, 128)
+
+    a64 = [t.double().to(DEV).requires_grad_(True) for t in (pb, pa, wcap, gctx)]
+    ref = eager(*a64)
+    (ref * cot.double()).sum().backward()
+    a32 = [t.to(DEV).requires_grad_(True) for t in (pb, pa, wcap, gctx)]
+    got = train._FusedQuery.apply(a32[0], a32[1] if tsp else None, None if tsp else a32[2], a32[3], cur,
+                                  first if tsp else None, None if tsp else rem)
+    (got * cot).sum().backward()
+    assert (got.double() - ref).abs().max().item() < 1e-5
+    used = [(0, "pb"), (1, "pa"), (3, "gctx")] if tsp else [(0, "pb"), (2, "wcap"), (3, "gctx")]
+    for i, name in used:
+        scale = max(a64[i].grad.abs().max().item(), 1e-6)
+        assert (a32[i].grad.double() - a64[i].grad).abs().max().item() / scale < 2e-5, name
+    assert a32[2 if tsp else 1].grad is None
