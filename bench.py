@@ -249,24 +249,33 @@ def train_leg(dev, rank, world, steps=8, warmup=3):
     env = P.get_env("cvrp", generator_params=dict(num_loc=N), device=dev)
     gen = P.DeviceGenerator("cvrp", num_loc=N, seed=7, device=dev)
     stats = None
-    # all-reduce alone, same flat buffer size (gradients + 3 logged scalars)
     n_par = sum(p.numel() for p in pol.parameters() if p.requires_grad)
-    times = []
-    for it in range(warmup + steps):
-        td = env.reset(gen(B, instance_offset=(it * world + rank) * B))
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        t0 = torch.cuda.Event(enable_timing=True)
-        t1 = torch.cuda.Event(enable_timing=True)
-        t0.record()
-        stats = train.pomo_train_step(pol, env, td, opt, noise_seed=it, instance_offset=(it * world + rank) * B)
-        t1.record()
-        torch.cuda.synchronize()
-        if it >= warmup:
-            times.append(t0.elapsed_time(t1))
+
+    def timed(encoder, first_it):
+        nonlocal stats
+        times = []
+        for it in range(first_it, first_it + warmup + steps):
+            td = env.reset(gen(B, instance_offset=(it * world + rank) * B))
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            t0 = torch.cuda.Event(enable_timing=True)
+            t1 = torch.cuda.Event(enable_timing=True)
+            t0.record()
+            stats = train.pomo_train_step(pol, env, td, opt, noise_seed=it, instance_offset=(it * world + rank) * B,
+                                          encoder=encoder)
+            t1.record()
+            torch.cuda.synchronize()
+            if it >= first_it + warmup:
+                times.append(t0.elapsed_time(t1))
+        return statistics.median(times)
+
+    eager_ms = timed(None, 0)
+    # the same step with the PyTorch encoder's forward / backward replayed from two CUDA graphs (train.graphed_encoder)
+    encode = train.graphed_encoder(pol, env.reset(gen(B, instance_offset=0)))
+    step_ms = timed(encode, warmup + steps)
     ar_ms = None
-    if world > 1:
+    if world > 1:   # the all-reduce alone, same flat buffer size (gradients + 3 logged scalars)
         buf = torch.zeros(n_par + 3, dtype=torch.float32, device=dev)
         for _ in range(3):
             dist.all_reduce(buf)
@@ -278,12 +287,12 @@ def train_leg(dev, rank, world, steps=8, warmup=3):
         a1.record()
         torch.cuda.synchronize()
         ar_ms = a0.elapsed_time(a1) / 10
-    step_ms = statistics.median(times)
-    step_ms, = sharding.max_over_ranks([step_ms], device=dev)
+    step_ms, eager_ms = sharding.max_over_ranks([step_ms, eager_ms], device=dev)
     return {"workload": "CVRP100 POMO REINFORCE step (multistart sampling S=100 on the rollout kernel, teacher-forced "
-                        "log-likelihood forward + backward on rl4co_eval_ll_fwd / rl4co_eval_ll_bwd, shared baseline, "
-                        "encoder + table products in PyTorch autograd, flat all-reduce, clip, Adam), 64 instances per GPU",
-            "ms_per_step": step_ms, "instances_per_s": world * B / (step_ms * 1e-3), "n_gpus": world,
+                        "log-likelihood forward + backward on rl4co_eval_query_* / rl4co_eval_ll_*, shared baseline, "
+                        "encoder + table products in PyTorch autograd with the encoder's forward / backward replayed from "
+                        "CUDA graphs, flat all-reduce, clip, Adam), 64 instances per GPU",
+            "ms_per_step": step_ms, "ms_per_step_encoder_not_graphed": eager_ms, "instances_per_s": world * B / (step_ms * 1e-3), "n_gpus": world,
             "allreduce_ms": ar_ms, "allreduce_bytes": 4 * (n_par + 3), "collectives_per_step": 1 if world > 1 else 0,
             "backend": "nccl" if world > 1 else None, "loss": stats["loss"], "reward": stats["reward"],
             "ll_gap_rollout_vs_reevaluation": stats["ll_gap"]}

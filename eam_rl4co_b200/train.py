@@ -253,17 +253,47 @@ def reinforce_loss(reward: torch.Tensor, log_likelihood: torch.Tensor, num_start
     return -(adv * ll).mean(), adv
 
 
+def graphed_encoder(policy, td, num_warmup_iters: int = 3):
+    """The differentiable (PyTorch-module) encoder with its forward and its backward each captured as ONE CUDA graph
+    (torch.cuda.make_graphed_callables): at the c5 size the ~600 launches of small fp32 GEMM / attention / normalisation
+    kernels per step are CPU-bound, replayed from two graphs they are not.  Returns `encode(td) -> h [B, n, E]` (with
+    its autograd graph) for instances of the shapes of `td`; pass it as `pomo_train_step(..., encoder=encode)`.  The
+    output and the parameter gradients live in the graphs' static buffers: valid until the next call / backward.
+    Buffers (BatchNorm running statistics) are restored after the capture's warm-up passes."""
+    keys = [k for k in ("locs", "demand") if k in td.keys()]
+
+    class _Encode(torch.nn.Module):
+        def __init__(self, enc):
+            super().__init__()
+            self.enc = enc
+
+        def forward(self, *xs):
+            return self.enc(dict(zip(keys, xs)))[0]
+
+    mod = _Encode(policy.encoder)
+    mod.train(policy.encoder.training)
+    saved = {k: v.clone() for k, v in mod.named_buffers()}
+    graphed = torch.cuda.make_graphed_callables(mod, tuple(td[k].detach().clone() for k in keys),
+                                                num_warmup_iters=num_warmup_iters)
+    with torch.no_grad():
+        for k, v in mod.named_buffers():
+            v.copy_(saved[k])
+    return lambda td_: graphed(*(td_[k] for k in keys))
+
+
 def pomo_train_step(policy, env, td, optimizer=None, num_starts: Optional[int] = None, noise_seed: Optional[int] = None,
-                    instance_offset: int = 0, max_grad_norm: Optional[float] = 1.0, group=None) -> Dict[str, float]:
+                    instance_offset: int = 0, max_grad_norm: Optional[float] = 1.0, group=None,
+                    encoder=None) -> Dict[str, float]:
     """One POMO training step on this rank's shard `td`: sampled multistart rollout (fused kernel), differentiable
     re-evaluation, shared-baseline REINFORCE loss, backward, one all-reduce, clip, optimiser step.
+    `encoder`: an `encode(td) -> h` replacing `policy.encoder(td)[0]` (see `graphed_encoder`).
     `noise_seed=None` draws a fresh seed per step from torch's global generator (decoding.fresh_noise_seed); ranks
     seeded alike draw alike and the noise is keyed by `instance_offset + b`, so shards never share noise."""
     kw = {} if num_starts is None else {"num_starts": num_starts}
     # ONE encoder pass per step, as in the reference's single differentiable forward (train-mode BatchNorm statistics
     # are updated once, and the rollout samples from exactly the embeddings the loss differentiates)
     with torch.enable_grad():
-        h, _ = policy.encoder(td)
+        h = encoder(td) if encoder is not None else policy.encoder(td)[0]
     with torch.no_grad():
         out = policy(td, env, decode_type="multistart_sampling", noise_seed=noise_seed,
                      instance_offset=instance_offset, hidden=h, **kw)

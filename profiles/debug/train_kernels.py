@@ -17,12 +17,13 @@ def main():
     env = P.get_env("cvrp", generator_params=dict(num_loc=100), device=dev)
     inst = {k: v for k, v in P.CVRPGenerator(num_loc=100)(B).items() if k != "capacity"}
     td = env.reset(P.TensorDict({k: v.to(dev) for k, v in inst.items()}, batch_size=[B]))
+    encode = T.graphed_encoder(pol, td) if os.environ.get("R4_GRAPH_ENCODER", "1") == "1" else None
     for it in range(3):
-        T.pomo_train_step(pol, env, td.clone(), opt, noise_seed=it)
+        T.pomo_train_step(pol, env, td.clone(), opt, noise_seed=it, encoder=encode)
     torch.cuda.synchronize()
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
         for it in range(3):
-            T.pomo_train_step(pol, env, td.clone(), opt, noise_seed=10 + it)
+            T.pomo_train_step(pol, env, td.clone(), opt, noise_seed=10 + it, encoder=encode)
         torch.cuda.synchronize()
     ev = [e for e in prof.key_averages() if e.device_time_total > 0 and e.device_type == torch.autograd.DeviceType.CUDA]
     ev.sort(key=lambda e: -e.device_time_total)

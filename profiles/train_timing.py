@@ -19,6 +19,7 @@ def main():
     inst = {k: v for k, v in P.CVRPGenerator(num_loc=100)(B).items() if k != "capacity"}
     td = env.reset(P.TensorDict({k: v.to(dev) for k, v in inst.items()}, batch_size=[B]))
     ev = lambda: torch.cuda.Event(enable_timing=True)
+    encode = T.graphed_encoder(pol, td) if os.environ.get("R4_GRAPH_ENCODER", "1") == "1" else None
     rows = []
     for it in range(3 + 5):
         e = [ev() for _ in range(6)]
@@ -29,7 +30,7 @@ def main():
         S = out["actions"].shape[0] // B
         states = T.teacher_forced_states(env, td, out["actions"], S)
         e[2].record()
-        ll = T.evaluate_log_likelihood(pol, td, env, out["actions"], S, states=states)
+        ll = T.evaluate_log_likelihood(pol, td, env, out["actions"], S, states=states, hidden=encode(td) if encode else None)
         loss, _ = T.reinforce_loss(out["reward"], ll, S)
         e[3].record()
         opt.zero_grad(set_to_none=True)

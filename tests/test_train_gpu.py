@@ -230,3 +230,29 @@ def test_fused_query_against_fp64(B, S, Tm, n, tsp, skew):
         scale = max(a64[i].grad.abs().max().item(), 1e-6)
         assert (a32[i].grad.double() - a64[i].grad).abs().max().item() / scale < 2e-5, name
     assert a32[2 if tsp else 1].grad is None
+
+
+@pytest.mark.parametrize("env_name", ["tsp", "cvrp"])
+def test_graphed_encoder_step_equals_the_eager_step(env_name):
+    """train.graphed_encoder: encoder forward / backward replayed from CUDA graphs give the loss and the gradients of the
+    module-by-module step (same kernels, same order), on fresh instances of the captured shape, and leave the
+    normalisation buffers as they were."""
+    import copy
+    inst, pol, env, td = _setup(env_name, 4, 20, seed=11)
+    pol.train()
+    pol2 = copy.deepcopy(pol)
+    bufs = {k: v.clone() for k, v in pol2.encoder.named_buffers()}
+    encode = train.graphed_encoder(pol2, td)
+    for k, v in pol2.encoder.named_buffers():
+        assert torch.equal(v, bufs[k]), k
+    for seed in (3, 4):
+        inst_s, _, _, td_s = _setup(env_name, 4, 20, seed=20 + seed)
+        a = train.pomo_train_step(pol, env, td_s.clone(), optimizer=None, noise_seed=seed, max_grad_norm=None)
+        b = train.pomo_train_step(pol2, env, td_s.clone(), optimizer=None, noise_seed=seed, max_grad_norm=None,
+                                  encoder=encode)
+        assert abs(a["loss"] - b["loss"]) < 1e-6 * max(1.0, abs(a["loss"])) and a["reward"] == b["reward"]
+        gmax = max(p.grad.abs().max().item() for p in pol.parameters())
+        for (k, p), (_, p2) in zip(pol.named_parameters(), pol2.named_parameters()):
+            # (biases in front of a normalisation layer have gradients that are rounding noise: floor the scale)
+            scale = max(p.grad.abs().max().item(), 1e-2 * gmax)
+            assert (p.grad - p2.grad).abs().max().item() / scale < 1e-4, k
