@@ -194,6 +194,7 @@ __device__ __forceinline__ void glimpse_rows(const float* s_gk, const float* s_g
 }
 
 // ---- forward: logp[b,r]; saved for the backward: heads [B,R,E], lse_h [B,R,H], lse_z [B,R], maskw [B,R,4] -----------------
+template <bool kPtr>
 __global__ void __launch_bounds__(kThreads, 1)
     eval_ll_fwd_kernel(const float* __restrict__ q, const float* __restrict__ gk, const float* __restrict__ gv,
                        const float* __restrict__ lkf, const uint8_t* __restrict__ mask, const int64_t* __restrict__ taken,
@@ -207,7 +208,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     const int64_t b = blockIdx.x;
     copy_table_swz(s_gk, gk + b * n * kE, n);
     copy_table_swz(s_gv, gv + b * n * kE, n);
-    copy_table_swz(s_lk, lkf + b * n * kE, n);
+    if (kPtr) copy_table_swz(s_lk, lkf + b * n * kE, n);
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
     const int ri = lane >> 3, h = lane & 7;
@@ -245,6 +246,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             st16(heads + row * kE + 16 * h, o);
             lse_h[row * kH + h] = lh;
         }
+        if (!kPtr) continue;   // the pointer runs on eval_ptr_fwd_tc_kernel
         // pointer: eight nodes per iteration; after the transposed reduction lane h holds the logit of node j[h]
         const int a = (int)taken[row];
         float zmax = -INFINITY, zsum = 0.f, za = -INFINITY;
@@ -744,6 +746,212 @@ __global__ void __launch_bounds__(256, 1)
     if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
+// ---- forward, pointer part on the tensor cores: logp and lse_z from the heads the glimpse kernel wrote ------------------------------
+// Per tile of 128 rows the logits U = heads lkf^T are 24 split-fp16 MMAs against the resident lkf tile (as in the backward's row
+// pass above); thread (row, 64 nodes) applies scale, tanh clip, mask and temperature, and the two threads of a row combine maximum,
+// sum and the taken node's value through shared memory.  Software pipeline over the tiles of a CTA: the fp32 heads of tile t+2
+// arrive by cp.async while tile t+1 is converted to the fp16 operand and multiplied into the second accumulator, and tile t's
+// logits are read from the first.
+namespace pfw {
+constexpr int kT = 128;
+constexpr int kStride = 132;                    // floats per staged row (+4: the conversion's 16 rows per warp hit distinct banks)
+constexpr uint32_t kHalf = 32 * 1024;
+constexpr uint32_t kOffL = 0;                   // lkf [node][ch] hi | lo (B operand, resident)
+constexpr uint32_t kOffH = 2 * kHalf;           // heads tile [row][ch] hi | lo (A operand)
+constexpr uint32_t kOffStage = 4 * kHalf;       // fp32 heads tile as it arrives
+constexpr uint32_t kOffRow = kOffStage + kT * kStride * 4;   // per row: taken (i32), 4 mask words; 2 x (max, sum, za) exchange
+constexpr uint32_t kOffBar = kOffRow + kT * (20 + 24);
+constexpr size_t kSmem = kOffBar + 64;
+}  // namespace pfw
+
+__global__ void __launch_bounds__(256, 1)
+    eval_ptr_fwd_tc_kernel(const float* __restrict__ lkf, const uint32_t* __restrict__ maskw, const int64_t* __restrict__ taken,
+                           const float* __restrict__ heads, float* __restrict__ logp, float* __restrict__ lse_z, int64_t R, int n,
+                           float clip, float temperature) {
+    using namespace tc;
+    extern __shared__ __align__(128) unsigned char smb[];
+    float* s_stage = reinterpret_cast<float*>(smb + pfw::kOffStage);
+    int* s_a = reinterpret_cast<int*>(smb + pfw::kOffRow);
+    uint32_t* s_mw = reinterpret_cast<uint32_t*>(s_a + pfw::kT);
+    float* s_x = reinterpret_cast<float*>(s_mw + 4 * pfw::kT);       // [2 halves][3][128]: max, sum, za
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smb + pfw::kOffBar);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smb + pfw::kOffBar + 32);
+    const int64_t b = blockIdx.x;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    int64_t r0, r1;
+    row_range(R, r0, r1);
+    if (r0 >= r1) return;
+    const int ntiles = (int)((r1 - r0 + pfw::kT - 1) / pfw::kT);
+    if (tid == 0) {
+        mbar_init(bars, 1);
+        mbar_init(bars + 1, 1);
+        fence_mbar_init();
+    }
+    __syncwarp();
+    if (warp == 0) tmem_alloc(tmem_slot, 256);
+
+    auto fetch = [&](int t) {   // fp32 heads of tile t -> staging (rows past the end keep stale values: their logits are masked)
+        const int64_t rt = r0 + (int64_t)t * pfw::kT;
+        const int rows = (int)(r1 - rt < pfw::kT ? r1 - rt : pfw::kT);
+        for (int i = tid; i < rows * 32; i += 256) {
+            const int r = i >> 5, c4 = i & 31;
+            cp_async16(s_stage + r * pfw::kStride + 4 * c4, heads + (b * R + rt + r) * kE + 4 * c4);
+        }
+        cp_async_commit();
+    };
+    auto convert = [&]() {      // staging -> K-major fp16 hi | lo, item = (row, 8-channel chunk)
+        for (int i = tid; i < pfw::kT * 16; i += 256) {
+            const int r = i >> 4, c = i & 15;
+            const float4 a = *reinterpret_cast<const float4*>(s_stage + r * pfw::kStride + 8 * c);
+            const float4 bb = *reinterpret_cast<const float4*>(s_stage + r * pfw::kStride + 8 * c + 4);
+            uint32_t hi[4], lo[4];
+            split2(a.x, a.y, hi[0], lo[0]);
+            split2(a.z, a.w, hi[1], lo[1]);
+            split2(bb.x, bb.y, hi[2], lo[2]);
+            split2(bb.z, bb.w, hi[3], lo[3]);
+            unsigned char* dst = smb + pfw::kOffH + (uint32_t)(r >> 3) * 2048u + (uint32_t)c * 128u + (uint32_t)(r & 7) * 16u;
+            *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(dst + pfw::kHalf) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        }
+    };
+    const uint32_t sb = smem_u32(smb);
+    auto issue = [&](uint32_t tmem, int t) {   // U(t) = heads lkf^T into accumulator t & 1
+        if (warp == 0) {
+            if (elect_one()) {
+                tc_fence_after();
+                const uint32_t id = idesc_f16(128, 128);
+                uint64_t a_hi = smem_desc(sb + pfw::kOffH, 128, 2048), a_lo = smem_desc(sb + pfw::kOffH + pfw::kHalf, 128, 2048);
+                uint64_t b_hi = smem_desc(sb + pfw::kOffL, 128, 2048), b_lo = smem_desc(sb + pfw::kOffL + pfw::kHalf, 128, 2048);
+                const uint32_t d = tmem + 128u * (uint32_t)(t & 1);
+#pragma unroll
+                for (int ks = 0; ks < 8; ++ks) {
+                    mma_ss(d, a_hi, b_hi, id, ks == 0 ? 0u : 1u);
+                    mma_ss(d, a_hi, b_lo, id, 1u);
+                    mma_ss(d, a_lo, b_hi, id, 1u);
+                    a_hi += 256u >> 4;
+                    a_lo += 256u >> 4;
+                    b_hi += 256u >> 4;
+                    b_lo += 256u >> 4;
+                }
+                tc_commit(bars + (t & 1));
+            }
+            __syncwarp();
+        }
+    };
+    // per-row scalars of a tile travel through registers one tile ahead (thread = row)
+    int reg_a = -1;
+    uint32_t reg_mw[4] = {0u, 0u, 0u, 0u};
+    auto fetch_rows = [&](int t) {
+        if (tid < pfw::kT) {
+            const int64_t rt = r0 + (int64_t)t * pfw::kT;
+            const bool ok = t < ntiles && rt + tid < r1;
+            const int64_t row = b * R + (ok ? rt + tid : r0);
+            reg_a = ok ? (int)taken[row] : -1;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) reg_mw[k] = ok ? maskw[row * kNB + k] : 0u;
+        }
+    };
+
+    fetch(0);
+    fetch_rows(0);
+    for (int i = tid; i < 128 * 16; i += 256) {   // resident B operand: lkf (K = channels), nodes >= n are zero
+        const int m = i >> 4, c = i & 15;
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a;
+        if (m < n) {
+            a = ld4(lkf + ((size_t)b * n + m) * kE + 8 * c);
+            bb = ld4(lkf + ((size_t)b * n + m) * kE + 8 * c + 4);
+        }
+        uint32_t hi[4], lo[4];
+        split2(a.x, a.y, hi[0], lo[0]);
+        split2(a.z, a.w, hi[1], lo[1]);
+        split2(bb.x, bb.y, hi[2], lo[2]);
+        split2(bb.z, bb.w, hi[3], lo[3]);
+        unsigned char* dst = smb + pfw::kOffL + (uint32_t)(m >> 3) * 2048u + (uint32_t)c * 128u + (uint32_t)(m & 7) * 16u;
+        *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(dst + pfw::kHalf) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+    cp_async_wait<0>();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    convert();
+    fence_proxy_async();
+    __syncthreads();
+    issue(tmem, 0);
+    if (ntiles > 1) fetch(1);
+
+    const int q4 = warp & 3, chalf = warp >> 2;          // TMEM lane quadrant (row = 32 q4 + lane), node half
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * q4) << 16);
+    const float sc = (clip > 0.f ? clip : 1.0f) / temperature;
+    uint32_t ph[2] = {0u, 0u};
+    for (int t = 0; t < ntiles; ++t) {
+        const int64_t rt = r0 + (int64_t)t * pfw::kT;
+        const int rows = (int)(r1 - rt < pfw::kT ? r1 - rt : pfw::kT);
+        if (tid < pfw::kT) {
+            s_a[tid] = reg_a;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) s_mw[tid * 4 + k] = reg_mw[k];
+        }
+        fetch_rows(t + 1);
+        mbar_wait(bars + (t & 1), ph[t & 1]);             // U(t) is complete: the operand tile is free
+        ph[t & 1] ^= 1u;
+        tc_fence_after();
+        if (t + 1 < ntiles) {
+            cp_async_wait<0>();
+            __syncthreads();
+            convert();
+            fence_proxy_async();
+            __syncthreads();
+            issue(tmem, t + 1);
+            if (t + 2 < ntiles) fetch(t + 2);
+        } else {
+            __syncthreads();
+        }
+        const int r = 32 * q4 + lane;
+        const int a = s_a[r];
+        const uint32_t m0 = s_mw[r * 4 + 2 * chalf], m1 = s_mw[r * 4 + 2 * chalf + 1];
+        float z[64];
+        float zmax = -INFINITY, za = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < 64; c += 16) {
+            uint32_t uv[16];
+            tmem_ld16(lane_base + 128u * (uint32_t)(t & 1) + (uint32_t)(64 * chalf + c), uv);
+            tc_wait_ld();
+            const uint32_t bits = ((c < 32 ? m0 : m1) >> (c & 31)) & 0xffffu;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float u = __uint_as_float(uv[i]) * kInvSqrtE;
+                const float zv = (clip > 0.f ? tanh_fast_ev(u) : u) * sc;     // decoding.py:171-172, :180
+                z[c + i] = (bits >> i) & 1u ? zv : -INFINITY;                  // :177
+                zmax = fmaxf(zmax, z[c + i]);
+                if (64 * chalf + c + i == a) za = z[c + i];
+            }
+        }
+        s_x[(chalf * 3 + 0) * pfw::kT + r] = zmax;
+        s_x[(chalf * 3 + 2) * pfw::kT + r] = za;
+        __syncthreads();
+        const float mx = fmaxf(zmax, s_x[((chalf ^ 1) * 3 + 0) * pfw::kT + r]);
+        const float mref = (mx == -INFINITY) ? 0.f : mx;
+        float zsum = 0.f;
+#pragma unroll
+        for (int i = 0; i < 64; ++i) zsum += __expf(z[i] - mref);
+        s_x[(chalf * 3 + 1) * pfw::kT + r] = zsum;
+        __syncthreads();
+        if (chalf == 0 && r < rows) {
+            const float tot = zsum + s_x[(1 * 3 + 1) * pfw::kT + r];
+            const float zt = fmaxf(za, s_x[(1 * 3 + 2) * pfw::kT + r]);
+            const bool any = tot > 0.f;
+            const float lz = any ? mref + __logf(tot) : 0.f;
+            logp[b * R + rt + r] = any ? zt - lz : 0.f;      // :190 log_softmax, :462 gather
+            lse_z[b * R + rt + r] = lz;
+        }
+        tc_fence_before();
+        __syncthreads();   // the row scalars, the exchange words and accumulator t & 1 are reused
+    }
+    if (warp == 0) tmem_dealloc(tmem, 256);
+}
+
 // ---- backward, glimpse part of the node pass on the tensor cores: dgk = dS^T (0.25 Q), dgv = P^T dO ------------------------------
 // The TRANSPOSED score tile is computed so that P^T and dS^T come out with TMEM lane = node, which is the M dimension the two
 // reductions over rows need (the flash-attention backward arrangement).  Per CTA (instance, row range), per tile of 128 rows,
@@ -1095,13 +1303,25 @@ extern "C" int rl4co_eval_ll_fwd(const float* q, const float* gk, const float* g
     int rc;
     if ((rc = eval_check("eval_ll_fwd", B, R, n_nodes, temperature))) return rc;
     if (B == 0 || R == 0) return RL4CO_OK;
-    const size_t smem = 3ull * n_nodes * kE * sizeof(float);
-    if ((rc = ev::set_smem(ev::eval_ll_fwd_kernel, smem, "eval_ll_fwd"))) return rc;
     dim3 grid((unsigned)B, (unsigned)ev::grid_split(B, 1));
-    ev::eval_ll_fwd_kernel<<<grid, ev::kThreads, smem, (cudaStream_t)stream>>>(q, gk, gv, lkf, mask, taken, logp, heads, lse_h,
-                                                                              lse_z, maskw, R, n_nodes, tanh_clipping,
-                                                                              temperature);
-    R4_CHECK_LAUNCH("eval_ll_fwd");
+    const char* mode = getenv("R4_EVAL_PTR_FWD");
+    if (mode && mode[0] == 'c') {   // experiment switch: the CUDA-core pointer inside the forward kernel
+        const size_t smem = 3ull * n_nodes * kE * sizeof(float);
+        if ((rc = ev::set_smem(ev::eval_ll_fwd_kernel<true>, smem, "eval_ll_fwd"))) return rc;
+        ev::eval_ll_fwd_kernel<true><<<grid, ev::kThreads, smem, (cudaStream_t)stream>>>(
+            q, gk, gv, lkf, mask, taken, logp, heads, lse_h, lse_z, maskw, R, n_nodes, tanh_clipping, temperature);
+        R4_CHECK_LAUNCH("eval_ll_fwd");
+        return RL4CO_OK;
+    }
+    const size_t smem = 2ull * n_nodes * kE * sizeof(float);
+    if ((rc = ev::set_smem(ev::eval_ll_fwd_kernel<false>, smem, "eval_ll_fwd (glimpse)"))) return rc;
+    ev::eval_ll_fwd_kernel<false><<<grid, ev::kThreads, smem, (cudaStream_t)stream>>>(
+        q, gk, gv, lkf, mask, taken, logp, heads, lse_h, lse_z, maskw, R, n_nodes, tanh_clipping, temperature);
+    R4_CHECK_LAUNCH("eval_ll_fwd (glimpse)");
+    if ((rc = ev::set_smem(ev::eval_ptr_fwd_tc_kernel, ev::pfw::kSmem, "eval_ll_fwd (pointer)"))) return rc;
+    ev::eval_ptr_fwd_tc_kernel<<<grid, 256, ev::pfw::kSmem, (cudaStream_t)stream>>>(lkf, maskw, taken, heads, logp, lse_z, R,
+                                                                                   n_nodes, tanh_clipping, temperature);
+    R4_CHECK_LAUNCH("eval_ll_fwd (pointer)");
     return RL4CO_OK;
 }
 
