@@ -1305,7 +1305,7 @@ extern "C" int rl4co_eval_ll_fwd(const float* q, const float* gk, const float* g
     if (B == 0 || R == 0) return RL4CO_OK;
     dim3 grid((unsigned)B, (unsigned)ev::grid_split(B, 1));
     const char* mode = getenv("R4_EVAL_PTR_FWD");
-    if (mode && mode[0] == 'c') {   // experiment switch: the CUDA-core pointer inside the forward kernel
+    if (!(mode && mode[0] == 't')) {   // experiment switch: R4_EVAL_PTR_FWD=tc runs the pointer on eval_ptr_fwd_tc_kernel
         const size_t smem = 3ull * n_nodes * kE * sizeof(float);
         if ((rc = ev::set_smem(ev::eval_ll_fwd_kernel<true>, smem, "eval_ll_fwd"))) return rc;
         ev::eval_ll_fwd_kernel<true><<<grid, ev::kThreads, smem, (cudaStream_t)stream>>>(
