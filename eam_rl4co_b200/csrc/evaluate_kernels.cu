@@ -4,11 +4,11 @@
 //
 // With the actions known, the rows (instance b, start s, step t) are independent: row r of instance b has its query q[b,r,:]
 // (context.py:118-157 gathers, built by the caller with autograd), its feasibility mask and its taken action.  All rows of an
-// instance share the three [n,128] tables, which a CTA keeps in shared memory; one warp owns one row at a time:
-//   glimpse  (attention.py:308-322): 8-head masked softmax attention, lane L holds channels 4L..4L+3 (head L/4),
-//   pointer  (attention.py:296-301,328; decoding.py:140-190): logits = heads . lkf[n] / sqrt(E), tanh clip, mask,
-//            temperature, log_softmax, gather at the taken action.
-// Only FEASIBLE nodes are visited (masked nodes have probability exactly 0 in both softmaxes and contribute no gradient).
+// instance share the three [n,128] tables, which a CTA keeps in shared memory:
+//   glimpse  (attention.py:308-322): 8-head masked softmax attention on the CUDA cores, a warp per four rows, lane = (row, head),
+//            only FEASIBLE nodes visited (masked nodes have probability exactly 0 and contribute no gradient);
+//   pointer  (attention.py:296-301,328; decoding.py:140-190): logits = heads . lkf[n] / sqrt(E) as tcgen05 MMAs per 128-row
+//            tile, then tanh clip, mask, temperature, log_softmax, gather at the taken action.
 // The backward recomputes the probabilities from the saved log-sum-exps (flash-attention style) in two passes:
 //   row pass : everything that reduces over NODES - du = d loss / d raw logit and dheads = dU lkf on tcgen05 (the logits are
 //             recomputed as an MMA per 128-row tile, du converted in place into the A operand of the second product); dq on
@@ -18,7 +18,7 @@
 //             atomics are CAS loops on sm_100: a first version that accumulated the table gradients in shared memory spent
 //             25 of 31 ms of the c5 evaluate in ATOMS.CAST.SPIN.)
 //
-// exp of the glimpse softmax on MUFU ex2 (as the tensor-path rollout), tanhf / expf / logf in the pointer.
+// exp / tanh / log on the MUFU approximations (ex2, rcp, lg2: the arithmetic of the tensor-path rollout kernels).
 #include "decode_core.cuh"
 #include "tc_ptx.cuh"
 
@@ -28,18 +28,6 @@ namespace ev {
 constexpr int kThreads = 512;
 constexpr float kInvSqrtE = 0.08838834764831845f;   // 1 / sqrt(128)
 
-__device__ __forceinline__ void load_mask_words(const uint8_t* __restrict__ m, int n, int lane, uint32_t (&w)[kNB]) {
-#pragma unroll
-    for (int blk = 0; blk < kNB; ++blk) {
-        const int i = 32 * blk + lane;
-        w[blk] = __ballot_sync(kFull, i < n && m[i] != 0);
-    }
-}
-
-__device__ __forceinline__ void copy_table(float* dst, const float* __restrict__ src, int n) {
-    for (int i = threadIdx.x; i < n * (kE / 4); i += blockDim.x)
-        reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(src)[i];
-}
 // The row kernels read a table row as "head h, 4-channel chunk i" = 8 lanes x 16 B per LDS.128; with the natural layout the
 // lanes are 64 B apart and heads h, h + 2, h + 4, h + 6 share banks (4-way conflict, measured 2.2x on the forward kernel).
 // Swizzled layout: chunk i of head h of node nd at nd * 128 + 32 i + 4 h, i.e. the 8 lanes read 128 contiguous bytes.
@@ -49,10 +37,6 @@ __device__ __forceinline__ void copy_table_swz(float* dst, const float* __restri
         reinterpret_cast<float4*>(dst)[nd * 32 + (c4 & 3) * 8 + (c4 >> 2)] = reinterpret_cast<const float4*>(src)[i];
     }
 }
-__device__ __forceinline__ float sel4(const float (&v)[kNB], int k) {
-    return k == 0 ? v[0] : (k == 1 ? v[1] : (k == 2 ? v[2] : v[3]));
-}
-
 __device__ __forceinline__ uint32_t sel4u(const uint32_t (&v)[kNB], int k) {
     return k == 0 ? v[0] : (k == 1 ? v[1] : (k == 2 ? v[2] : v[3]));
 }
@@ -129,24 +113,6 @@ __device__ __forceinline__ void next_nodes(uint32_t& wb, int (&j)[G], bool (&ok)
 #pragma unroll
     for (int u = 1; u < G; ++u) j[u] = ok[u] ? j[u] : j[0];
 }
-// Transposed reduction over the 8 head lanes of a row: d[u] is this lane's partial of value u; afterwards lane h of the row
-// holds the total of value h (7 shuffles instead of 8 x 3).
-__device__ __forceinline__ float reduce_scatter8(const float (&d)[8], int h) {
-    const bool b2 = h & 4, b1 = h & 2, b0 = h & 1;
-    float a[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) a[i] = (b2 ? d[4 + i] : d[i]) + __shfl_xor_sync(kFull, b2 ? d[i] : d[4 + i], 4);
-    float e[2];
-#pragma unroll
-    for (int i = 0; i < 2; ++i) e[i] = (b1 ? a[2 + i] : a[i]) + __shfl_xor_sync(kFull, b1 ? a[i] : a[2 + i], 2);
-    return (b0 ? e[1] : e[0]) + __shfl_xor_sync(kFull, b0 ? e[0] : e[1], 1);
-}
-__device__ __forceinline__ int sel8i(const int (&v)[8], int k) {
-    int r = v[0];
-#pragma unroll
-    for (int u = 1; u < 8; ++u) r = (k == u) ? v[u] : r;
-    return r;
-}
 __device__ __forceinline__ bool bit_of(const uint32_t (&w)[kNB], int node) {
     return (sel4u(w, node >> 5) >> (node & 31)) & 1u;
 }
@@ -193,22 +159,18 @@ __device__ __forceinline__ void glimpse_rows(const float* s_gk, const float* s_g
     lse = any ? m + logf(l) : 0.f;
 }
 
-// ---- forward: logp[b,r]; saved for the backward: heads [B,R,E], lse_h [B,R,H], lse_z [B,R], maskw [B,R,4] -----------------
-template <bool kPtr>
+// ---- forward, glimpse: heads [B,R,E], lse_h [B,R,H] and the mask as bit words maskw [B,R,4] (saved for the backward; the
+// pointer - logp [B,R], lse_z [B,R] - runs on eval_ptr_fwd_tc_kernel from the heads written here) ------------------------------
 __global__ void __launch_bounds__(kThreads, 1)
-    eval_ll_fwd_kernel(const float* __restrict__ q, const float* __restrict__ gk, const float* __restrict__ gv,
-                       const float* __restrict__ lkf, const uint8_t* __restrict__ mask, const int64_t* __restrict__ taken,
-                       float* __restrict__ logp, float* __restrict__ heads, float* __restrict__ lse_h,
-                       float* __restrict__ lse_z, uint32_t* __restrict__ maskw, int64_t R, int n, float clip,
-                       float temperature) {
+    eval_glimpse_fwd_kernel(const float* __restrict__ q, const float* __restrict__ gk, const float* __restrict__ gv,
+                            const uint8_t* __restrict__ mask, float* __restrict__ heads, float* __restrict__ lse_h,
+                            uint32_t* __restrict__ maskw, int64_t R, int n) {
     extern __shared__ __align__(16) float sm[];
     float* s_gk = sm;
     float* s_gv = sm + n * kE;
-    float* s_lk = sm + 2 * n * kE;
     const int64_t b = blockIdx.x;
     copy_table_swz(s_gk, gk + b * n * kE, n);
     copy_table_swz(s_gv, gv + b * n * kE, n);
-    if (kPtr) copy_table_swz(s_lk, lkf + b * n * kE, n);
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
     const int ri = lane >> 3, h = lane & 7;
@@ -245,52 +207,6 @@ __global__ void __launch_bounds__(kThreads, 1)
         if (valid) {
             st16(heads + row * kE + 16 * h, o);
             lse_h[row * kH + h] = lh;
-        }
-        if (!kPtr) continue;   // the pointer runs on eval_ptr_fwd_tc_kernel
-        // pointer: eight nodes per iteration; after the transposed reduction lane h holds the logit of node j[h]
-        const int a = (int)taken[row];
-        float zmax = -INFINITY, zsum = 0.f, za = -INFINITY;
-#pragma unroll 1
-        for (int blk = 0; blk < kNB; ++blk) {
-            uint32_t wb = sel4u(wu, blk);
-            while (wb) {
-                int j[8];
-                bool ok[8];
-                next_nodes<8>(wb, j, ok);
-                float d[8];
-#pragma unroll
-                for (int u = 0; u < 8; ++u) d[u] = dot16(o, s_lk + (blk * 32 + j[u]) * kE + 4 * h);
-                const float tot = reduce_scatter8(d, h);
-                const int jm = sel8i(j, h);
-                bool f = (sel4u(w, blk) >> jm) & 1u;
-#pragma unroll
-                for (int u = 1; u < 8; ++u) f = f && (ok[u] || h != u);
-                float z = tot * kInvSqrtE;
-                if (clip > 0.f) z = tanhf(z) * clip;            // decoding.py:171-172
-                z = f ? z / temperature : -INFINITY;            // :177, :180
-                const float mn = fmaxf(zmax, z);
-                const float mref = (mn == -INFINITY) ? 0.f : mn;
-                zsum = zsum * expf(zmax - mref) + expf(z - mref);
-                zmax = mn;
-                if (f && blk * 32 + jm == a) za = z;
-            }
-        }
-        // combine the eight lanes of the row: log-sum-exp and the taken action's z
-#pragma unroll
-        for (int o2 = 4; o2 > 0; o2 >>= 1) {
-            const float om = __shfl_xor_sync(kFull, zmax, o2), os = __shfl_xor_sync(kFull, zsum, o2);
-            const float oa = __shfl_xor_sync(kFull, za, o2);
-            const float mn = fmaxf(zmax, om);
-            const float mref = (mn == -INFINITY) ? 0.f : mn;
-            zsum = zsum * expf(zmax - mref) + os * expf(om - mref);
-            zmax = mn;
-            za = fmaxf(za, oa);
-        }
-        if (valid && h == 0) {
-            const bool any = zsum > 0.f;
-            const float lz = any ? zmax + logf(zsum) : 0.f;
-            logp[row] = any ? za - lz : 0.f;                    // :190 log_softmax, :462 gather
-            lse_z[row] = lz;
         }
     }
 }
@@ -525,6 +441,9 @@ __global__ void __launch_bounds__(256, 1)
 // the feasible nodes (softmax from the saved lse_z), stores it (du_t feeds eval_dlk_tc_kernel) and writes it back IN PLACE as
 // a TS-form A operand; dheads = du lkf is 24 TS-form MMAs against the resident TRANSPOSED lkf tile.  The dot products that
 // made up most of the CUDA-core version's instructions (1.6 ms) are gone.
+// Item mapping of the (row, 8-channel chunk) conversions into a K-major operand tile ("item_rc"): consecutive lanes take the 8 rows
+// of a core matrix (16 bytes apart in the tile), then the next chunk: a warp's STS.128 covers 512 contiguous bytes.  (Lanes running
+// over the chunks of ONE row are 128 bytes apart in the tile - a 16-way bank conflict that cost the pointer kernels half their time.)
 namespace pbw {
 constexpr int kT = 128;
 constexpr uint32_t kHalf = 32 * 1024;           // [128 x 128] fp16 K-major: 16 row groups x 16 chunks x 128 B
@@ -569,7 +488,7 @@ __global__ void __launch_bounds__(256, 1)
     if (warp == 0) tmem_alloc(tmem_slot, 256);
     // resident B operands: lkf (K = channels) and its transpose (K = nodes); nodes >= n are zero
     for (int i = tid; i < 128 * 16; i += 256) {
-        const int m = i >> 4, c = i & 15;                // lkf: (node m, 8-channel chunk c)
+        const int m = 8 * (i >> 7) + (i & 7), c = (i >> 3) & 15;   // lkf: (node m, 8-channel chunk c), see item_rc
         float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a;
         if (m < n) {
             a = ld4(lkf + ((size_t)b * n + m) * kE + 8 * c);
@@ -605,17 +524,45 @@ __global__ void __launch_bounds__(256, 1)
     const uint32_t lane_base = tmem + ((uint32_t)(32 * q4) << 16);
     const float sc = (clip > 0.f ? clip : 1.0f) / temperature;
     uint32_t p1 = 0, p2 = 0;
+    // The fp32 heads of a tile (8 items = 16 float4 per thread) and its per-row scalars travel through registers ONE TILE AHEAD:
+    // the loads of tile t+1 are issued right after tile t's first product and land during its elementwise pass.
+    float4 pre[16];
+    float pre_g = 0.f, pre_lz = 0.f;
+    int pre_a = -1;
+    uint32_t pre_mw[4] = {0u, 0u, 0u, 0u};
+    auto prefetch = [&](int t) {
+        const int64_t rt = r0 + (int64_t)t * pbw::kT;
+        const int rows = t < ntiles ? (int)(r1 - rt < pbw::kT ? r1 - rt : pbw::kT) : 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int i = tid + 256 * k;
+            const int r = 8 * (i >> 7) + (i & 7), c = (i >> 3) & 15;   // conflict-free operand stores (item_rc)
+            pre[2 * k] = pre[2 * k + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (r < rows) {
+                pre[2 * k] = ld4(heads + (b * R + rt + r) * kE + 8 * c);
+                pre[2 * k + 1] = ld4(heads + (b * R + rt + r) * kE + 8 * c + 4);
+            }
+        }
+        if (tid < pbw::kT) {
+            const bool ok = tid < rows;
+            const int64_t row = b * R + (ok ? rt + tid : r0);
+            pre_g = ok ? dlogp[row] : 0.f;
+            pre_lz = ok ? lse_z[row] : 0.f;
+            pre_a = ok ? (int)taken[row] : -1;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) pre_mw[k] = ok ? maskw[row * kNB + k] : 0u;
+        }
+    };
+    prefetch(0);
     for (int t = 0; t < ntiles; ++t) {
         const int64_t rt = r0 + (int64_t)t * pbw::kT;
         const int rows = (int)(r1 - rt < pbw::kT ? r1 - rt : pbw::kT);
         // heads tile -> K-major fp16 hi | lo (item = (row, 8-channel chunk)); per-row scalars
-        for (int i = tid; i < pbw::kT * 16; i += 256) {
-            const int r = i >> 4, c = i & 15;
-            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a;
-            if (r < rows) {
-                a = ld4(heads + (b * R + rt + r) * kE + 8 * c);
-                bb = ld4(heads + (b * R + rt + r) * kE + 8 * c + 4);
-            }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int i = tid + 256 * k;
+            const int r = 8 * (i >> 7) + (i & 7), c = (i >> 3) & 15;
+            const float4 a = pre[2 * k], bb = pre[2 * k + 1];
             uint32_t hi[4], lo[4];
             split2(a.x, a.y, hi[0], lo[0]);
             split2(a.z, a.w, hi[1], lo[1]);
@@ -626,13 +573,11 @@ __global__ void __launch_bounds__(256, 1)
             *reinterpret_cast<uint4*>(dst + pbw::kHalf) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
         }
         if (tid < pbw::kT) {
-            const bool ok = tid < rows;
-            const int64_t row = b * R + rt + (ok ? tid : 0);
-            s_g[tid] = ok ? dlogp[row] : 0.f;
-            s_lz[tid] = ok ? lse_z[row] : 0.f;
-            s_a[tid] = ok ? (int)taken[row] : -1;
+            s_g[tid] = pre_g;
+            s_lz[tid] = pre_lz;
+            s_a[tid] = pre_a;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) s_mw[tid * 4 + k] = ok ? maskw[row * kNB + k] : 0u;
+            for (int k = 0; k < 4; ++k) s_mw[tid * 4 + k] = pre_mw[k];
         }
         fence_proxy_async();
         __syncthreads();
@@ -656,6 +601,7 @@ __global__ void __launch_bounds__(256, 1)
             }
             __syncwarp();
         }
+        prefetch(t + 1);
         mbar_wait(bar1, p1);
         p1 ^= 1u;
         tc_fence_after();
@@ -748,7 +694,7 @@ __global__ void __launch_bounds__(256, 1)
 
 // ---- forward, pointer part on the tensor cores: logp and lse_z from the heads the glimpse kernel wrote ------------------------------
 // Per tile of 128 rows the logits U = heads lkf^T are 24 split-fp16 MMAs against the resident lkf tile (as in the backward's row
-// pass above); thread (row, 64 nodes) applies scale, tanh clip, mask and temperature, and the two threads of a row combine maximum,
+// pass above); thread (row, 32 nodes) applies scale, tanh clip, mask and temperature, and the four threads of a row combine maximum,
 // sum and the taken node's value through shared memory.  Software pipeline over the tiles of a CTA: the fp32 heads of tile t+2
 // arrive by cp.async while tile t+1 is converted to the fp16 operand and multiplied into the second accumulator, and tile t's
 // logits are read from the first.
@@ -759,12 +705,13 @@ constexpr uint32_t kHalf = 32 * 1024;
 constexpr uint32_t kOffL = 0;                   // lkf [node][ch] hi | lo (B operand, resident)
 constexpr uint32_t kOffH = 2 * kHalf;           // heads tile [row][ch] hi | lo (A operand)
 constexpr uint32_t kOffStage = 4 * kHalf;       // fp32 heads tile as it arrives
-constexpr uint32_t kOffRow = kOffStage + kT * kStride * 4;   // per row: taken (i32), 4 mask words; 2 x (max, sum, za) exchange
-constexpr uint32_t kOffBar = kOffRow + kT * (20 + 24);
+constexpr int kThreads = 512;                   // thread = (row, 32 nodes): 16 warps hide the MUFU / tcgen05.ld latencies
+constexpr uint32_t kOffRow = kOffStage + kT * kStride * 4;   // per row: taken (i32), 4 mask words; 4 x (max, sum, za) exchange
+constexpr uint32_t kOffBar = kOffRow + kT * (20 + 48);
 constexpr size_t kSmem = kOffBar + 64;
 }  // namespace pfw
 
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(pfw::kThreads, 1)
     eval_ptr_fwd_tc_kernel(const float* __restrict__ lkf, const uint32_t* __restrict__ maskw, const int64_t* __restrict__ taken,
                            const float* __restrict__ heads, float* __restrict__ logp, float* __restrict__ lse_z, int64_t R, int n,
                            float clip, float temperature) {
@@ -773,7 +720,7 @@ __global__ void __launch_bounds__(256, 1)
     float* s_stage = reinterpret_cast<float*>(smb + pfw::kOffStage);
     int* s_a = reinterpret_cast<int*>(smb + pfw::kOffRow);
     uint32_t* s_mw = reinterpret_cast<uint32_t*>(s_a + pfw::kT);
-    float* s_x = reinterpret_cast<float*>(s_mw + 4 * pfw::kT);       // [2 halves][3][128]: max, sum, za
+    float* s_x = reinterpret_cast<float*>(s_mw + 4 * pfw::kT);       // [4 node quarters][3][128]: max, sum, za
     uint64_t* bars = reinterpret_cast<uint64_t*>(smb + pfw::kOffBar);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smb + pfw::kOffBar + 32);
     const int64_t b = blockIdx.x;
@@ -793,15 +740,15 @@ __global__ void __launch_bounds__(256, 1)
     auto fetch = [&](int t) {   // fp32 heads of tile t -> staging (rows past the end keep stale values: their logits are masked)
         const int64_t rt = r0 + (int64_t)t * pfw::kT;
         const int rows = (int)(r1 - rt < pfw::kT ? r1 - rt : pfw::kT);
-        for (int i = tid; i < rows * 32; i += 256) {
+        for (int i = tid; i < rows * 32; i += pfw::kThreads) {
             const int r = i >> 5, c4 = i & 31;
             cp_async16(s_stage + r * pfw::kStride + 4 * c4, heads + (b * R + rt + r) * kE + 4 * c4);
         }
         cp_async_commit();
     };
     auto convert = [&]() {      // staging -> K-major fp16 hi | lo, item = (row, 8-channel chunk)
-        for (int i = tid; i < pfw::kT * 16; i += 256) {
-            const int r = i >> 4, c = i & 15;
+        for (int i = tid; i < pfw::kT * 16; i += pfw::kThreads) {
+            const int r = 8 * (i >> 7) + (i & 7), c = (i >> 3) & 15;   // conflict-free operand stores (item_rc)
             const float4 a = *reinterpret_cast<const float4*>(s_stage + r * pfw::kStride + 8 * c);
             const float4 bb = *reinterpret_cast<const float4*>(s_stage + r * pfw::kStride + 8 * c + 4);
             uint32_t hi[4], lo[4];
@@ -854,8 +801,8 @@ __global__ void __launch_bounds__(256, 1)
 
     fetch(0);
     fetch_rows(0);
-    for (int i = tid; i < 128 * 16; i += 256) {   // resident B operand: lkf (K = channels), nodes >= n are zero
-        const int m = i >> 4, c = i & 15;
+    for (int i = tid; i < 128 * 16; i += pfw::kThreads) {   // resident B operand: lkf (K = channels), nodes >= n are zero
+        const int m = 8 * (i >> 7) + (i & 7), c = (i >> 3) & 15;
         float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a;
         if (m < n) {
             a = ld4(lkf + ((size_t)b * n + m) * kE + 8 * c);
@@ -881,7 +828,7 @@ __global__ void __launch_bounds__(256, 1)
     issue(tmem, 0);
     if (ntiles > 1) fetch(1);
 
-    const int q4 = warp & 3, chalf = warp >> 2;          // TMEM lane quadrant (row = 32 q4 + lane), node half
+    const int q4 = warp & 3, cq = warp >> 2;             // TMEM lane quadrant (row = 32 q4 + lane), node quarter
     const uint32_t lane_base = tmem + ((uint32_t)(32 * q4) << 16);
     const float sc = (clip > 0.f ? clip : 1.0f) / temperature;
     uint32_t ph[2] = {0u, 0u};
@@ -910,37 +857,42 @@ __global__ void __launch_bounds__(256, 1)
         }
         const int r = 32 * q4 + lane;
         const int a = s_a[r];
-        const uint32_t m0 = s_mw[r * 4 + 2 * chalf], m1 = s_mw[r * 4 + 2 * chalf + 1];
-        float z[64];
+        const uint32_t mw = s_mw[r * 4 + cq];
+        float z[32];
         float zmax = -INFINITY, za = -INFINITY;
 #pragma unroll
-        for (int c = 0; c < 64; c += 16) {
+        for (int c = 0; c < 32; c += 16) {
             uint32_t uv[16];
-            tmem_ld16(lane_base + 128u * (uint32_t)(t & 1) + (uint32_t)(64 * chalf + c), uv);
+            tmem_ld16(lane_base + 128u * (uint32_t)(t & 1) + (uint32_t)(32 * cq + c), uv);
             tc_wait_ld();
-            const uint32_t bits = ((c < 32 ? m0 : m1) >> (c & 31)) & 0xffffu;
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
                 const float u = __uint_as_float(uv[i]) * kInvSqrtE;
                 const float zv = (clip > 0.f ? tanh_fast_ev(u) : u) * sc;     // decoding.py:171-172, :180
-                z[c + i] = (bits >> i) & 1u ? zv : -INFINITY;                  // :177
+                z[c + i] = (mw >> (c + i)) & 1u ? zv : -INFINITY;              // :177
                 zmax = fmaxf(zmax, z[c + i]);
-                if (64 * chalf + c + i == a) za = z[c + i];
+                if (32 * cq + c + i == a) za = z[c + i];
             }
         }
-        s_x[(chalf * 3 + 0) * pfw::kT + r] = zmax;
-        s_x[(chalf * 3 + 2) * pfw::kT + r] = za;
+        s_x[(cq * 3 + 0) * pfw::kT + r] = zmax;
+        s_x[(cq * 3 + 2) * pfw::kT + r] = za;
         __syncthreads();
-        const float mx = fmaxf(zmax, s_x[((chalf ^ 1) * 3 + 0) * pfw::kT + r]);
+        float mx = zmax;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) mx = fmaxf(mx, s_x[(k * 3 + 0) * pfw::kT + r]);
         const float mref = (mx == -INFINITY) ? 0.f : mx;
         float zsum = 0.f;
 #pragma unroll
-        for (int i = 0; i < 64; ++i) zsum += __expf(z[i] - mref);
-        s_x[(chalf * 3 + 1) * pfw::kT + r] = zsum;
+        for (int i = 0; i < 32; ++i) zsum += __expf(z[i] - mref);
+        s_x[(cq * 3 + 1) * pfw::kT + r] = zsum;
         __syncthreads();
-        if (chalf == 0 && r < rows) {
-            const float tot = zsum + s_x[(1 * 3 + 1) * pfw::kT + r];
-            const float zt = fmaxf(za, s_x[(1 * 3 + 2) * pfw::kT + r]);
+        if (cq == 0 && r < rows) {
+            float tot = 0.f, zt = -INFINITY;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                tot += s_x[(k * 3 + 1) * pfw::kT + r];
+                zt = fmaxf(zt, s_x[(k * 3 + 2) * pfw::kT + r]);
+            }
             const bool any = tot > 0.f;
             const float lz = any ? mref + __logf(tot) : 0.f;
             logp[b * R + rt + r] = any ? zt - lz : 0.f;      // :190 log_softmax, :462 gather
@@ -1304,22 +1256,13 @@ extern "C" int rl4co_eval_ll_fwd(const float* q, const float* gk, const float* g
     if ((rc = eval_check("eval_ll_fwd", B, R, n_nodes, temperature))) return rc;
     if (B == 0 || R == 0) return RL4CO_OK;
     dim3 grid((unsigned)B, (unsigned)ev::grid_split(B, 1));
-    const char* mode = getenv("R4_EVAL_PTR_FWD");
-    if (!(mode && mode[0] == 't')) {   // experiment switch: R4_EVAL_PTR_FWD=tc runs the pointer on eval_ptr_fwd_tc_kernel
-        const size_t smem = 3ull * n_nodes * kE * sizeof(float);
-        if ((rc = ev::set_smem(ev::eval_ll_fwd_kernel<true>, smem, "eval_ll_fwd"))) return rc;
-        ev::eval_ll_fwd_kernel<true><<<grid, ev::kThreads, smem, (cudaStream_t)stream>>>(
-            q, gk, gv, lkf, mask, taken, logp, heads, lse_h, lse_z, maskw, R, n_nodes, tanh_clipping, temperature);
-        R4_CHECK_LAUNCH("eval_ll_fwd");
-        return RL4CO_OK;
-    }
     const size_t smem = 2ull * n_nodes * kE * sizeof(float);
-    if ((rc = ev::set_smem(ev::eval_ll_fwd_kernel<false>, smem, "eval_ll_fwd (glimpse)"))) return rc;
-    ev::eval_ll_fwd_kernel<false><<<grid, ev::kThreads, smem, (cudaStream_t)stream>>>(
-        q, gk, gv, lkf, mask, taken, logp, heads, lse_h, lse_z, maskw, R, n_nodes, tanh_clipping, temperature);
+    if ((rc = ev::set_smem(ev::eval_glimpse_fwd_kernel, smem, "eval_ll_fwd (glimpse)"))) return rc;
+    ev::eval_glimpse_fwd_kernel<<<grid, ev::kThreads, smem, (cudaStream_t)stream>>>(q, gk, gv, mask, heads, lse_h, maskw, R,
+                                                                                   n_nodes);
     R4_CHECK_LAUNCH("eval_ll_fwd (glimpse)");
     if ((rc = ev::set_smem(ev::eval_ptr_fwd_tc_kernel, ev::pfw::kSmem, "eval_ll_fwd (pointer)"))) return rc;
-    ev::eval_ptr_fwd_tc_kernel<<<grid, 256, ev::pfw::kSmem, (cudaStream_t)stream>>>(lkf, maskw, taken, heads, logp, lse_z, R,
+    ev::eval_ptr_fwd_tc_kernel<<<grid, ev::pfw::kThreads, ev::pfw::kSmem, (cudaStream_t)stream>>>(lkf, maskw, taken, heads, logp, lse_z, R,
                                                                                    n_nodes, tanh_clipping, temperature);
     R4_CHECK_LAUNCH("eval_ll_fwd (pointer)");
     return RL4CO_OK;
