@@ -4,11 +4,12 @@
 //
 // With the actions known, the rows (instance b, start s, step t) are independent: row r of instance b has its query q[b,r,:]
 // (context.py:118-157 gathers, built by the caller with autograd), its feasibility mask and its taken action.  All rows of an
-// instance share the three [n,128] tables, which a CTA keeps in shared memory:
-//   glimpse  (attention.py:308-322): 8-head masked softmax attention on the CUDA cores, a warp per four rows, lane = (row, head),
-//            only FEASIBLE nodes visited (masked nodes have probability exactly 0 and contribute no gradient);
-//   pointer  (attention.py:296-301,328; decoding.py:140-190): logits = heads . lkf[n] / sqrt(E) as tcgen05 MMAs per 128-row
-//            tile, then tanh clip, mask, temperature, log_softmax, gather at the taken action.
+// instance share the three [n,128] tables, which a CTA keeps in shared memory as fp16 hi / lo MMA operand tiles.  Forward, both
+// parts on tcgen05 over tiles of 128 rows (TMEM lane = row):
+//   glimpse  (attention.py:308-322): per head S = (0.25 Q_h) K_h^T, masked softmax numerator P in place as the TS-form A operand,
+//            O_h = P V_h (masked nodes have probability exactly 0 and contribute no gradient);
+//   pointer  (attention.py:296-301,328; decoding.py:140-190): logits = heads . lkf[n] / sqrt(E), then tanh clip, mask,
+//            temperature, log_softmax, gather at the taken action.
 // The backward recomputes the probabilities from the saved log-sum-exps (flash-attention style) in two passes:
 //   row pass : everything that reduces over NODES - du = d loss / d raw logit and dheads = dU lkf on tcgen05 (the logits are
 //             recomputed as an MMA per 128-row tile, du converted in place into the A operand of the second product); dq on
@@ -113,104 +114,6 @@ __device__ __forceinline__ void next_nodes(uint32_t& wb, int (&j)[G], bool (&ok)
 #pragma unroll
     for (int u = 1; u < G; ++u) j[u] = ok[u] ? j[u] : j[0];
 }
-__device__ __forceinline__ bool bit_of(const uint32_t (&w)[kNB], int node) {
-    return (sel4u(w, node >> 5) >> (node & 31)) & 1u;
-}
-
-// masked 8-head glimpse of the warp's four rows (attention.py:308-322), online softmax in chunks of four nodes
-__device__ __forceinline__ void glimpse_rows(const float* s_gk, const float* s_gv, const float (&qs)[16],
-                                             const uint32_t (&w)[kNB], const uint32_t (&wu)[kNB], int h, float (&o)[16],
-                                             float& lse) {
-    float m = -INFINITY, l = 0.f;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) o[i] = 0.f;
-#pragma unroll 1
-    for (int blk = 0; blk < kNB; ++blk) {
-        uint32_t wb = sel4u(wu, blk);
-        const uint32_t own = sel4u(w, blk);
-        while (wb) {
-            int j[4];
-            bool ok[4];
-            next_nodes<4>(wb, j, ok);
-            float s[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const float v = dot16(qs, s_gk + (blk * 32 + j[u]) * kE + 4 * h);
-                s[u] = (ok[u] && ((own >> j[u]) & 1u)) ? v : -INFINITY;
-            }
-            const float mn = fmaxf(fmaxf(fmaxf(s[0], s[1]), fmaxf(s[2], s[3])), m);
-            const float mref = (mn == -INFINITY) ? 0.f : mn;      // nothing feasible for this row so far
-            const float c = fexp(m - mref);
-            float p[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) p[u] = fexp(s[u] - mref);
-            l = fmaf(l, c, (p[0] + p[1]) + (p[2] + p[3]));
-#pragma unroll
-            for (int i = 0; i < 16; ++i) o[i] *= c;
-#pragma unroll
-            for (int u = 0; u < 4; ++u) axpy16(o, p[u], s_gv + (blk * 32 + j[u]) * kE + 4 * h);
-            m = mn;
-        }
-    }
-    const bool any = l > 0.f;
-    const float inv = any ? 1.0f / l : 0.f;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) o[i] *= inv;
-    lse = any ? m + logf(l) : 0.f;
-}
-
-// ---- forward, glimpse: heads [B,R,E], lse_h [B,R,H] and the mask as bit words maskw [B,R,4] (saved for the backward; the
-// pointer - logp [B,R], lse_z [B,R] - runs on eval_ptr_fwd_tc_kernel from the heads written here) ------------------------------
-__global__ void __launch_bounds__(kThreads, 1)
-    eval_glimpse_fwd_kernel(const float* __restrict__ q, const float* __restrict__ gk, const float* __restrict__ gv,
-                            const uint8_t* __restrict__ mask, float* __restrict__ heads, float* __restrict__ lse_h,
-                            uint32_t* __restrict__ maskw, int64_t R, int n) {
-    extern __shared__ __align__(16) float sm[];
-    float* s_gk = sm;
-    float* s_gv = sm + n * kE;
-    const int64_t b = blockIdx.x;
-    copy_table_swz(s_gk, gk + b * n * kE, n);
-    copy_table_swz(s_gv, gv + b * n * kE, n);
-    __syncthreads();
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-    const int ri = lane >> 3, h = lane & 7;
-    int64_t r0, r1;
-    row_range(R, r0, r1);
-    for (int64_t rb = r0 + 4 * warp; rb < r1; rb += 4 * nw) {
-        const bool valid = rb + ri < r1;
-        const int64_t row = b * R + (valid ? rb + ri : r1 - 1);
-        // the four rows' masks as bit words: 32 lanes read 32 bytes of a row, one ballot per word
-        uint32_t w[kNB], wu[kNB];
-#pragma unroll
-        for (int blk = 0; blk < kNB; ++blk) {
-            w[blk] = 0u;
-            wu[blk] = 0u;
-        }
-#pragma unroll
-        for (int rr = 0; rr < 4; ++rr) {
-            const int64_t rrow = b * R + (rb + rr < r1 ? rb + rr : r1 - 1);
-#pragma unroll
-            for (int blk = 0; blk < kNB; ++blk) {
-                const int i = 32 * blk + lane;
-                const uint32_t bal = __ballot_sync(kFull, i < n && mask[rrow * n + i] != 0);
-                w[blk] = (ri == rr) ? bal : w[blk];
-                wu[blk] |= bal;
-            }
-        }
-        if (valid && h < kNB) maskw[row * kNB + h] = sel4u(w, h);
-        float qs[16];
-        ld16(q + row * kE + 16 * h, qs);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) qs[i] *= 0.25f;
-        float o[16], lh;
-        glimpse_rows(s_gk, s_gv, qs, w, wu, h, o, lh);
-        if (valid) {
-            st16(heads + row * kE + 16 * h, o);
-            lse_h[row * kH + h] = lh;
-        }
-    }
-}
-
 // du_t [B,R,128]: d loss / d (raw logit of node n), column = node; columns >= n are zero
 
 // ---- backward, row pass of the glimpse: dq = 0.25 sum_n dS[n] k[n], dS = P (dP - D), P from the saved log-sum-exp; dd = D ------
@@ -1202,6 +1105,293 @@ __global__ void __launch_bounds__(256, (KT == 64 && NH == 4) ? 2 : 1)
     if (warp == 0) tmem_dealloc(tmem, L::kTmemCols);
 }
 
+// ---- mask bytes [rows, n] -> bit words [rows, 4] (the form every evaluate kernel reads) ----------------------------------------
+__global__ void __launch_bounds__(256)
+    eval_pack_mask_kernel(const uint8_t* __restrict__ mask, uint32_t* __restrict__ maskw, int64_t rows, int n) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; row < rows; row += nw) {
+        uint32_t w[kNB];
+#pragma unroll
+        for (int blk = 0; blk < kNB; ++blk) {
+            const int i = 32 * blk + lane;
+            w[blk] = __ballot_sync(kFull, i < n && mask[row * n + i] != 0);
+        }
+        if (lane < kNB) maskw[row * kNB + lane] = sel4u(w, lane);
+    }
+}
+
+// ---- forward, glimpse on the tensor cores: heads = softmax(0.25 Q_h K_h^T + mask) V_h, lse_h ------------------------------------
+// CTA = (instance, row range, four heads); per tile of 128 rows and head h:
+//   S = (0.25 Q_h) K_h^T  [rows x nodes]  3 split-fp16 MMAs, A = the tile's Q_h slice, B = the resident K_h tile -> TMEM [0, npad)
+//   thread (row, 64 nodes): row maximum over the feasible nodes (the two threads of a row exchange through shared memory),
+//     P = exp(S - max) written back IN PLACE as the fp16 hi / lo TS-form A operand, row sum l
+//   O_h = P V_h           [rows x 16]     3 x npad / 16 TS-form MMAs (N = 16), B = the resident V_h^T tile -> TMEM [128 + 16 h, +16)
+//   heads[row, 16 h ..] = O_h / l, lse_h = max + log l: stored while the next head's S product runs.
+// 256 TMEM columns and ~100 KB of shared memory: two CTAs per SM whose serial S -> softmax -> O chains overlap.
+namespace gfw {
+constexpr int kNH = 4;
+constexpr uint32_t kHeadTile = 4096;                  // [128 x 16] or [16 x 128] fp16 K-major (hi or lo)
+constexpr uint32_t kOffK = 0;                         // K_h   [node][dim] hi | lo per head (B of S: N = nodes, K = 16)
+constexpr uint32_t kOffVT = kNH * 2 * kHeadTile;      // V_h^T [dim][node] hi | lo per head (B of O: N = 16, K = nodes)
+constexpr uint32_t kOffQ = 2 * kOffVT;                // Q_h   [row][dim]  hi | lo per head (A of S), rewritten per tile
+constexpr uint32_t kOffMaskW = 3 * kOffVT;            // [128 rows][4] u32
+constexpr uint32_t kOffX = kOffMaskW + 128 * 16;      // exchange between the two threads of a row: max [2][128], sum [2][128]
+constexpr uint32_t kOffBar = kOffX + 4 * 128 * 4;
+constexpr size_t kSmem = kOffBar + 64;
+}  // namespace gfw
+
+__global__ void __launch_bounds__(256, 2)
+    eval_glimpse_fwd_tc_kernel(const float* __restrict__ q, const float* __restrict__ gk, const float* __restrict__ gv,
+                               const uint32_t* __restrict__ maskw, float* __restrict__ heads, float* __restrict__ lse_h,
+                               int64_t R, int n) {
+    using namespace tc;
+    extern __shared__ __align__(128) unsigned char smb[];
+    uint32_t* s_mw = reinterpret_cast<uint32_t*>(smb + gfw::kOffMaskW);
+    float* s_max = reinterpret_cast<float*>(smb + gfw::kOffX);
+    float* s_sum = s_max + 256;
+    uint64_t* bar1 = reinterpret_cast<uint64_t*>(smb + gfw::kOffBar);
+    uint64_t* bar2 = bar1 + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smb + gfw::kOffBar + 32);
+    const int64_t b = blockIdx.x;
+    const int h0 = (int)blockIdx.z * gfw::kNH;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    int64_t r0, r1;
+    row_range(R, r0, r1);
+    if (r0 >= r1) return;
+    const int ntiles = (int)((r1 - r0 + 127) / 128);
+    const int npad = (n + 15) & ~15;
+    if (tid == 0) {
+        mbar_init(bar1, 1);
+        mbar_init(bar2, 1);
+        fence_mbar_init();
+    }
+    __syncwarp();
+    if (warp == 0) tmem_alloc(tmem_slot, 256);
+    // resident B operands (nodes >= n are zero).  K_h: item = (head, node m, 8-dim chunk c), lanes over m & 7 first (item_rc)
+    for (int i = tid; i < gfw::kNH * 256; i += 256) {
+        const int hl = i >> 8, m = 8 * ((i >> 4) & 15) + (i & 7), c = (i >> 3) & 1;
+        const float* src = gk + ((size_t)b * n + m) * kE + 16 * (h0 + hl) + 8 * c;
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a;
+        if (m < n) {
+            a = ld4(src);
+            bb = ld4(src + 4);
+        }
+        uint32_t hi[4], lo[4];
+        split2(a.x, a.y, hi[0], lo[0]);
+        split2(a.z, a.w, hi[1], lo[1]);
+        split2(bb.x, bb.y, hi[2], lo[2]);
+        split2(bb.z, bb.w, hi[3], lo[3]);
+        unsigned char* dst = smb + gfw::kOffK + (uint32_t)hl * 2u * gfw::kHeadTile + (uint32_t)(m >> 3) * 256u + (uint32_t)c * 128u +
+                             (uint32_t)(m & 7) * 16u;
+        *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(dst + gfw::kHeadTile) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+    // V_h^T: item = (head, 8-node group g, dim dm); the conversion is the transposition (8 nodes of one dim = one K chunk)
+    for (int i = tid; i < gfw::kNH * 256; i += 256) {
+        const int hl = i >> 8, g = (i >> 4) & 15, dm = i & 15;
+        float v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = (8 * g + k < n) ? gv[((size_t)b * n + 8 * g + k) * kE + 16 * (h0 + hl) + dm] : 0.f;
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int w = 0; w < 4; ++w) split2(v[2 * w], v[2 * w + 1], hi[w], lo[w]);
+        unsigned char* dst = smb + gfw::kOffVT + (uint32_t)hl * 2u * gfw::kHeadTile + (uint32_t)(dm >> 3) * 2048u + (uint32_t)g * 128u +
+                             (uint32_t)(dm & 7) * 16u;
+        *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(dst + gfw::kHeadTile) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+    // the tile's Q slices (4 heads x 128 rows x 2 chunks = 4 items per thread, item k = head k) and mask words travel through
+    // registers one tile ahead
+    float4 pre[8];
+    uint32_t pre_mw[4] = {0u, 0u, 0u, 0u};
+    auto prefetch = [&](int t) {
+        const int64_t rt = r0 + (int64_t)t * 128;
+        const int rows = t < ntiles ? (int)(r1 - rt < 128 ? r1 - rt : 128) : 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int r = 8 * ((tid >> 4) & 15) + (tid & 7), c = (tid >> 3) & 1;
+            pre[2 * k] = pre[2 * k + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (r < rows) {
+                const float* src = q + (b * R + rt + r) * kE + 16 * (h0 + k) + 8 * c;
+                pre[2 * k] = ld4(src);
+                pre[2 * k + 1] = ld4(src + 4);
+            }
+        }
+        if (tid < 128) {
+            const bool ok = tid < rows;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) pre_mw[k] = ok ? maskw[(b * R + rt + tid) * kNB + k] : 0u;
+        }
+    };
+    prefetch(0);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t sb = smem_u32(smb);
+    const int q4 = warp & 3, chalf = warp >> 2;          // TMEM lane quadrant (row = 32 q4 + lane), node half
+    const int r = 32 * q4 + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * q4) << 16);
+    uint32_t p1 = 0, p2 = 0;
+    bool pv_pending = false;
+    // epilogue of the previous (tile, head): valid in the threads of node half 0
+    float epi_inv = 0.f, epi_lse = 0.f;
+    int64_t epi_rt = 0;
+    int epi_rows = 0, epi_hl = 0;
+    auto epilogue = [&]() {
+        if (chalf == 0) {
+            uint32_t v[16];
+            tmem_ld16(lane_base + 128u + 16u * (uint32_t)epi_hl, v);
+            tc_wait_ld();
+            if (r < epi_rows) {
+                float* dst = heads + (b * R + epi_rt + r) * kE + 16 * (h0 + epi_hl);
+#pragma unroll
+                for (int i = 0; i < 16; i += 4)
+                    *reinterpret_cast<float4*>(dst + i) =
+                        make_float4(__uint_as_float(v[i]) * epi_inv, __uint_as_float(v[i + 1]) * epi_inv,
+                                    __uint_as_float(v[i + 2]) * epi_inv, __uint_as_float(v[i + 3]) * epi_inv);
+                lse_h[(b * R + epi_rt + r) * kH + h0 + epi_hl] = epi_lse;
+            }
+        }
+    };
+    for (int t = 0; t < ntiles; ++t) {
+        const int64_t rt = r0 + (int64_t)t * 128;
+        const int rows = (int)(r1 - rt < 128 ? r1 - rt : 128);
+        // (every S product of the previous tile has completed: its heads' bar1 were waited for)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int rr = 8 * ((tid >> 4) & 15) + (tid & 7), c = (tid >> 3) & 1;
+            const float4 a = pre[2 * k], bb = pre[2 * k + 1];
+            uint32_t hi[4], lo[4];
+            split2(a.x * 0.25f, a.y * 0.25f, hi[0], lo[0]);
+            split2(a.z * 0.25f, a.w * 0.25f, hi[1], lo[1]);
+            split2(bb.x * 0.25f, bb.y * 0.25f, hi[2], lo[2]);
+            split2(bb.z * 0.25f, bb.w * 0.25f, hi[3], lo[3]);
+            unsigned char* dst = smb + gfw::kOffQ + (uint32_t)k * 2u * gfw::kHeadTile + (uint32_t)(rr >> 3) * 256u + (uint32_t)c * 128u +
+                                 (uint32_t)(rr & 7) * 16u;
+            *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(dst + gfw::kHeadTile) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        }
+        if (tid < 128) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) s_mw[tid * 4 + k] = pre_mw[k];
+        }
+        fence_proxy_async();
+        __syncthreads();
+        prefetch(t + 1);
+        const uint32_t m0 = s_mw[r * 4 + 2 * chalf], m1 = s_mw[r * 4 + 2 * chalf + 1];
+        for (int hl = 0; hl < gfw::kNH; ++hl) {
+            if (pv_pending) {                            // O of the previous head is complete and P has been read
+                mbar_wait(bar2, p2);
+                p2 ^= 1u;
+                tc_fence_after();
+            }
+            if (warp == 0) {
+                if (elect_one()) {
+                    tc_fence_after();
+                    const uint32_t id = idesc_f16(128, npad);
+                    const uint32_t qo = sb + gfw::kOffQ + (uint32_t)hl * 2u * gfw::kHeadTile;
+                    const uint32_t ko = sb + gfw::kOffK + (uint32_t)hl * 2u * gfw::kHeadTile;
+                    const uint64_t q_hi = smem_desc(qo, 128, 256), q_lo = smem_desc(qo + gfw::kHeadTile, 128, 256);
+                    const uint64_t k_hi = smem_desc(ko, 128, 256), k_lo = smem_desc(ko + gfw::kHeadTile, 128, 256);
+                    mma_ss(tmem, q_hi, k_hi, id, 0u);
+                    mma_ss(tmem, q_hi, k_lo, id, 1u);
+                    mma_ss(tmem, q_lo, k_hi, id, 1u);
+                    tc_commit(bar1);
+                }
+                __syncwarp();
+            }
+            if (pv_pending) {
+                epilogue();
+                pv_pending = false;
+            }
+            mbar_wait(bar1, p1);
+            p1 ^= 1u;
+            tc_fence_after();
+            // pass 1: maximum over this thread's feasible nodes
+            float mx = -INFINITY;
+#pragma unroll 1
+            for (int c = 0; c < 64; c += 16) {
+                const int col = 64 * chalf + c;
+                if (col >= npad) break;
+                uint32_t sv[16];
+                tmem_ld16(lane_base + (uint32_t)col, sv);
+                tc_wait_ld();
+                const uint32_t bits = ((c < 32 ? m0 : m1) >> (c & 31)) & 0xffffu;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) mx = fmaxf(mx, (bits >> i) & 1u ? __uint_as_float(sv[i]) : -INFINITY);
+            }
+            s_max[chalf * 128 + r] = mx;
+            __syncthreads();
+            mx = fmaxf(mx, s_max[(chalf ^ 1) * 128 + r]);
+            const float mref = (mx == -INFINITY) ? 0.f : mx;
+            // pass 2: P = exp(S - max) in place (fp16 hi | lo per 16-column chunk), row sum
+            float lsum = 0.f;
+#pragma unroll 1
+            for (int c = 0; c < 64; c += 16) {
+                const int col = 64 * chalf + c;
+                if (col >= npad) break;
+                uint32_t sv[16];
+                tmem_ld16(lane_base + (uint32_t)col, sv);
+                tc_wait_ld();
+                const uint32_t bits = ((c < 32 ? m0 : m1) >> (c & 31)) & 0xffffu;
+                uint32_t phi[8], plo[8];
+#pragma unroll
+                for (int i = 0; i < 16; i += 2) {
+                    const float pa = (bits >> i) & 1u ? fexp(__uint_as_float(sv[i]) - mref) : 0.f;
+                    const float pb = (bits >> (i + 1)) & 1u ? fexp(__uint_as_float(sv[i + 1]) - mref) : 0.f;
+                    lsum += pa + pb;
+                    split2(pa, pb, phi[i >> 1], plo[i >> 1]);
+                }
+                tmem_st8(lane_base + (uint32_t)col, phi);
+                tmem_st8(lane_base + (uint32_t)col + 8u, plo);
+            }
+            s_sum[chalf * 128 + r] = lsum;
+            tc_wait_st();
+            tc_fence_before();
+            __syncthreads();
+            if (chalf == 0) {
+                const float l = lsum + s_sum[128 + r];
+                const bool any = l > 0.f;
+                epi_inv = any ? 1.0f / l : 0.f;
+                epi_lse = any ? mref + __logf(l) : 0.f;
+            }
+            epi_rt = rt;
+            epi_rows = rows;
+            epi_hl = hl;
+            if (warp == 0) {
+                if (elect_one()) {
+                    tc_fence_after();
+                    const uint32_t id = idesc_f16(128, 16);
+                    const uint32_t vo = sb + gfw::kOffVT + (uint32_t)hl * 2u * gfw::kHeadTile;
+                    uint64_t v_hi = smem_desc(vo, 128, 2048), v_lo = smem_desc(vo + gfw::kHeadTile, 128, 2048);
+                    const uint32_t d = tmem + 128u + 16u * (uint32_t)hl;
+                    for (int ks = 0; ks < npad / 16; ++ks) {
+                        mma_ts(d, tmem + 16u * ks, v_hi, id, ks == 0 ? 0u : 1u);   // O_h = P V_h
+                        mma_ts(d, tmem + 16u * ks, v_lo, id, 1u);
+                        mma_ts(d, tmem + 16u * ks + 8u, v_hi, id, 1u);
+                        v_hi += 256u >> 4;
+                        v_lo += 256u >> 4;
+                    }
+                    tc_commit(bar2);
+                }
+                __syncwarp();
+            }
+            pv_pending = true;
+        }
+    }
+    if (pv_pending) {
+        mbar_wait(bar2, p2);
+        tc_fence_after();
+        epilogue();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, 256);
+}
+
 // Row split per instance: `units` equal CTAs per split step over sms * ctas_per_sm slots, the split in [1, 32] with the
 // fewest waves per unit of work (64 instances x 2 = 128 CTAs would leave 20 SMs idle; x 9 = 576 CTAs fill 3.9 of 4 waves).
 static int grid_split(int64_t units, int ctas_per_sm) {
@@ -1255,12 +1445,20 @@ extern "C" int rl4co_eval_ll_fwd(const float* q, const float* gk, const float* g
     int rc;
     if ((rc = eval_check("eval_ll_fwd", B, R, n_nodes, temperature))) return rc;
     if (B == 0 || R == 0) return RL4CO_OK;
-    dim3 grid((unsigned)B, (unsigned)ev::grid_split(B, 1));
-    const size_t smem = 2ull * n_nodes * kE * sizeof(float);
-    if ((rc = ev::set_smem(ev::eval_glimpse_fwd_kernel, smem, "eval_ll_fwd (glimpse)"))) return rc;
-    ev::eval_glimpse_fwd_kernel<<<grid, ev::kThreads, smem, (cudaStream_t)stream>>>(q, gk, gv, mask, heads, lse_h, maskw, R,
-                                                                                   n_nodes);
+    {   // mask bytes -> bit words
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        const int64_t want = (B * R + 7) / 8;
+        ev::eval_pack_mask_kernel<<<(unsigned)(want < (int64_t)sms * 8 ? want : (int64_t)sms * 8), 256, 0, (cudaStream_t)stream>>>(
+            mask, maskw, B * R, n_nodes);
+        R4_CHECK_LAUNCH("eval_ll_fwd (mask words)");
+    }
+    if ((rc = ev::set_smem(ev::eval_glimpse_fwd_tc_kernel, ev::gfw::kSmem, "eval_ll_fwd (glimpse)"))) return rc;
+    dim3 g2((unsigned)B, (unsigned)ev::grid_split(2 * B, 2), 2u);
+    ev::eval_glimpse_fwd_tc_kernel<<<g2, 256, ev::gfw::kSmem, (cudaStream_t)stream>>>(q, gk, gv, maskw, heads, lse_h, R, n_nodes);
     R4_CHECK_LAUNCH("eval_ll_fwd (glimpse)");
+    dim3 grid((unsigned)B, (unsigned)ev::grid_split(B, 1));
     if ((rc = ev::set_smem(ev::eval_ptr_fwd_tc_kernel, ev::pfw::kSmem, "eval_ll_fwd (pointer)"))) return rc;
     ev::eval_ptr_fwd_tc_kernel<<<grid, ev::pfw::kThreads, ev::pfw::kSmem, (cudaStream_t)stream>>>(lkf, maskw, taken, heads, logp, lse_z, R,
                                                                                    n_nodes, tanh_clipping, temperature);
