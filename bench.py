@@ -274,6 +274,16 @@ def train_leg(dev, rank, world, steps=8, warmup=3):
     # the same step with the PyTorch encoder's forward / backward replayed from two CUDA graphs (train.graphed_encoder)
     encode = train.graphed_encoder(pol, env.reset(gen(B, instance_offset=0)))
     step_ms = timed(encode, warmup + steps)
+    # the reference's trainer default is 16-mixed autocast with torch.set_float32_matmul_precision("medium")
+    # (rl4co/utils/trainer.py:56-60); the headline above keeps fp32 matmuls ("highest").  Sub-record: the same step with
+    # PyTorch's fp32 matmuls (encoder, table products) on TF32 tensor cores ("high") - our kernels are unaffected.
+    stats_fp32 = stats
+    torch.set_float32_matmul_precision("high")
+    try:
+        encode_tf32 = train.graphed_encoder(pol, env.reset(gen(B, instance_offset=0)))
+        tf32_ms = timed(encode_tf32, 2 * (warmup + steps))
+    finally:
+        torch.set_float32_matmul_precision("highest")
     ar_ms = None
     if world > 1:   # the all-reduce alone, same flat buffer size (gradients + 3 logged scalars)
         buf = torch.zeros(n_par + 3, dtype=torch.float32, device=dev)
@@ -287,15 +297,17 @@ def train_leg(dev, rank, world, steps=8, warmup=3):
         a1.record()
         torch.cuda.synchronize()
         ar_ms = a0.elapsed_time(a1) / 10
-    step_ms, eager_ms = sharding.max_over_ranks([step_ms, eager_ms], device=dev)
+    step_ms, eager_ms, tf32_ms = sharding.max_over_ranks([step_ms, eager_ms, tf32_ms], device=dev)
     return {"workload": "CVRP100 POMO REINFORCE step (multistart sampling S=100 on the rollout kernel, teacher-forced "
                         "log-likelihood forward + backward on rl4co_eval_query_* / rl4co_eval_ll_*, shared baseline, "
                         "encoder + table products in PyTorch autograd with the encoder's forward / backward replayed from "
                         "CUDA graphs, flat all-reduce, clip, Adam), 64 instances per GPU",
-            "ms_per_step": step_ms, "ms_per_step_encoder_not_graphed": eager_ms, "instances_per_s": world * B / (step_ms * 1e-3), "n_gpus": world,
+            "ms_per_step": step_ms, "ms_per_step_encoder_not_graphed": eager_ms,
+            "ms_per_step_torch_matmuls_tf32": tf32_ms, "instances_per_s": world * B / (step_ms * 1e-3), "n_gpus": world,
             "allreduce_ms": ar_ms, "allreduce_bytes": 4 * (n_par + 3), "collectives_per_step": 1 if world > 1 else 0,
-            "backend": "nccl" if world > 1 else None, "loss": stats["loss"], "reward": stats["reward"],
-            "ll_gap_rollout_vs_reevaluation": stats["ll_gap"]}
+            "backend": "nccl" if world > 1 else None, "loss": stats_fp32["loss"], "reward": stats_fp32["reward"],
+            "ll_gap_rollout_vs_reevaluation": stats_fp32["ll_gap"],
+            "ll_gap_rollout_vs_reevaluation_tf32": stats["ll_gap"]}
 
 
 def run_b200(args):
