@@ -356,6 +356,7 @@ constexpr uint32_t kOffH = 4 * kHalf;           // heads tile [row][ch] hi | lo 
 constexpr uint32_t kOffRow = 6 * kHalf;         // per row of the tile: g, lse_z (f32), taken (i32), 4 mask words
 constexpr uint32_t kOffBar = kOffRow + kT * 28;
 constexpr size_t kSmem = kOffBar + 64;
+constexpr int kThreads = 512;                   // thread = (row, 32 nodes): 16 warps for the elementwise pass
 }  // namespace pbw
 
 __device__ __forceinline__ float tanh_fast_ev(float v) {   // 1 - 2 / (1 + e^(2v)) on MUFU ex2 / rcp: abs. error ~2e-7
@@ -363,7 +364,7 @@ __device__ __forceinline__ float tanh_fast_ev(float v) {   // 1 - 2 / (1 + e^(2v
     return 1.0f - __fdividef(2.0f, e2 + 1.0f);
 }
 
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(pbw::kThreads, 1)
     eval_ptr_bwd_tc_kernel(const float* __restrict__ lkf, const uint32_t* __restrict__ maskw, const int64_t* __restrict__ taken,
                            const float* __restrict__ heads, const float* __restrict__ lse_z, const float* __restrict__ dlogp,
                            float* __restrict__ dheads, float* __restrict__ du_t, int64_t R, int n, float clip, float temperature) {
@@ -390,7 +391,7 @@ __global__ void __launch_bounds__(256, 1)
     __syncwarp();
     if (warp == 0) tmem_alloc(tmem_slot, 256);
     // resident B operands: lkf (K = channels) and its transpose (K = nodes); nodes >= n are zero
-    for (int i = tid; i < 128 * 16; i += 256) {
+    for (int i = tid; i < 128 * 16; i += pbw::kThreads) {
         const int m = 8 * (i >> 7) + (i & 7), c = (i >> 3) & 15;   // lkf: (node m, 8-channel chunk c), see item_rc
         float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a;
         if (m < n) {
@@ -406,7 +407,7 @@ __global__ void __launch_bounds__(256, 1)
         *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
         *reinterpret_cast<uint4*>(dst + pbw::kHalf) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
     }
-    for (int i = tid; i < 128 * 16; i += 256) {
+    for (int i = tid; i < 128 * 16; i += pbw::kThreads) {
         const int ch = i & 127, g = i >> 7;              // lkf^T: (channel ch, 8-node group g); lanes run over channels
         float v[8];
 #pragma unroll
@@ -423,13 +424,13 @@ __global__ void __launch_bounds__(256, 1)
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     const uint32_t sb = smem_u32(smb);
-    const int q4 = warp & 3, chalf = warp >> 2;          // TMEM lane quadrant (row = 32 q4 + lane), node half
+    const int q4 = warp & 3, cq = warp >> 2;             // TMEM lane quadrant (row = 32 q4 + lane), node quarter
     const uint32_t lane_base = tmem + ((uint32_t)(32 * q4) << 16);
     const float sc = (clip > 0.f ? clip : 1.0f) / temperature;
     uint32_t p1 = 0, p2 = 0;
-    // The fp32 heads of a tile (8 items = 16 float4 per thread) and its per-row scalars travel through registers ONE TILE AHEAD:
+    // The fp32 heads of a tile (4 items = 8 float4 per thread) and its per-row scalars travel through registers ONE TILE AHEAD:
     // the loads of tile t+1 are issued right after tile t's first product and land during its elementwise pass.
-    float4 pre[16];
+    float4 pre[8];
     float pre_g = 0.f, pre_lz = 0.f;
     int pre_a = -1;
     uint32_t pre_mw[4] = {0u, 0u, 0u, 0u};
@@ -437,8 +438,8 @@ __global__ void __launch_bounds__(256, 1)
         const int64_t rt = r0 + (int64_t)t * pbw::kT;
         const int rows = t < ntiles ? (int)(r1 - rt < pbw::kT ? r1 - rt : pbw::kT) : 0;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const int i = tid + 256 * k;
+        for (int k = 0; k < 4; ++k) {
+            const int i = tid + pbw::kThreads * k;
             const int r = 8 * (i >> 7) + (i & 7), c = (i >> 3) & 15;   // conflict-free operand stores (item_rc)
             pre[2 * k] = pre[2 * k + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (r < rows) {
@@ -462,8 +463,8 @@ __global__ void __launch_bounds__(256, 1)
         const int rows = (int)(r1 - rt < pbw::kT ? r1 - rt : pbw::kT);
         // heads tile -> K-major fp16 hi | lo (item = (row, 8-channel chunk)); per-row scalars
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const int i = tid + 256 * k;
+        for (int k = 0; k < 4; ++k) {
+            const int i = tid + pbw::kThreads * k;
             const int r = 8 * (i >> 7) + (i & 7), c = (i >> 3) & 15;
             const float4 a = pre[2 * k], bb = pre[2 * k + 1];
             uint32_t hi[4], lo[4];
@@ -513,15 +514,15 @@ __global__ void __launch_bounds__(256, 1)
             const bool rv = r < rows;
             const float g = s_g[r], lz = s_lz[r];
             const int a = s_a[r];
-            const uint32_t m0 = s_mw[r * 4 + 2 * chalf], m1 = s_mw[r * 4 + 2 * chalf + 1];
+            const uint32_t mw = s_mw[r * 4 + cq];
             float* dut = du_t + (b * R + rt + (rv ? r : 0)) * kE;
 #pragma unroll 1
-            for (int c = 0; c < 64; c += 16) {
-                const int col = 64 * chalf + c;
+            for (int c = 0; c < 32; c += 16) {
+                const int col = 32 * cq + c;
                 uint32_t uv[16];
                 tmem_ld16(lane_base + (uint32_t)col, uv);
                 tc_wait_ld();
-                const uint32_t bits = ((c < 32 ? m0 : m1) >> (c & 31)) & 0xffffu;
+                const uint32_t bits = (mw >> c) & 0xffffu;
                 float du[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
@@ -575,11 +576,11 @@ __global__ void __launch_bounds__(256, 1)
         tc_fence_after();
         {
             const int r = 32 * q4 + lane;
-            float* dh = dheads + (b * R + rt + (r < rows ? r : 0)) * kE + 64 * chalf;
+            float* dh = dheads + (b * R + rt + (r < rows ? r : 0)) * kE + 32 * cq;
 #pragma unroll 1
-            for (int c = 0; c < 64; c += 16) {
+            for (int c = 0; c < 32; c += 16) {
                 uint32_t v[16];
-                tmem_ld16(lane_base + 128u + 64u * (uint32_t)chalf + (uint32_t)c, v);
+                tmem_ld16(lane_base + 128u + 32u * (uint32_t)cq + (uint32_t)c, v);
                 tc_wait_ld();
                 if (r < rows) {
 #pragma unroll
@@ -1482,7 +1483,7 @@ extern "C" int rl4co_eval_ll_bwd(const float* q, const float* gk, const float* g
     if ((rc = ev::set_smem(ev::eval_row_bwd_glimpse_kernel, 2 * table, "eval_ll_bwd (row pass, glimpse)"))) return rc;
     dim3 g1((unsigned)B, (unsigned)ev::grid_split(B, 1));
     if ((rc = ev::set_smem(ev::eval_ptr_bwd_tc_kernel, ev::pbw::kSmem, "eval_ll_bwd (row pass, pointer)"))) return rc;
-    ev::eval_ptr_bwd_tc_kernel<<<g1, 256, ev::pbw::kSmem, st>>>(lkf, maskw, taken, heads, lse_z, dlogp, dheads, du_t, R, n_nodes,
+    ev::eval_ptr_bwd_tc_kernel<<<g1, ev::pbw::kThreads, ev::pbw::kSmem, st>>>(lkf, maskw, taken, heads, lse_z, dlogp, dheads, du_t, R, n_nodes,
                                                                tanh_clipping, temperature);
     R4_CHECK_LAUNCH("eval_ll_bwd (row pass, pointer)");
     ev::eval_row_bwd_glimpse_kernel<<<g1, ev::kThreads, 2 * table, st>>>(q, gk, gv, maskw, heads, lse_h, dheads, dq, dd, R,
