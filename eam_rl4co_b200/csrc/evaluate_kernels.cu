@@ -10,14 +10,14 @@
 //            O_h = P V_h (masked nodes have probability exactly 0 and contribute no gradient);
 //   pointer  (attention.py:296-301,328; decoding.py:140-190): logits = heads . lkf[n] / sqrt(E), then tanh clip, mask,
 //            temperature, log_softmax, gather at the taken action.
-// The backward recomputes the probabilities from the saved log-sum-exps (flash-attention style) in two passes:
-//   row pass : everything that reduces over NODES - du = d loss / d raw logit and dheads = dU lkf on tcgen05 (the logits are
-//             recomputed as an MMA per 128-row tile, du converted in place into the A operand of the second product); dq on
-//             the CUDA cores (a warp per four rows, only feasible nodes visited);
-//   node pass (tcgen05): dgk = dS^T Q, dgv = P^T dO, dlkf = dU^T O - the reductions over ROWS as MMAs with split-fp16 operands
-//             and fp32 accumulators that stay in TMEM across a CTA's row tiles.  (fp32 shared-memory
-//             atomics are CAS loops on sm_100: a first version that accumulated the table gradients in shared memory spent
-//             25 of 31 ms of the c5 evaluate in ATOMS.CAST.SPIN.)
+// The backward recomputes the probabilities from the saved log-sum-exps (flash-attention style) in two passes, both on tcgen05:
+//   row pass : everything that reduces over NODES, TMEM lane = row - du = d loss / d raw logit and dheads = dU lkf (the logits are
+//             recomputed as an MMA per 128-row tile, du converted in place into the A operand of the second product); then
+//             S = Q K^T and dP = dO V^T per head, dS = P (dP - D) in place, dq = 0.25 dS K;
+//   node pass: the reductions over ROWS, TMEM lane = node - dgk = dS^T Q, dgv = P^T dO, dlkf = dU^T O - as MMAs with split-fp16
+//             operands and fp32 accumulators that stay in TMEM across a CTA's row tiles.  (fp32 shared-memory atomics are CAS
+//             loops on sm_100: a first version that accumulated the table gradients in shared memory spent 25 of 31 ms of the c5
+//             evaluate in ATOMS.CAST.SPIN.)
 //
 // exp / tanh / log on the MUFU approximations (ex2, rcp, lg2: the arithmetic of the tensor-path rollout kernels).
 #include "decode_core.cuh"
@@ -26,18 +26,8 @@
 namespace r4 {
 namespace ev {
 
-constexpr int kThreads = 512;
 constexpr float kInvSqrtE = 0.08838834764831845f;   // 1 / sqrt(128)
 
-// The row kernels read a table row as "head h, 4-channel chunk i" = 8 lanes x 16 B per LDS.128; with the natural layout the
-// lanes are 64 B apart and heads h, h + 2, h + 4, h + 6 share banks (4-way conflict, measured 2.2x on the forward kernel).
-// Swizzled layout: chunk i of head h of node nd at nd * 128 + 32 i + 4 h, i.e. the 8 lanes read 128 contiguous bytes.
-__device__ __forceinline__ void copy_table_swz(float* dst, const float* __restrict__ src, int n) {
-    for (int i = threadIdx.x; i < n * (kE / 4); i += blockDim.x) {
-        const int nd = i >> 5, c4 = i & 31;            // c4 = 4 h + chunk
-        reinterpret_cast<float4*>(dst)[nd * 32 + (c4 & 3) * 8 + (c4 >> 2)] = reinterpret_cast<const float4*>(src)[i];
-    }
-}
 __device__ __forceinline__ uint32_t sel4u(const uint32_t (&v)[kNB], int k) {
     return k == 0 ? v[0] : (k == 1 ? v[1] : (k == 2 ? v[2] : v[3]));
 }
@@ -52,148 +42,16 @@ __device__ __forceinline__ void row_range(int64_t R, int64_t& r0, int64_t& r1) {
 // exp on the MUFU ex2 approximation (relative error ~2^-22, the arithmetic of the tensor-path rollout kernels)
 __device__ __forceinline__ float fexp(float x) { return __expf(x); }
 
-// ---- lane mapping of the row kernels ------------------------------------------------------------------------------------------
-// A warp owns FOUR consecutive rows (consecutive steps of one start: nearly the same feasible set); lane = 8 ri + h holds
-// head h of row ri, i.e. 16 query / head channels in registers.  A 16-channel dot product is 16 FMAs without a shuffle
-// (a lane-owns-4-channels mapping needs two shuffle levels per score and repeats the softmax arithmetic in four lanes:
-// 2.4x the instructions, measured), table rows are read as 4 x LDS.128 (the four rows of the warp broadcast).
-// The node loops run over the UNION of the four rows' feasible sets; a row's own mask gates its probabilities.
-__device__ __forceinline__ void ld16(const float* __restrict__ p, float (&v)[16]) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const float4 t = ld4(p + 4 * i);
-        v[4 * i] = t.x;
-        v[4 * i + 1] = t.y;
-        v[4 * i + 2] = t.z;
-        v[4 * i + 3] = t.w;
-    }
-}
-__device__ __forceinline__ void st16(float* __restrict__ p, const float (&v)[16]) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-        *reinterpret_cast<float4*>(p + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-}
-// t = swizzled table row of a node + 4 h (copy_table_swz): chunk i at t + 32 i
-__device__ __forceinline__ float dot16(const float (&a)[16], const float* t) {
-    float s0 = 0.f, s1 = 0.f;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const float4 k = ld4(t + 32 * i);
-        s0 = fmaf(a[4 * i], k.x, s0);
-        s1 = fmaf(a[4 * i + 1], k.y, s1);
-        s0 = fmaf(a[4 * i + 2], k.z, s0);
-        s1 = fmaf(a[4 * i + 3], k.w, s1);
-    }
-    return s0 + s1;
-}
-__device__ __forceinline__ void axpy16(float (&acc)[16], float a, const float* t) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const float4 k = ld4(t + 32 * i);
-        acc[4 * i] = fmaf(a, k.x, acc[4 * i]);
-        acc[4 * i + 1] = fmaf(a, k.y, acc[4 * i + 1]);
-        acc[4 * i + 2] = fmaf(a, k.z, acc[4 * i + 2]);
-        acc[4 * i + 3] = fmaf(a, k.w, acc[4 * i + 3]);
-    }
-}
-// union of a per-row word over the four rows of the warp
-__device__ __forceinline__ uint32_t or_rows(uint32_t w) {
-    w |= __shfl_xor_sync(kFull, w, 8);
-    w |= __shfl_xor_sync(kFull, w, 16);
-    return w;
-}
-// up to G node indices of `wb` (ascending), the rest repeat the first one with ok = false
-template <int G>
-__device__ __forceinline__ void next_nodes(uint32_t& wb, int (&j)[G], bool (&ok)[G]) {
-#pragma unroll
-    for (int u = 0; u < G; ++u) {
-        ok[u] = wb != 0u;
-        j[u] = ok[u] ? (__ffs(wb) - 1) : 0;
-        wb &= wb - 1u;
-    }
-#pragma unroll
-    for (int u = 1; u < G; ++u) j[u] = ok[u] ? j[u] : j[0];
-}
-// du_t [B,R,128]: d loss / d (raw logit of node n), column = node; columns >= n are zero
-
-// ---- backward, row pass of the glimpse: dq = 0.25 sum_n dS[n] k[n], dS = P (dP - D), P from the saved log-sum-exp; dd = D ------
-__global__ void __launch_bounds__(kThreads, 1)
-    eval_row_bwd_glimpse_kernel(const float* __restrict__ q, const float* __restrict__ gk, const float* __restrict__ gv,
-                                const uint32_t* __restrict__ maskw, const float* __restrict__ heads,
-                                const float* __restrict__ lse_h, const float* __restrict__ dheads, float* __restrict__ dq,
-                                float* __restrict__ dd_out, int64_t R, int n) {
-    extern __shared__ __align__(16) float sm[];
-    float* s_gk = sm;
-    float* s_gv = sm + n * kE;
-    const int64_t b = blockIdx.x;
-    copy_table_swz(s_gk, gk + b * n * kE, n);
-    copy_table_swz(s_gv, gv + b * n * kE, n);
-    __syncthreads();
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-    const int ri = lane >> 3, h = lane & 7;
-    int64_t r0, r1;
-    row_range(R, r0, r1);
-    for (int64_t rb = r0 + 4 * warp; rb < r1; rb += 4 * nw) {
-        const bool valid = rb + ri < r1;
-        const int64_t row = b * R + (valid ? rb + ri : r1 - 1);
-        uint32_t w[kNB], wu[kNB];
-        {
-            const uint4 mw = *reinterpret_cast<const uint4*>(maskw + row * kNB);
-            w[0] = mw.x, w[1] = mw.y, w[2] = mw.z, w[3] = mw.w;
-        }
-#pragma unroll
-        for (int blk = 0; blk < kNB; ++blk) wu[blk] = or_rows(w[blk]);
-        float dh[16];
-        ld16(dheads + row * kE + 16 * h, dh);
-        float dd = 0.f;
-        {
-            float o[16];
-            ld16(heads + row * kE + 16 * h, o);
-#pragma unroll
-            for (int i = 0; i < 16; ++i) dd = fmaf(dh[i], o[i], dd);
-        }
-        float qs[16];
-        ld16(q + row * kE + 16 * h, qs);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) qs[i] *= 0.25f;
-        const float lh = lse_h[row * kH + h];
-        if (valid) dd_out[row * kH + h] = dd;
-        float dqs[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) dqs[i] = 0.f;
-#pragma unroll 1
-        for (int blk = 0; blk < kNB; ++blk) {
-            uint32_t wb = sel4u(wu, blk);
-            const uint32_t own = sel4u(w, blk);
-            while (wb) {
-                int j[2];
-                bool ok[2];
-                next_nodes<2>(wb, j, ok);
-#pragma unroll
-                for (int u = 0; u < 2; ++u) {
-                    const float* kr = s_gk + (blk * 32 + j[u]) * kE + 4 * h;
-                    const float sv = dot16(qs, kr);
-                    const float dp = dot16(dh, s_gv + (blk * 32 + j[u]) * kE + 4 * h);
-                    const bool f = ok[u] && ((own >> j[u]) & 1u);
-                    const float ds = f ? fexp(sv - lh) * (dp - dd) : 0.f;
-                    axpy16(dqs, ds, kr);
-                }
-            }
-        }
-        if (valid) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) dqs[i] *= 0.25f;
-            st16(dq + row * kE + 16 * h, dqs);
-        }
-    }
-}
-
-// ---- backward, node pass: the GEMM-shaped reductions over ROWS, on tcgen05 ---------------------------------------------------------
-//   dlkf = dU^T O                      : eval_dlk_tc_kernel;
-//   dgv = P^T dO, dgk = dS^T (0.25 Q)  : eval_dkv_tc_kernel (transposed score tiles, P^T / dS^T as TS-form A operands in TMEM).
-// (Round-2 history: a CUDA-core node pass with register accumulators - a warp per two nodes visiting every row, row tiles
-// staged with cp.async - took 4.3 ms for the three reductions; the two tensor-core kernels take 0.23 + 1.9 ms.)
-constexpr int kMaxNodes = 128;   // four mask words per row, 128-node MMA tiles, three [n,128] fp32 tables in shared memory (forward)
+// ---- the kernels below: every product of the evaluate on tcgen05 -------------------------------------------------------------------
+//   backward, reductions over ROWS: dlkf = dU^T O (eval_dlk_tc_kernel); dgv = P^T dO, dgk = dS^T (0.25 Q) (eval_dkv_tc_kernel:
+//     transposed score tiles, P^T / dS^T as TS-form A operands in TMEM);
+//   backward, row passes: du and dheads = dU lkf (eval_ptr_bwd_tc_kernel); dq = 0.25 dS K and D = dO . O (eval_dq_tc_kernel);
+//   forward: glimpse (eval_glimpse_fwd_tc_kernel) and pointer (eval_ptr_fwd_tc_kernel).
+// du_t [B,R,128] is d loss / d (raw logit of node n), column = node; columns >= n are zero.
+// (Round-2 history, measured on c5: CUDA-core versions - a warp per four rows x eight heads with the tables in shared memory for
+// the row work, a warp per two nodes with register accumulators for the reductions over rows - took 2.1 ms forward and 7.5 ms
+// backward; the tensor-core kernels take 1.06 and 2.65 ms.)
+constexpr int kMaxNodes = 128;   // four mask words per row, 128-node MMA tiles
 
 // cp.async staging of row tiles (eval_dlk_tc_kernel)
 __device__ __forceinline__ void cp_async16(void* dst, const void* src) {
@@ -1393,6 +1251,277 @@ __global__ void __launch_bounds__(256, 2)
     if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
+// ---- backward, glimpse part of the row pass on the tensor cores: dq = 0.25 dS K, D = dO . O ---------------------------------------
+// CTA = (instance, row range, TWO heads); per tile of 128 rows and head h (TMEM lane = row):
+//   S  = (0.25 Q_h) K_h^T and dP = dO_h V_h^T   [rows x nodes]   3 + 3 split-fp16 MMAs against the resident K_h / V_h tiles
+//   thread (row, 64 nodes): P = exp(S - lse_h[row]) on the feasible nodes (the saved log-sum-exp: no maximum pass),
+//     dS = P (dP - D_h[row]) written over S IN PLACE as the fp16 hi / lo TS-form A operand
+//   dq_h = dS K_h   [rows x 16]   3 x npad / 16 TS-form MMAs (N = 16) against the resident K_h^T tile; stored (x 0.25) while the next
+//     head's products run.  D_h[row] = dO_h . O_h comes from the staging of the tile (also written out: the dK / dV kernel reads it).
+// TMEM: S at 0, dP at 112 (128 if n > 112), two dq slots behind them: 256 columns for n <= 112 (two CTAs per SM; ~84 KB of shared
+// memory each), 512 beyond (the second CTA of an SM then waits for the first one's columns).
+namespace dqk {
+constexpr int kNH = 2;
+constexpr uint32_t kHeadTile = 4096;                  // [128 x 16] or [16 x 128] fp16 K-major (hi or lo)
+constexpr uint32_t kOffK = 0;                         // K_h   [node][dim] hi | lo per head (B of S)
+constexpr uint32_t kOffV = kNH * 2 * kHeadTile;       // V_h   [node][dim] hi | lo per head (B of dP)
+constexpr uint32_t kOffKT = 2 * kOffV;                // K_h^T [dim][node] hi | lo per head (B of dq)
+constexpr uint32_t kOffQ = 3 * kOffV;                 // Q_h  tile [row][dim] hi | lo per head (A of S)
+constexpr uint32_t kOffDO = 4 * kOffV;                // dO_h tile [row][dim] hi | lo per head (A of dP)
+constexpr uint32_t kOffMaskW = 5 * kOffV;             // [128 rows][4] u32
+constexpr uint32_t kOffLse = kOffMaskW + 128 * 16;    // [2 heads][128] f32
+constexpr uint32_t kOffD = kOffLse + kNH * 128 * 4;   // [2 heads][128] f32
+constexpr uint32_t kOffBar = kOffD + kNH * 128 * 4;
+constexpr size_t kSmem = kOffBar + 64;
+}  // namespace dqk
+
+__global__ void __launch_bounds__(256, 2)
+    eval_dq_tc_kernel(const float* __restrict__ q, const float* __restrict__ gk, const float* __restrict__ gv,
+                      const uint32_t* __restrict__ maskw, const float* __restrict__ heads, const float* __restrict__ lse_h,
+                      const float* __restrict__ dheads, float* __restrict__ dq, float* __restrict__ dd_out, int64_t R, int n) {
+    using namespace tc;
+    extern __shared__ __align__(128) unsigned char smb[];
+    uint32_t* s_mw = reinterpret_cast<uint32_t*>(smb + dqk::kOffMaskW);
+    float* s_lse = reinterpret_cast<float*>(smb + dqk::kOffLse);
+    float* s_d = reinterpret_cast<float*>(smb + dqk::kOffD);
+    uint64_t* bar1 = reinterpret_cast<uint64_t*>(smb + dqk::kOffBar);
+    uint64_t* bar2 = bar1 + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smb + dqk::kOffBar + 32);
+    const int64_t b = blockIdx.x;
+    const int h0 = (int)blockIdx.z * dqk::kNH;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    int64_t r0, r1;
+    row_range(R, r0, r1);
+    if (r0 >= r1) return;
+    const int ntiles = (int)((r1 - r0 + 127) / 128);
+    const int npad = (n + 15) & ~15;
+    const uint32_t col_dp = npad <= 112 ? 112u : 128u, col_dq = 2u * col_dp, tmem_cols = npad <= 112 ? 256u : 512u;
+    if (tid == 0) {
+        mbar_init(bar1, 1);
+        mbar_init(bar2, 1);
+        fence_mbar_init();
+    }
+    __syncwarp();
+    if (warp == 0) tmem_alloc(tmem_slot, tmem_cols);
+    // resident B operands (nodes >= n are zero).  K_h, V_h: item = (table, head, node m, 8-dim chunk c), lanes over m & 7 first
+    for (int i = tid; i < 2 * dqk::kNH * 256; i += 256) {
+        const int tab = i >> 9, hl = (i >> 8) & 1, m = 8 * ((i >> 4) & 15) + (i & 7), c = (i >> 3) & 1;
+        const float* src = (tab ? gv : gk) + ((size_t)b * n + m) * kE + 16 * (h0 + hl) + 8 * c;
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bb = a;
+        if (m < n) {
+            a = ld4(src);
+            bb = ld4(src + 4);
+        }
+        uint32_t hi[4], lo[4];
+        split2(a.x, a.y, hi[0], lo[0]);
+        split2(a.z, a.w, hi[1], lo[1]);
+        split2(bb.x, bb.y, hi[2], lo[2]);
+        split2(bb.z, bb.w, hi[3], lo[3]);
+        unsigned char* dst = smb + (tab ? dqk::kOffV : dqk::kOffK) + (uint32_t)hl * 2u * dqk::kHeadTile + (uint32_t)(m >> 3) * 256u +
+                             (uint32_t)c * 128u + (uint32_t)(m & 7) * 16u;
+        *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(dst + dqk::kHeadTile) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+    // K_h^T: item = (head, 8-node group g, dim dm): 8 nodes of one dim = one K chunk
+    for (int i = tid; i < dqk::kNH * 256; i += 256) {
+        const int hl = i >> 8, g = (i >> 4) & 15, dm = i & 15;
+        float v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = (8 * g + k < n) ? gk[((size_t)b * n + 8 * g + k) * kE + 16 * (h0 + hl) + dm] : 0.f;
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int w = 0; w < 4; ++w) split2(v[2 * w], v[2 * w + 1], hi[w], lo[w]);
+        unsigned char* dst = smb + dqk::kOffKT + (uint32_t)hl * 2u * dqk::kHeadTile + (uint32_t)(dm >> 3) * 2048u + (uint32_t)g * 128u +
+                             (uint32_t)(dm & 7) * 16u;
+        *reinterpret_cast<uint4*>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(dst + dqk::kHeadTile) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+    // per tile: the head slices of q, dheads and heads (2 heads x 128 rows x 2 chunks = 2 items per thread and tensor, item k =
+    // head k), lse (thread = (head, row)) and the mask words travel through registers one tile ahead
+    float4 pq[4], pg[4], po[4];
+    float pre_lse = 0.f;
+    uint32_t pre_mw[4] = {0u, 0u, 0u, 0u};
+    const int sr = 8 * ((tid >> 4) & 15) + (tid & 7), sc = (tid >> 3) & 1;     // staging row and chunk of this thread
+    auto prefetch = [&](int t) {
+        const int64_t rt = r0 + (int64_t)t * 128;
+        const int rows = t < ntiles ? (int)(r1 - rt < 128 ? r1 - rt : 128) : 0;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            pq[2 * k] = pq[2 * k + 1] = pg[2 * k] = pg[2 * k + 1] = po[2 * k] = po[2 * k + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (sr < rows) {
+                const int64_t off = (b * R + rt + sr) * kE + 16 * (h0 + k) + 8 * sc;
+                pq[2 * k] = ld4(q + off);
+                pq[2 * k + 1] = ld4(q + off + 4);
+                pg[2 * k] = ld4(dheads + off);
+                pg[2 * k + 1] = ld4(dheads + off + 4);
+                po[2 * k] = ld4(heads + off);
+                po[2 * k + 1] = ld4(heads + off + 4);
+            }
+        }
+        {
+            const int hl = tid >> 7, rr = tid & 127;
+            pre_lse = rr < rows ? lse_h[(b * R + rt + rr) * kH + h0 + hl] : 0.f;
+        }
+        if (tid < 128) {
+            const bool ok = tid < rows;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) pre_mw[k] = ok ? maskw[(b * R + rt + tid) * kNB + k] : 0u;
+        }
+    };
+    prefetch(0);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t sb = smem_u32(smb);
+    const int q4 = warp & 3, chalf = warp >> 2;          // TMEM lane quadrant (row = 32 q4 + lane), node half
+    const int r = 32 * q4 + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * q4) << 16);
+    uint32_t p1 = 0, p2 = 0;
+    bool pending = false;
+    int64_t epi_rt = 0;
+    int epi_rows = 0, epi_h = 0, cnt = 0;
+    auto epilogue = [&]() {   // dq of the previous (tile, head): slot (cnt - 1) & 1, 8 of its 16 columns per node half
+        uint32_t v[8];
+        tmem_ld8(lane_base + col_dq + 16u * (uint32_t)((cnt - 1) & 1) + 8u * (uint32_t)chalf, v);
+        tc_wait_ld();
+        if (r < epi_rows) {
+            float* dst = dq + (b * R + epi_rt + r) * kE + 16 * epi_h + 8 * chalf;
+            *reinterpret_cast<float4*>(dst) = make_float4(0.25f * __uint_as_float(v[0]), 0.25f * __uint_as_float(v[1]),
+                                                          0.25f * __uint_as_float(v[2]), 0.25f * __uint_as_float(v[3]));
+            *reinterpret_cast<float4*>(dst + 4) = make_float4(0.25f * __uint_as_float(v[4]), 0.25f * __uint_as_float(v[5]),
+                                                              0.25f * __uint_as_float(v[6]), 0.25f * __uint_as_float(v[7]));
+        }
+    };
+    for (int t = 0; t < ntiles; ++t) {
+        const int64_t rt = r0 + (int64_t)t * 128;
+        const int rows = (int)(r1 - rt < 128 ? r1 - rt : 128);
+        // (the S / dP products of the previous tile have completed: their bar1 were waited for)
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const float4 a = pq[2 * k], bb = pq[2 * k + 1], g0 = pg[2 * k], g1 = pg[2 * k + 1], o0 = po[2 * k], o1 = po[2 * k + 1];
+            uint32_t hi[4], lo[4];
+            split2(a.x * 0.25f, a.y * 0.25f, hi[0], lo[0]);
+            split2(a.z * 0.25f, a.w * 0.25f, hi[1], lo[1]);
+            split2(bb.x * 0.25f, bb.y * 0.25f, hi[2], lo[2]);
+            split2(bb.z * 0.25f, bb.w * 0.25f, hi[3], lo[3]);
+            const uint32_t off = (uint32_t)k * 2u * dqk::kHeadTile + (uint32_t)(sr >> 3) * 256u + (uint32_t)sc * 128u + (uint32_t)(sr & 7) * 16u;
+            *reinterpret_cast<uint4*>(smb + dqk::kOffQ + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(smb + dqk::kOffQ + off + dqk::kHeadTile) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            split2(g0.x, g0.y, hi[0], lo[0]);
+            split2(g0.z, g0.w, hi[1], lo[1]);
+            split2(g1.x, g1.y, hi[2], lo[2]);
+            split2(g1.z, g1.w, hi[3], lo[3]);
+            *reinterpret_cast<uint4*>(smb + dqk::kOffDO + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(smb + dqk::kOffDO + off + dqk::kHeadTile) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            // D = dO . O: this thread's 8 channels, the other chunk of the row is 8 lanes away
+            float dpart = g0.x * o0.x + g0.y * o0.y + g0.z * o0.z + g0.w * o0.w + g1.x * o1.x + g1.y * o1.y + g1.z * o1.z + g1.w * o1.w;
+            dpart += __shfl_xor_sync(kFull, dpart, 8);
+            if (sc == 0) {
+                s_d[k * 128 + sr] = dpart;
+                if (sr < rows) dd_out[(b * R + rt + sr) * kH + h0 + k] = dpart;
+            }
+        }
+        s_lse[tid] = pre_lse;                              // tid = head * 128 + row
+        if (tid < 128) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) s_mw[tid * 4 + k] = pre_mw[k];
+        }
+        fence_proxy_async();
+        __syncthreads();
+        prefetch(t + 1);
+        const uint32_t m0 = s_mw[r * 4 + 2 * chalf], m1 = s_mw[r * 4 + 2 * chalf + 1];
+        for (int hl = 0; hl < dqk::kNH; ++hl) {
+            if (pending) {                               // dq of the previous head is complete and dS has been read
+                mbar_wait(bar2, p2);
+                p2 ^= 1u;
+                tc_fence_after();
+            }
+            if (warp == 0) {
+                if (elect_one()) {
+                    tc_fence_after();
+                    const uint32_t id = idesc_f16(128, npad);
+                    const uint32_t ho = (uint32_t)hl * 2u * dqk::kHeadTile;
+                    const uint64_t q_hi = smem_desc(sb + dqk::kOffQ + ho, 128, 256), q_lo = smem_desc(sb + dqk::kOffQ + ho + dqk::kHeadTile, 128, 256);
+                    const uint64_t k_hi = smem_desc(sb + dqk::kOffK + ho, 128, 256), k_lo = smem_desc(sb + dqk::kOffK + ho + dqk::kHeadTile, 128, 256);
+                    const uint64_t g_hi = smem_desc(sb + dqk::kOffDO + ho, 128, 256), g_lo = smem_desc(sb + dqk::kOffDO + ho + dqk::kHeadTile, 128, 256);
+                    const uint64_t v_hi = smem_desc(sb + dqk::kOffV + ho, 128, 256), v_lo = smem_desc(sb + dqk::kOffV + ho + dqk::kHeadTile, 128, 256);
+                    mma_ss(tmem, q_hi, k_hi, id, 0u);                              // S
+                    mma_ss(tmem, q_hi, k_lo, id, 1u);
+                    mma_ss(tmem, q_lo, k_hi, id, 1u);
+                    mma_ss(tmem + col_dp, g_hi, v_hi, id, 0u);                     // dP
+                    mma_ss(tmem + col_dp, g_hi, v_lo, id, 1u);
+                    mma_ss(tmem + col_dp, g_lo, v_hi, id, 1u);
+                    tc_commit(bar1);
+                }
+                __syncwarp();
+            }
+            if (pending) {
+                epilogue();
+                pending = false;
+            }
+            mbar_wait(bar1, p1);
+            p1 ^= 1u;
+            tc_fence_after();
+            const float lse = s_lse[hl * 128 + r], dval = s_d[hl * 128 + r];
+#pragma unroll 1
+            for (int c = 0; c < 64; c += 16) {
+                const int col = 64 * chalf + c;
+                if (col >= npad) break;
+                uint32_t sv[16], dv[16];
+                tmem_ld16(lane_base + (uint32_t)col, sv);
+                tmem_ld16(lane_base + col_dp + (uint32_t)col, dv);
+                tc_wait_ld();
+                const uint32_t bits = ((c < 32 ? m0 : m1) >> (c & 31)) & 0xffffu;
+                uint32_t hi[8], lo[8];
+#pragma unroll
+                for (int i = 0; i < 16; i += 2) {
+                    const float pa = (bits >> i) & 1u ? fexp(__uint_as_float(sv[i]) - lse) : 0.f;
+                    const float pb = (bits >> (i + 1)) & 1u ? fexp(__uint_as_float(sv[i + 1]) - lse) : 0.f;
+                    split2(pa * (__uint_as_float(dv[i]) - dval), pb * (__uint_as_float(dv[i + 1]) - dval), hi[i >> 1], lo[i >> 1]);
+                }
+                tmem_st8(lane_base + (uint32_t)col, hi);
+                tmem_st8(lane_base + (uint32_t)col + 8u, lo);
+            }
+            tc_wait_st();
+            tc_fence_before();
+            __syncthreads();
+            epi_rt = rt;
+            epi_rows = rows;
+            epi_h = h0 + hl;
+            if (warp == 0) {
+                if (elect_one()) {
+                    tc_fence_after();
+                    const uint32_t id = idesc_f16(128, 16);
+                    const uint32_t ko = sb + dqk::kOffKT + (uint32_t)hl * 2u * dqk::kHeadTile;
+                    uint64_t kt_hi = smem_desc(ko, 128, 2048), kt_lo = smem_desc(ko + dqk::kHeadTile, 128, 2048);
+                    const uint32_t d = tmem + col_dq + 16u * (uint32_t)(cnt & 1);
+                    for (int ks = 0; ks < npad / 16; ++ks) {
+                        mma_ts(d, tmem + 16u * ks, kt_hi, id, ks == 0 ? 0u : 1u);   // dq_h = dS K_h
+                        mma_ts(d, tmem + 16u * ks, kt_lo, id, 1u);
+                        mma_ts(d, tmem + 16u * ks + 8u, kt_hi, id, 1u);
+                        kt_hi += 256u >> 4;
+                        kt_lo += 256u >> 4;
+                    }
+                    tc_commit(bar2);
+                }
+                __syncwarp();
+            }
+            ++cnt;
+            pending = true;
+        }
+    }
+    if (pending) {
+        mbar_wait(bar2, p2);
+        tc_fence_after();
+        epilogue();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, tmem_cols);
+}
+
 // Row split per instance: `units` equal CTAs per split step over sms * ctas_per_sm slots, the split in [1, 32] with the
 // fewest waves per unit of work (64 instances x 2 = 128 CTAs would leave 20 SMs idle; x 9 = 576 CTAs fill 3.9 of 4 waves).
 static int grid_split(int64_t units, int ctas_per_sm) {
@@ -1479,15 +1608,14 @@ extern "C" int rl4co_eval_ll_bwd(const float* q, const float* gk, const float* g
     if ((rc = eval_check("eval_ll_bwd", B, R, n_nodes, temperature))) return rc;
     if (B == 0 || R == 0) return RL4CO_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    const size_t table = (size_t)n_nodes * kE * sizeof(float);
-    if ((rc = ev::set_smem(ev::eval_row_bwd_glimpse_kernel, 2 * table, "eval_ll_bwd (row pass, glimpse)"))) return rc;
     dim3 g1((unsigned)B, (unsigned)ev::grid_split(B, 1));
     if ((rc = ev::set_smem(ev::eval_ptr_bwd_tc_kernel, ev::pbw::kSmem, "eval_ll_bwd (row pass, pointer)"))) return rc;
     ev::eval_ptr_bwd_tc_kernel<<<g1, ev::pbw::kThreads, ev::pbw::kSmem, st>>>(lkf, maskw, taken, heads, lse_z, dlogp, dheads, du_t, R, n_nodes,
                                                                tanh_clipping, temperature);
     R4_CHECK_LAUNCH("eval_ll_bwd (row pass, pointer)");
-    ev::eval_row_bwd_glimpse_kernel<<<g1, ev::kThreads, 2 * table, st>>>(q, gk, gv, maskw, heads, lse_h, dheads, dq, dd, R,
-                                                                        n_nodes);
+    if ((rc = ev::set_smem(ev::eval_dq_tc_kernel, ev::dqk::kSmem, "eval_ll_bwd (row pass, glimpse)"))) return rc;
+    dim3 g2((unsigned)B, (unsigned)ev::grid_split(4 * B, 2), 4u);
+    ev::eval_dq_tc_kernel<<<g2, 256, ev::dqk::kSmem, st>>>(q, gk, gv, maskw, heads, lse_h, dheads, dq, dd, R, n_nodes);
     R4_CHECK_LAUNCH("eval_ll_bwd (row pass)");
     // node pass (tcgen05): dlkf = dU^T O, then dgv = P^T dO and dgk = dS^T (0.25 Q)
     if ((rc = ev::set_smem(ev::eval_dlk_tc_kernel, ev::dlk::kSmem, "eval_ll_bwd (dlkf)"))) return rc;
