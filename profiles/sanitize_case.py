@@ -1,7 +1,7 @@
 """Tiny end-to-end exercise of every product kernel for compute-sanitizer (profiles/r02_sanitize.sh):
 TSP20 / CVRP20 multistart rollouts on the tcgen05 kernel (greedy, sampling, evaluate), the fp32 multistart kernel,
 single-start rollouts on the cooperative and streaming kernels, the step-granular kernels, the encoder kernels,
-best-of-starts and the state replay."""
+best-of-starts, the state replay and one training step (query + evaluate kernels, forward and backward)."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -29,6 +29,10 @@ for env_name in ("tsp", "cvrp"):
     o2 = am(td.clone(), env, decode_type="greedy", fused=False)          # step-granular kernels
     o3 = pomo(td.clone(), env, decode_type="multistart_greedy", fused=False)
     st = train.teacher_forced_states(env, td, out["actions"], N)
+    # training step: query rows, evaluate forward / backward (all tcgen05 kernels), query gradient
+    pomo.train()
+    stats = train.pomo_train_step(pomo, env, td.clone(), optimizer=None, noise_seed=5)
+    pomo.eval()
     torch.cuda.synchronize()
-    print(env_name, "ok", out["reward"].mean().item(), o1["reward"].mean().item(), o2["reward"].mean().item())
+    print(env_name, "ok", out["reward"].mean().item(), o1["reward"].mean().item(), o2["reward"].mean().item(), stats["loss"])
 print("sanitize case done")
