@@ -259,7 +259,9 @@ def graphed_encoder(policy, td, num_warmup_iters: int = 3):
     kernels per step are CPU-bound, replayed from two graphs they are not.  Returns `encode(td) -> h [B, n, E]` (with
     its autograd graph) for instances of the shapes of `td`; pass it as `pomo_train_step(..., encoder=encode)`.  The
     output and the parameter gradients live in the graphs' static buffers: valid until the next call / backward.
-    Buffers (BatchNorm running statistics) are restored after the capture's warm-up passes."""
+    Buffers (BatchNorm running statistics) are restored after the capture's warm-up passes.  (PyTorch warns once that the
+    parameters' AccumulateGrad nodes were created on the capture's side stream: the engine then synchronises the two
+    streams when it accumulates the encoder gradients, which is what the step needs anyway.)"""
     keys = [k for k in ("locs", "demand") if k in td.keys()]
 
     class _Encode(torch.nn.Module):

@@ -256,3 +256,53 @@ def test_graphed_encoder_step_equals_the_eager_step(env_name):
             # (biases in front of a normalisation layer have gradients that are rounding noise: floor the scale)
             scale = max(p.grad.abs().max().item(), 1e-2 * gmax)
             assert (p.grad - p2.grad).abs().max().item() / scale < 1e-4, k
+
+
+@pytest.mark.parametrize("B,S,Tm,n", [(3, 1, 37, 101), (2, 131, 1, 128), (2, 5, 1, 2), (5, 13, 10, 64)])
+def test_evaluate_entry_points_stay_inside_their_buffers(B, S, Tm, n):
+    """Every output / scratch buffer of rl4co_eval_query_* and rl4co_eval_ll_* sits between two guard bands filled with a
+    sentinel; after forward and backward the bands are untouched (ragged tiles, n below / at the tile width)."""
+    import ctypes as C
+    from eam_rl4co_b200 import _lib
+    L = _lib.lib()
+    R, G, SENT = S * Tm, 4096, -7.25
+    g = torch.Generator().manual_seed(B + R + n)
+    bufs = []
+
+    def guarded(*shape, dtype=torch.float32):
+        numel = 1
+        for d in shape:
+            numel *= d
+        flat = torch.full((numel + 2 * G,), SENT if dtype.is_floating_point else -7, dtype=dtype, device=DEV)
+        bufs.append((flat, numel))
+        return flat[G:G + numel].view(*shape)
+
+    dev = lambda t: t.to(DEV).contiguous()
+    pb, gctx, wcap = dev(torch.randn(B, n, 128, generator=g)), dev(torch.randn(B, 128, generator=g)), dev(torch.randn(128, generator=g))
+    gk, gv, lkf = (dev(torch.randn(B, n, 128, generator=g)) for _ in range(3))
+    cur, rem = dev(torch.randint(0, n, (B, S, Tm), generator=g)), dev(torch.rand(B, S, Tm, generator=g))
+    mask = torch.rand(B, R, n, generator=g) < 0.5
+    taken = torch.randint(0, n, (B, R), generator=g)
+    mask.scatter_(2, taken[..., None], True)
+    mask, taken = dev(mask), dev(taken)
+    dlogp = dev(torch.randn(B, R, generator=g))
+    q, heads, dheads, du_t, dq = (guarded(B, R, 128) for _ in range(5))
+    logp, lse_z, lse_h, dd = guarded(B, R), guarded(B, R), guarded(B, R, 8), guarded(B, R, 8)
+    maskw = guarded(B, R, 4, dtype=torch.int32)
+    dgk, dgv, dlkf, dpb, dwcap = guarded(B, n, 128), guarded(B, n, 128), guarded(B, n, 128), guarded(B, n, 128), guarded(128)
+    for t in (dgk, dgv, dlkf, dpb, dwcap):
+        t.zero_()
+    i64, i32, f32, p = C.c_int64, C.c_int32, C.c_float, _lib.ptr
+    st = _lib.stream_ptr()
+    _lib.check(L.rl4co_eval_query_fwd(p(pb), None, p(wcap), p(gctx), p(cur), None, p(rem), p(q), i64(B), i64(S), i64(Tm), i32(n), st), "q fwd")
+    _lib.check(L.rl4co_eval_ll_fwd(p(q), p(gk), p(gv), p(lkf), p(mask), p(taken), p(logp), p(heads), p(lse_h), p(lse_z), p(maskw),
+                                   i64(B), i64(R), i32(n), f32(10.0), f32(1.0), st), "fwd")
+    _lib.check(L.rl4co_eval_ll_bwd(p(q), p(gk), p(gv), p(lkf), p(maskw), p(taken), p(heads), p(lse_h), p(lse_z), p(dlogp), p(dheads),
+                                   p(du_t), p(dd), p(dq), p(dgk), p(dgv), p(dlkf), i64(B), i64(R), i32(n), f32(10.0), f32(1.0), st), "bwd")
+    _lib.check(L.rl4co_eval_query_bwd(p(dq), p(cur), None, p(rem), p(dpb), None, p(dwcap), i64(B), i64(S), i64(Tm), i32(n), st), "q bwd")
+    torch.cuda.synchronize()
+    for flat, numel in bufs:
+        sent = SENT if flat.dtype.is_floating_point else -7
+        assert bool((flat[:G] == sent).all()) and bool((flat[G + numel:] == sent).all())
+        assert bool(torch.isfinite(flat[G:G + numel].float()).all())
+    assert bool((q != SENT).all()) and bool((logp <= 1e-6).all())
