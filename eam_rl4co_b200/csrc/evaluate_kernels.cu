@@ -64,6 +64,40 @@ __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
+// ---- backward: power-of-two scale of the incoming gradient -------------------------------------------------------------------------
+// The backward MMAs take their operands as fp16 hi + lo: ~22 bits of mantissa but fp16's EXPONENT range.  dlogp of a training step
+// is advantage / (B S) ~ 1e-4, the quantities derived from it (du, dheads, dS) reach into fp16's subnormals and the gradients lose
+// accuracy with the loss scale (measured: 2e-3 relative at a cotangent of 1e-4, 0.2 at 1e-6, all zero at 1e-8).  Every output is
+// linear in dlogp, so the whole backward runs on dlogp * s with s = 2^-ceil(log2 max|dlogp|) (exact in fp32) and the kernels that
+// write results multiply by 1 / s in their epilogues.  ws[0] = s, ws[1] = 1 / s.
+__global__ void __launch_bounds__(1024)
+    eval_grad_scale_kernel(const float* __restrict__ dlogp, int64_t rows, float* __restrict__ ws) {
+    __shared__ float s_m[32];
+    float m = 0.f;
+    for (int64_t i = threadIdx.x; i < rows; i += 1024) {
+        const float a = fabsf(dlogp[i]);
+        m = (a <= 3.0e38f && a > m) ? a : m;      // ignores NaN / inf
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(kFull, m, o));
+    if ((threadIdx.x & 31) == 0) s_m[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        m = s_m[threadIdx.x];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(kFull, m, o));
+        if (threadIdx.x == 0) {
+            int e = 0;
+            if (m > 0.f) {
+                frexpf(m, &e);                    // m = f 2^e, f in [0.5, 1)
+                e = e > 100 ? 100 : (e < -100 ? -100 : e);
+            }
+            ws[0] = ldexpf(1.0f, -e);
+            ws[1] = ldexpf(1.0f, e);
+        }
+    }
+}
+
 // ---- backward, pointer part of the node pass on the tensor cores: dlkf[b] = dU^T O (tcgen05, split fp16) -------------------------
 // Per CTA a [128 x 128] fp32 accumulator in TMEM (rows = the 128 du_t columns = nodes; columns = the 128
 // head channels), summed over the CTA's row tiles of 64 rows (the K dimension).  A tile of du_t and heads is staged as fp32
@@ -82,8 +116,8 @@ constexpr size_t kSmem = kOffBar + 64;
 }  // namespace dlk
 
 __global__ void __launch_bounds__(256, 1)
-    eval_dlk_tc_kernel(const float* __restrict__ heads, const float* __restrict__ du_t, float* __restrict__ dlkf, int64_t R,
-                       int n) {
+    eval_dlk_tc_kernel(const float* __restrict__ heads, const float* __restrict__ du_t, const float* __restrict__ gscale,
+                       float* __restrict__ dlkf, int64_t R, int n) {
     using namespace tc;
     extern __shared__ __align__(128) unsigned char smb[];
     unsigned char* op = smb;
@@ -185,9 +219,10 @@ __global__ void __launch_bounds__(256, 1)
             tmem_ld16(src + (uint32_t)c, v);
             tc_wait_ld();
             if (node < n) {
+                const float inv_s = gscale[1];
                 float* dst = dlkf + (b * n + node) * kE + 64 * (warp >> 2) + c;
 #pragma unroll
-                for (int i = 0; i < 16; ++i) atomicAdd(dst + i, __uint_as_float(v[i]));
+                for (int i = 0; i < 16; ++i) atomicAdd(dst + i, __uint_as_float(v[i]) * inv_s);
             }
         }
     }
@@ -225,7 +260,7 @@ __device__ __forceinline__ float tanh_fast_ev(float v) {   // 1 - 2 / (1 + e^(2v
 __global__ void __launch_bounds__(pbw::kThreads, 1)
     eval_ptr_bwd_tc_kernel(const float* __restrict__ lkf, const uint32_t* __restrict__ maskw, const int64_t* __restrict__ taken,
                            const float* __restrict__ heads, const float* __restrict__ lse_z, const float* __restrict__ dlogp,
-                           float* __restrict__ dheads, float* __restrict__ du_t, int64_t R, int n, float clip, float temperature) {
+                           const float* __restrict__ gscale, float* __restrict__ dheads, float* __restrict__ du_t, int64_t R, int n, float clip, float temperature) {
     using namespace tc;
     extern __shared__ __align__(128) unsigned char smb[];
     float* s_g = reinterpret_cast<float*>(smb + pbw::kOffRow);
@@ -308,7 +343,7 @@ __global__ void __launch_bounds__(pbw::kThreads, 1)
         if (tid < pbw::kT) {
             const bool ok = tid < rows;
             const int64_t row = b * R + (ok ? rt + tid : r0);
-            pre_g = ok ? dlogp[row] : 0.f;
+            pre_g = ok ? dlogp[row] * gscale[0] : 0.f;
             pre_lz = ok ? lse_z[row] : 0.f;
             pre_a = ok ? (int)taken[row] : -1;
 #pragma unroll
@@ -705,7 +740,8 @@ template <int KT, int NH>
 __global__ void __launch_bounds__(256, (KT == 64 && NH == 4) ? 2 : 1)
     eval_dkv_tc_kernel(const float* __restrict__ q, const float* __restrict__ gk, const float* __restrict__ gv,
                        const uint32_t* __restrict__ maskw, const float* __restrict__ lse_h, const float* __restrict__ dheads,
-                       const float* __restrict__ dd, float* __restrict__ dgk, float* __restrict__ dgv, int64_t R, int n) {
+                       const float* __restrict__ dd, const float* __restrict__ gscale, float* __restrict__ dgk,
+                       float* __restrict__ dgv, int64_t R, int n) {
     using namespace tc;
     using L = Dkv<KT, NH>;
     constexpr int NW = KT / 32;                          // 32-row words per tile
@@ -949,12 +985,13 @@ __global__ void __launch_bounds__(256, (KT == 64 && NH == 4) ? 2 : 1)
             tmem_ld16(lane_base + 2u * KT + 32u * (uint32_t)hl + 16u, k);
             tc_wait_ld();
             if (node < n) {
+                const float inv_s = gscale[1];
                 float* pv = dgv + ((size_t)b * n + node) * kE + 16 * (h0 + hl);
                 float* pk = dgk + ((size_t)b * n + node) * kE + 16 * (h0 + hl);
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
-                    atomicAdd(pv + i, __uint_as_float(v[i]));
-                    atomicAdd(pk + i, __uint_as_float(k[i]));
+                    atomicAdd(pv + i, __uint_as_float(v[i]) * inv_s);
+                    atomicAdd(pk + i, __uint_as_float(k[i]) * inv_s);
                 }
             }
         }
@@ -1278,7 +1315,8 @@ constexpr size_t kSmem = kOffBar + 64;
 __global__ void __launch_bounds__(256, 2)
     eval_dq_tc_kernel(const float* __restrict__ q, const float* __restrict__ gk, const float* __restrict__ gv,
                       const uint32_t* __restrict__ maskw, const float* __restrict__ heads, const float* __restrict__ lse_h,
-                      const float* __restrict__ dheads, float* __restrict__ dq, float* __restrict__ dd_out, int64_t R, int n) {
+                      const float* __restrict__ dheads, const float* __restrict__ gscale, float* __restrict__ dq,
+                      float* __restrict__ dd_out, int64_t R, int n) {
     using namespace tc;
     extern __shared__ __align__(128) unsigned char smb[];
     uint32_t* s_mw = reinterpret_cast<uint32_t*>(smb + dqk::kOffMaskW);
@@ -1382,16 +1420,17 @@ __global__ void __launch_bounds__(256, 2)
     bool pending = false;
     int64_t epi_rt = 0;
     int epi_rows = 0, epi_h = 0, cnt = 0;
+    const float out_sc = 0.25f * gscale[1];              // the query scale and the inverse gradient scale
     auto epilogue = [&]() {   // dq of the previous (tile, head): slot (cnt - 1) & 1, 8 of its 16 columns per node half
         uint32_t v[8];
         tmem_ld8(lane_base + col_dq + 16u * (uint32_t)((cnt - 1) & 1) + 8u * (uint32_t)chalf, v);
         tc_wait_ld();
         if (r < epi_rows) {
             float* dst = dq + (b * R + epi_rt + r) * kE + 16 * epi_h + 8 * chalf;
-            *reinterpret_cast<float4*>(dst) = make_float4(0.25f * __uint_as_float(v[0]), 0.25f * __uint_as_float(v[1]),
-                                                          0.25f * __uint_as_float(v[2]), 0.25f * __uint_as_float(v[3]));
-            *reinterpret_cast<float4*>(dst + 4) = make_float4(0.25f * __uint_as_float(v[4]), 0.25f * __uint_as_float(v[5]),
-                                                              0.25f * __uint_as_float(v[6]), 0.25f * __uint_as_float(v[7]));
+            *reinterpret_cast<float4*>(dst) = make_float4(out_sc * __uint_as_float(v[0]), out_sc * __uint_as_float(v[1]),
+                                                          out_sc * __uint_as_float(v[2]), out_sc * __uint_as_float(v[3]));
+            *reinterpret_cast<float4*>(dst + 4) = make_float4(out_sc * __uint_as_float(v[4]), out_sc * __uint_as_float(v[5]),
+                                                              out_sc * __uint_as_float(v[6]), out_sc * __uint_as_float(v[7]));
         }
     };
     for (int t = 0; t < ntiles; ++t) {
@@ -1598,35 +1637,37 @@ extern "C" int rl4co_eval_ll_fwd(const float* q, const float* gk, const float* g
 
 extern "C" int rl4co_eval_ll_bwd(const float* q, const float* gk, const float* gv, const float* lkf, const uint32_t* maskw,
                                  const int64_t* taken, const float* heads, const float* lse_h, const float* lse_z,
-                                 const float* dlogp, float* dheads, float* du_t, float* dd, float* dq, float* dgk,
-                                 float* dgv, float* dlkf, int64_t B, int64_t R, int32_t n_nodes, float tanh_clipping, float temperature,
-                                 void* stream) {
-    R4_CHECK_ARG(q && gk && gv && lkf && maskw && taken && heads && lse_h && lse_z && dlogp && dheads && du_t && dd && dq &&
-                     dgk && dgv && dlkf,
+                                 const float* dlogp, float* dheads, float* du_t, float* dd, float* scale_ws, float* dq,
+                                 float* dgk, float* dgv, float* dlkf, int64_t B, int64_t R, int32_t n_nodes, float tanh_clipping,
+                                 float temperature, void* stream) {
+    R4_CHECK_ARG(q && gk && gv && lkf && maskw && taken && heads && lse_h && lse_z && dlogp && dheads && du_t && dd && scale_ws &&
+                     dq && dgk && dgv && dlkf,
                  "eval_ll_bwd: null pointer");
     int rc;
     if ((rc = eval_check("eval_ll_bwd", B, R, n_nodes, temperature))) return rc;
     if (B == 0 || R == 0) return RL4CO_OK;
     cudaStream_t st = (cudaStream_t)stream;
     dim3 g1((unsigned)B, (unsigned)ev::grid_split(B, 1));
+    ev::eval_grad_scale_kernel<<<1, 1024, 0, st>>>(dlogp, B * R, scale_ws);
+    R4_CHECK_LAUNCH("eval_ll_bwd (gradient scale)");
     if ((rc = ev::set_smem(ev::eval_ptr_bwd_tc_kernel, ev::pbw::kSmem, "eval_ll_bwd (row pass, pointer)"))) return rc;
-    ev::eval_ptr_bwd_tc_kernel<<<g1, ev::pbw::kThreads, ev::pbw::kSmem, st>>>(lkf, maskw, taken, heads, lse_z, dlogp, dheads, du_t, R, n_nodes,
-                                                               tanh_clipping, temperature);
+    ev::eval_ptr_bwd_tc_kernel<<<g1, ev::pbw::kThreads, ev::pbw::kSmem, st>>>(lkf, maskw, taken, heads, lse_z, dlogp, scale_ws, dheads,
+                                                                              du_t, R, n_nodes, tanh_clipping, temperature);
     R4_CHECK_LAUNCH("eval_ll_bwd (row pass, pointer)");
     if ((rc = ev::set_smem(ev::eval_dq_tc_kernel, ev::dqk::kSmem, "eval_ll_bwd (row pass, glimpse)"))) return rc;
     dim3 g2((unsigned)B, (unsigned)ev::grid_split(4 * B, 2), 4u);
-    ev::eval_dq_tc_kernel<<<g2, 256, ev::dqk::kSmem, st>>>(q, gk, gv, maskw, heads, lse_h, dheads, dq, dd, R, n_nodes);
+    ev::eval_dq_tc_kernel<<<g2, 256, ev::dqk::kSmem, st>>>(q, gk, gv, maskw, heads, lse_h, dheads, scale_ws, dq, dd, R, n_nodes);
     R4_CHECK_LAUNCH("eval_ll_bwd (row pass)");
     // node pass (tcgen05): dlkf = dU^T O, then dgv = P^T dO and dgk = dS^T (0.25 Q)
     if ((rc = ev::set_smem(ev::eval_dlk_tc_kernel, ev::dlk::kSmem, "eval_ll_bwd (dlkf)"))) return rc;
     dim3 g3((unsigned)B, (unsigned)ev::grid_split(B, 1));
-    ev::eval_dlk_tc_kernel<<<g3, 256, ev::dlk::kSmem, st>>>(heads, du_t, dlkf, R, n_nodes);
+    ev::eval_dlk_tc_kernel<<<g3, 256, ev::dlk::kSmem, st>>>(heads, du_t, scale_ws, dlkf, R, n_nodes);
     R4_CHECK_LAUNCH("eval_ll_bwd (dlkf)");
     {   // two CTAs per SM: 64-row tiles, four heads each (blockIdx.z); <128, 8> - one CTA per SM - measured 1.96 against 1.47 ms
         auto kern = ev::eval_dkv_tc_kernel<64, 4>;
         if ((rc = ev::set_smem(kern, ev::Dkv<64, 4>::kSmem, "eval_ll_bwd (dgk, dgv)"))) return rc;
         dim3 g4((unsigned)B, (unsigned)ev::grid_split(2 * B, 2), 2u);
-        kern<<<g4, 256, ev::Dkv<64, 4>::kSmem, st>>>(q, gk, gv, maskw, lse_h, dheads, dd, dgk, dgv, R, n_nodes);
+        kern<<<g4, 256, ev::Dkv<64, 4>::kSmem, st>>>(q, gk, gv, maskw, lse_h, dheads, dd, scale_ws, dgk, dgv, R, n_nodes);
     }
     R4_CHECK_LAUNCH("eval_ll_bwd (dgk, dgv)");
     return RL4CO_OK;

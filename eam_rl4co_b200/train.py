@@ -120,12 +120,13 @@ class _FusedEvaluate(torch.autograd.Function):
         n = gk.shape[1]
         dlogp = dlogp.contiguous().float()
         dheads, du_t, dd = torch.empty_like(heads), torch.empty_like(heads), torch.empty_like(lse_h)   # scratch
+        scale_ws = torch.empty(2, device=q.device)                                                     # scratch
         dq = torch.empty_like(q)
         dgk, dgv, dlkf = torch.zeros_like(gk), torch.zeros_like(gv), torch.zeros_like(lkf)
         rc = _lib.lib().rl4co_eval_ll_bwd(_lib.ptr(q), _lib.ptr(gk), _lib.ptr(gv), _lib.ptr(lkf), _lib.ptr(maskw),
                                           _lib.ptr(taken), _lib.ptr(heads), _lib.ptr(lse_h), _lib.ptr(lse_z), _lib.ptr(dlogp),
-                                          _lib.ptr(dheads), _lib.ptr(du_t), _lib.ptr(dd), _lib.ptr(dq), _lib.ptr(dgk), _lib.ptr(dgv),
-                                          _lib.ptr(dlkf),
+                                          _lib.ptr(dheads), _lib.ptr(du_t), _lib.ptr(dd), _lib.ptr(scale_ws), _lib.ptr(dq),
+                                          _lib.ptr(dgk), _lib.ptr(dgv), _lib.ptr(dlkf),
                                           C.c_int64(B), C.c_int64(R), C.c_int32(n), C.c_float(ctx.scalars[0]),
                                           C.c_float(ctx.scalars[1]), _lib.stream_ptr())
         _lib.check(rc, "rl4co_eval_ll_bwd")

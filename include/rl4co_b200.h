@@ -279,15 +279,17 @@ int rl4co_best_of_starts(const float* reward, const int64_t* actions, int64_t B,
  *      backward reuses: heads [B,R,128], lse_h [B,R,8] (log-sum-exp of each head's scores), lse_z [B,R], maskw [B,R,4]
  *      (the mask as bit words).
  * bwd: given dlogp [B,R]: dq [B,R,128] (written), dgk / dgv / dlkf [B,n,128] (ACCUMULATED: zero them first);
- *      dheads, du_t [B,R,128] and dd [B,R,8] are scratch.  n_nodes <= rl4co_eval_ll_max_nodes() (128).                                  */
+ *      dheads, du_t [B,R,128], dd [B,R,8] and scale_ws [2] are scratch.  The backward runs on dlogp * s, s the power of two that
+ *      brings max|dlogp| into [0.5, 1) (scale_ws = {s, 1/s}), and unscales its outputs: the fp16 hi / lo MMA operands keep their
+ *      accuracy at any loss scale.  n_nodes <= rl4co_eval_ll_max_nodes() (128).                                              */
 int32_t rl4co_eval_ll_max_nodes(void);
 int rl4co_eval_ll_fwd(const float* q, const float* gk, const float* gv, const float* lkf, const uint8_t* mask,
                       const int64_t* taken, float* logp, float* heads, float* lse_h, float* lse_z, uint32_t* maskw,
                       int64_t B, int64_t R, int32_t n_nodes, float tanh_clipping, float temperature, void* stream);
 int rl4co_eval_ll_bwd(const float* q, const float* gk, const float* gv, const float* lkf, const uint32_t* maskw,
                       const int64_t* taken, const float* heads, const float* lse_h, const float* lse_z, const float* dlogp,
-                      float* dheads, float* du_t, float* dd, float* dq, float* dgk, float* dgv, float* dlkf, int64_t B,
-                      int64_t R, int32_t n_nodes, float tanh_clipping, float temperature, void* stream);
+                      float* dheads, float* du_t, float* dd, float* scale_ws, float* dq, float* dgk, float* dgv, float* dlkf,
+                      int64_t B, int64_t R, int32_t n_nodes, float tanh_clipping, float temperature, void* stream);
 
 /* ---- the glimpse query of all teacher-forced rows and its gradient (context.py:118-157, am/decoder.py:223-224) ----------
  * q[b,s,t,:] = pb[b,cur[b,s,t],:] (+ pa[b,first[b,s],:]) (+ rem[b,s,t] * wcap[:]) (+ ctx[b,:]), 128 channels, where

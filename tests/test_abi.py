@@ -55,9 +55,9 @@ def test_argument_errors_return_codes_without_launching():
                              C.c_int32(20), C.c_float(10.0), C.c_float(1.0), None)
     assert rc == -1 and b"null pointer" in L.rl4co_last_error()
     one = C.c_void_p(16)                                           # never dereferenced: the size checks come first
-    rc = L.rl4co_eval_ll_bwd(*([one] * 17), C.c_int64(2), C.c_int64(3), C.c_int32(200), C.c_float(10.0), C.c_float(1.0), None)
+    rc = L.rl4co_eval_ll_bwd(*([one] * 18), C.c_int64(2), C.c_int64(3), C.c_int32(200), C.c_float(10.0), C.c_float(1.0), None)
     assert rc == -1 and b"n_nodes=200" in L.rl4co_last_error()
-    rc = L.rl4co_eval_ll_bwd(*([one] * 17), C.c_int64(2), C.c_int64(3), C.c_int32(50), C.c_float(10.0), C.c_float(0.0), None)
+    rc = L.rl4co_eval_ll_bwd(*([one] * 18), C.c_int64(2), C.c_int64(3), C.c_int32(50), C.c_float(10.0), C.c_float(0.0), None)
     assert rc == -1 and b"temperature" in L.rl4co_last_error()
     sz = (C.c_int64(2), C.c_int64(3), C.c_int64(4))
     rc = L.rl4co_eval_query_fwd(one, None, None, None, one, None, None, one, *sz, C.c_int32(129), None)

@@ -170,6 +170,17 @@ def _eager_rows(q, gk, gv, lkf, mask, taken, clip, temp):
 @pytest.mark.parametrize("B,R,n,clip,temp", [(3, 37, 101, 10.0, 1.0), (2, 5, 2, 10.0, 1.0), (1, 1, 112, 0.0, 0.5), (2, 131, 128, 10.0, 1.0),
                                               (5, 130, 64, 10.0, 2.0), (70, 9, 21, 10.0, 1.0)])
 def test_fused_evaluate_rows_against_fp64(B, R, n, clip, temp):
+    _fused_rows_against_fp64(B, R, n, clip, temp, 1.0)
+
+
+@pytest.mark.parametrize("cot_scale", [1e-4, 1e-8, 1e-20, 3e4])
+def test_fused_evaluate_gradients_at_any_loss_scale(cot_scale):
+    """dlogp of a training step is advantage / (B S) ~ 1e-4 and below: the backward's fp16 hi / lo operands must not lose the
+    gradient to fp16's exponent range (rl4co_eval_ll_bwd rescales by a power of two)."""
+    _fused_rows_against_fp64(3, 37, 101, 10.0, 1.0, cot_scale)
+
+
+def _fused_rows_against_fp64(B, R, n, clip, temp, cot_scale):
     """Ragged row counts (not a multiple of the four-row groups or of the CTA split), the smallest and largest node
     counts, rows with a single feasible node, more instances than SMs / 2."""
     g = torch.Generator().manual_seed(B * 1000 + R * 10 + n)
@@ -179,7 +190,7 @@ def test_fused_evaluate_rows_against_fp64(B, R, n, clip, temp):
     taken = torch.randint(0, n, (B, R), generator=g)
     mask[:, ::3] = False                                          # every third row: only the taken node is feasible
     mask.scatter_(2, taken[..., None], True)
-    cot = rnd(B, R)
+    cot = rnd(B, R) * cot_scale
     args64 = [t.double().to(DEV).requires_grad_(True) for t in (q, gk, gv, lkf)]
     ref = _eager_rows(*args64, mask.to(DEV), taken.to(DEV), clip, temp)
     (ref * cot.double().to(DEV)).sum().backward()
@@ -189,7 +200,7 @@ def test_fused_evaluate_rows_against_fp64(B, R, n, clip, temp):
     assert (got.double() - ref).abs().max().item() < 2e-5 * max(1.0, ref.abs().max().item())
     assert (got[:, ::3].abs() < 1e-6).all()                       # a single feasible node has probability one
     for a32, a64, name in zip(args32, args64, ("q", "gk", "gv", "lkf")):
-        scale = max(a64.grad.abs().max().item(), 1e-6)
+        scale = max(a64.grad.abs().max().item(), 1e-6 * cot_scale)
         assert (a32.grad.double() - a64.grad).abs().max().item() / scale < 1e-4, name
 
 
@@ -288,7 +299,7 @@ def test_evaluate_entry_points_stay_inside_their_buffers(B, S, Tm, n):
     dlogp = dev(torch.randn(B, R, generator=g))
     q, heads, dheads, du_t, dq = (guarded(B, R, 128) for _ in range(5))
     logp, lse_z, lse_h, dd = guarded(B, R), guarded(B, R), guarded(B, R, 8), guarded(B, R, 8)
-    maskw = guarded(B, R, 4, dtype=torch.int32)
+    maskw, ws = guarded(B, R, 4, dtype=torch.int32), guarded(2)
     dgk, dgv, dlkf, dpb, dwcap = guarded(B, n, 128), guarded(B, n, 128), guarded(B, n, 128), guarded(B, n, 128), guarded(128)
     for t in (dgk, dgv, dlkf, dpb, dwcap):
         t.zero_()
@@ -298,7 +309,8 @@ def test_evaluate_entry_points_stay_inside_their_buffers(B, S, Tm, n):
     _lib.check(L.rl4co_eval_ll_fwd(p(q), p(gk), p(gv), p(lkf), p(mask), p(taken), p(logp), p(heads), p(lse_h), p(lse_z), p(maskw),
                                    i64(B), i64(R), i32(n), f32(10.0), f32(1.0), st), "fwd")
     _lib.check(L.rl4co_eval_ll_bwd(p(q), p(gk), p(gv), p(lkf), p(maskw), p(taken), p(heads), p(lse_h), p(lse_z), p(dlogp), p(dheads),
-                                   p(du_t), p(dd), p(dq), p(dgk), p(dgv), p(dlkf), i64(B), i64(R), i32(n), f32(10.0), f32(1.0), st), "bwd")
+                                   p(du_t), p(dd), p(ws), p(dq), p(dgk), p(dgv), p(dlkf), i64(B), i64(R), i32(n), f32(10.0), f32(1.0), st),
+               "bwd")
     _lib.check(L.rl4co_eval_query_bwd(p(dq), p(cur), None, p(rem), p(dpb), None, p(dwcap), i64(B), i64(S), i64(Tm), i32(n), st), "q bwd")
     torch.cuda.synchronize()
     for flat, numel in bufs:
