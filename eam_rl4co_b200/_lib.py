@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # RL4CO_B200_LIB: experiment builds of the same sources (profiles/variants.sh); the product path is the in-tree library
 LIB_PATH = os.environ.get("RL4CO_B200_LIB") or os.path.join(_HERE, "librl4co_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["capi.cu", "env_kernels.cu", "decode_kernels.cu", "rollout_kernel.cu", "rollout_coop.cu", "rollout_tc.cu", "encoder_tc.cu", "reduce_kernels.cu", "data_kernels.cu", "evaluate_kernels.cu", "evaluate_query.cu"]
+SOURCES = ["capi.cu", "env_kernels.cu", "decode_kernels.cu", "rollout_kernel.cu", "rollout_coop.cu", "rollout_tc.cu", "encoder_tc.cu", "reduce_kernels.cu", "data_kernels.cu", "evaluate_kernels.cu", "evaluate_query.cu", "norm_kernels.cu"]
 
 ENV_TSP, ENV_CVRP = 0, 1
 MODE_GREEDY, MODE_SAMPLING, MODE_EVALUATE = 0, 1, 2
@@ -35,7 +35,7 @@ EXPORTS = [
     "rl4co_cvrp_action_mask", "rl4co_tour_reward", "rl4co_select", "rl4co_decode_step",
     "rl4co_rollout", "rl4co_rollout_noalloc", "rl4co_noalloc_max_instances", "rl4co_noise_gumbel", "rl4co_tc_image_bytes", "rl4co_tc_preferred_layout", "rl4co_tc_pack", "rl4co_tc_decode_step",
     "rl4co_enc_packed_bytes", "rl4co_enc_pack_weight", "rl4co_enc_linear", "rl4co_enc_ffn", "rl4co_enc_attn_block", "rl4co_enc_attention", "rl4co_best_of_starts", "rl4co_generate_instances", "rl4co_replay_states",
-    "rl4co_eval_ll_max_nodes", "rl4co_eval_ll_fwd", "rl4co_eval_ll_bwd", "rl4co_eval_query_fwd", "rl4co_eval_query_bwd",
+    "rl4co_eval_ll_max_nodes", "rl4co_eval_ll_fwd", "rl4co_eval_ll_bwd", "rl4co_eval_query_fwd", "rl4co_eval_query_bwd", "rl4co_instnorm_max_nodes", "rl4co_instnorm_fwd", "rl4co_instnorm_bwd",
 ]
 
 

@@ -304,6 +304,16 @@ int rl4co_eval_query_fwd(const float* pb, const float* pa, const float* wcap, co
 int rl4co_eval_query_bwd(const float* dq, const int64_t* cur, const int64_t* first, const float* rem, float* dpb,
                          float* dpa, float* dwcap, int64_t B, int64_t S, int64_t Tm, int32_t n_nodes, void* stream);
 
+/* ---- instance normalisation of the encoder's TRAINING path and its backward (nn/ops.py:48-49: nn.InstanceNorm1d over the node
+ * axis of x [B,N,128], affine w / bias [128], biased variance, eps inside the square root); fp32.  fwd writes y and the
+ * statistics mean / rstd [B,128] the backward reads; bwd writes dx and ACCUMULATES dw / db [128] (zero them first).
+ * N <= rl4co_instnorm_max_nodes() (128).  (Inference runs the fused encoder kernels, rl4co_enc_*.)                          */
+int32_t rl4co_instnorm_max_nodes(void);
+int rl4co_instnorm_fwd(const float* x, const float* w, const float* bias, float* y, float* mean, float* rstd, int64_t B,
+                       int32_t N, float eps, void* stream);
+int rl4co_instnorm_bwd(const float* x, const float* w, const float* mean, const float* rstd, const float* dy, float* dx,
+                       float* dw, float* db, int64_t B, int32_t N, void* stream);
+
 /* ---- on-device instance generation: the input spec of tsp/generator.py:53-62 and cvrp/generator.py:120-147 -----------
  * locs [B, n_loc, 2] uniform in [0,1); CVRP also depot [B,2] and demand [B, n_loc] = integer 1..9 / capacity.  Values come
  * from the counter hash keyed (seed, inst_offset + b, element), so shards of a global batch agree with the whole.   */

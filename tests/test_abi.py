@@ -68,6 +68,11 @@ def test_argument_errors_return_codes_without_launching():
     assert rc == -1 and b"dwcap and rem" in L.rl4co_last_error()
     rc = L.rl4co_eval_query_bwd(one, one, None, None, None, None, None, *sz, C.c_int32(20), None)
     assert rc == -1 and b"null dq / cur / dpb" in L.rl4co_last_error()
+    assert L.rl4co_instnorm_max_nodes() == 128
+    rc = L.rl4co_instnorm_fwd(one, one, one, one, one, one, C.c_int64(2), C.c_int32(129), C.c_float(1e-5), None)
+    assert rc == -1 and b"N=129" in L.rl4co_last_error()
+    rc = L.rl4co_instnorm_bwd(one, one, one, one, one, one, one, None, C.c_int64(2), C.c_int32(20), None)
+    assert rc == -1 and b"null pointer" in L.rl4co_last_error()
 
 
 def test_no_fallback_when_library_missing(monkeypatch):

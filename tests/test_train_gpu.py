@@ -320,3 +320,34 @@ def test_evaluate_entry_points_stay_inside_their_buffers(B, S, Tm, n):
         assert bool((flat[:G] == sent).all()) and bool((flat[G + numel:] == sent).all())
         assert bool(torch.isfinite(flat[G:G + numel].float()).all())
     assert bool((q != SENT).all()) and bool((logp <= 1e-6).all())
+
+
+@pytest.mark.parametrize("B,N", [(3, 21), (70, 101), (2, 128), (4, 2), (5, 9)])
+def test_instance_norm_kernels_against_fp64(B, N):
+    """rl4co_instnorm_fwd / rl4co_instnorm_bwd against nn/ops.py:48-49 (nn.InstanceNorm1d over the node axis, affine)
+    in fp64: output and the gradients w.r.t. input, weight and bias."""
+    from eam_rl4co_b200 import encoder as E
+    g = torch.Generator().manual_seed(B * 31 + N)
+    x = torch.randn(B, N, 128, generator=g) * 3 + 0.5
+    w, b = torch.randn(128, generator=g), torch.randn(128, generator=g)
+    cot = torch.randn(B, N, 128, generator=g)
+    ref_mod = torch.nn.InstanceNorm1d(128, affine=True).double().to(DEV)
+    ref_mod.weight.data.copy_(w)
+    ref_mod.bias.data.copy_(b)
+    x64 = x.double().to(DEV).requires_grad_(True)
+    ref = ref_mod(x64.permute(0, 2, 1)).permute(0, 2, 1)
+    (ref * cot.double().to(DEV)).sum().backward()
+    x32, w32, b32 = (t.to(DEV).requires_grad_(True) for t in (x, w, b))
+    assert E.instance_norm_kernel_applies(x32)
+    got = E._InstanceNormFn.apply(x32, w32, b32, ref_mod.eps)
+    (got * cot.to(DEV)).sum().backward()
+    tol = lambda a, r: (a.double() - r).abs().max().item() / max(r.abs().max().item(), 1e-6)
+    assert tol(got, ref) < 1e-5
+    assert tol(x32.grad, x64.grad) < 1e-4
+    assert tol(w32.grad, ref_mod.weight.grad) < 1e-5 and tol(b32.grad, ref_mod.bias.grad) < 1e-5
+    # the module routes its differentiable CUDA path through the kernel and equals its own PyTorch statement
+    mod = E.Normalization(128, "instance").to(DEV)
+    xa = x.to(DEV)
+    with torch.no_grad():
+        plain = mod(xa)
+    assert tol(mod(xa.clone().requires_grad_(True)), plain.double()) < 1e-5
