@@ -245,7 +245,7 @@ def train_leg(dev, rank, world, steps=8, warmup=3):
     N, B = 100, 64
     torch.manual_seed(4321)
     pol = P.POMOPolicy("cvrp").to(dev).train()
-    opt = torch.optim.Adam(pol.parameters(), lr=1e-4)
+    opt = torch.optim.Adam(pol.parameters(), lr=1e-4, fused=True)      # PyTorch's single-kernel Adam (optim_helpers.py:21-38 builds torch.optim.Adam)
     env = P.get_env("cvrp", generator_params=dict(num_loc=N), device=dev)
     gen = P.DeviceGenerator("cvrp", num_loc=N, seed=7, device=dev)
     stats = None

@@ -13,7 +13,7 @@ def main():
     dev = torch.device("cuda", 0)
     torch.manual_seed(4321)
     pol = P.POMOPolicy("cvrp").to(dev).train()
-    opt = torch.optim.Adam(pol.parameters(), lr=1e-4)
+    opt = torch.optim.Adam(pol.parameters(), lr=1e-4, fused=True)
     env = P.get_env("cvrp", generator_params=dict(num_loc=100), device=dev)
     inst = {k: v for k, v in P.CVRPGenerator(num_loc=100)(B).items() if k != "capacity"}
     td = env.reset(P.TensorDict({k: v.to(dev) for k, v in inst.items()}, batch_size=[B]))

@@ -351,3 +351,27 @@ def test_instance_norm_kernels_against_fp64(B, N):
     with torch.no_grad():
         plain = mod(xa)
     assert tol(mod(xa.clone().requires_grad_(True)), plain.double()) < 1e-5
+
+
+def test_split_k_linear_gradients_equal_nn_linear():
+    """encoder._SplitKLinearFn (weight gradient as a split-K bmm) against nn.Linear's own autograd on the encoder's
+    feed-forward block at the c5 token count."""
+    from eam_rl4co_b200 import encoder as E
+    torch.manual_seed(3)
+    mlp = E.MLP(128, 512).to(DEV)
+    x = torch.randn(64, 101, 128, device=DEV)
+    cot = torch.randn(64, 101, 128, device=DEV)
+    res = {}
+    for flag in (True, False):
+        E.SPLITK_LINEAR = flag
+        try:
+            xi = x.clone().requires_grad_(True)
+            for p in mlp.parameters():
+                p.grad = None
+            (mlp(xi) * cot).sum().backward()
+            res[flag] = [xi.grad.clone()] + [p.grad.clone() for p in mlp.parameters()]
+        finally:
+            E.SPLITK_LINEAR = True
+    assert E._split_chunks(64 * 101) == 32
+    for a, b in zip(res[True], res[False]):
+        assert (a - b).abs().max().item() < 2e-5 * max(b.abs().max().item(), 1e-6)
