@@ -177,8 +177,28 @@ class MLP(nn.Module):
         return _linear(self.lins[1], F.relu(_linear(self.lins[0], x)))
 
 
+# Derived copies of the weights (packed fp16 MMA tiles, folded BatchNorm affines) are cached.  A parameter's `_version`
+# counter does NOT see every in-place update: PyTorch's fused optimisers (`torch.optim.Adam(..., fused=True)`) write the
+# parameters from a multi-tensor kernel without touching it - measured: after one fused Adam step the rollout ran on the
+# previous step's packed decoder weights (log-likelihood 21 off its re-evaluation).  Every `torch.optim` step therefore
+# moves a global epoch that is part of every cache stamp.
+_OPTIMIZER_EPOCH = [0]
+
+
+def _bump_optimizer_epoch(*_args, **_kwargs):
+    _OPTIMIZER_EPOCH[0] += 1
+
+
+try:
+    from torch.optim.optimizer import register_optimizer_step_post_hook as _register_step_hook
+    _register_step_hook(_bump_optimizer_epoch)
+except ImportError:                                   # pragma: no cover - torch < 2.0
+    pass
+
+
 class WeightPacker:
-    """fp32 weight [n_out, k] -> fp16 hi/lo MMA tiles of csrc/encoder_tc.cu, cached per (key, version, storage)."""
+    """fp32 weight [n_out, k] -> fp16 hi/lo MMA tiles of csrc/encoder_tc.cu, cached per (key, version, storage,
+    optimiser epoch)."""
 
     def __init__(self):
         self.cache = {}
@@ -188,9 +208,10 @@ class WeightPacker:
 
     @staticmethod
     def stamp(w):
-        # `_version` moves with in-place updates autograd can see (optimiser steps), data_ptr with re-allocation
-        # (`.to`, `load_state_dict(assign=True)`); writes through `.data` that keep both need invalidate_packed()
-        return (w._version, w.data_ptr(), w.device)
+        # `_version` moves with in-place updates autograd can see, data_ptr with re-allocation (`.to`,
+        # `load_state_dict(assign=True)`), the epoch with every torch.optim step; writes through `.data` outside an
+        # optimiser that keep all three need invalidate_packed()
+        return (w._version, w.data_ptr(), w.device, _OPTIMIZER_EPOCH[0])
 
     def pack(self, w, key=None, stamp=None):
         key = id(w) if key is None else key

@@ -375,3 +375,23 @@ def test_split_k_linear_gradients_equal_nn_linear():
     assert E._split_chunks(64 * 101) == 32
     for a, b in zip(res[True], res[False]):
         assert (a - b).abs().max().item() < 2e-5 * max(b.abs().max().item(), 1e-6)
+
+
+def test_fused_optimizer_does_not_leave_stale_packed_weights():
+    """torch.optim.Adam(fused=True) updates the parameters without moving their `_version`: the packed fp16 copies of the
+    decoder / encoder weights must still follow (the caches are stamped with a global optimiser-step epoch).  Measured
+    before the fix: the rollout of the second step ran on the first step's weights, ll_gap = 21."""
+    inst, pol, env, td = _setup("cvrp", 4, 20, seed=13)
+    pol.train()
+    opt = torch.optim.Adam(pol.parameters(), lr=1e-3, fused=True)
+    for it in range(4):
+        stats = train.pomo_train_step(pol, env, td.clone(), optimizer=opt, noise_seed=it)
+        assert stats["ll_gap"] < 1e-3, (it, stats)
+    pol.eval()
+    net = pol.encoder.net
+    with torch.no_grad():
+        hk, _ = pol.encoder(td)
+        net.use_kernels = False
+        ht, _ = pol.encoder(td)
+        net.use_kernels = True
+    assert (hk - ht).abs().max().item() < 1e-4
