@@ -82,3 +82,28 @@ def test_folded_tables_equal_reference_cache_algebra():
         lg = torch.einsum("be,bne->bn", heads, c.logit_key_folded)
         assert torch.allclose(lg, lg_ref, atol=1e-4, rtol=1e-4)
         assert torch.allclose(c.logit_key, ref["logit_key"], atol=1e-5)
+
+
+def test_cache_stamp_follows_optimizer_steps_and_split_k_linear_on_cpu():
+    """Host logic of two training-path pieces: (1) every torch.optim step moves the stamp the packed-weight caches are keyed
+    by (fused optimisers do not move a parameter's `_version`); (2) the split-K weight gradient of the encoder's Linear
+    layers equals nn.Linear's autograd (pure torch ops, checked here on CPU)."""
+    import torch
+    from eam_rl4co_b200 import encoder as E
+    w = torch.nn.Parameter(torch.randn(8, 8))
+    before = E.WeightPacker.stamp(w)
+    opt = torch.optim.SGD([w], lr=0.1)
+    w.grad = torch.ones_like(w)
+    opt.step()
+    assert E.WeightPacker.stamp(w) != before and E.WeightPacker.stamp(w)[3] == before[3] + 1
+    assert E._split_chunks(64 * 101) == 32 and E._split_chunks(101) == 1 and E._split_chunks(512) == 4
+    torch.manual_seed(0)
+    lin = torch.nn.Linear(16, 24)
+    x = torch.randn(8, 64, 16, requires_grad=True)
+    cot = torch.randn(8, 64, 24)
+    (E._SplitKLinearFn.apply(x, lin.weight, lin.bias) * cot).sum().backward()
+    got = (x.grad.clone(), lin.weight.grad.clone(), lin.bias.grad.clone())
+    x.grad = lin.weight.grad = lin.bias.grad = None
+    (lin(x) * cot).sum().backward()
+    for a, b in zip(got, (x.grad, lin.weight.grad, lin.bias.grad)):
+        assert torch.allclose(a, b, rtol=1e-5, atol=1e-5)
